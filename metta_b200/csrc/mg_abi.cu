@@ -1,0 +1,462 @@
+// mg_abi.cu -- the C-ABI of libmettagrid_b200.so (declared in include/mettagrid_b200.h).
+//
+// Plain pointers and sizes only. A batch of environments is an opaque handle; observation,
+// reward, terminal, truncation and action buffers are caller-owned device memory bound with
+// mg_set_buffers, exactly like MettaGrid::set_buffers binds caller-owned numpy arrays
+// (bindings/mettagrid_c.cpp:721-738). Errors come back as non-zero status codes with a message
+// in mg_last_error(); nothing here falls back to the CPU.
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "mg_kernels.cuh"
+
+static thread_local std::string g_err;
+
+#define MG_OK 0
+#define MG_ERR_ARG 1
+#define MG_ERR_CUDA 2
+#define MG_ERR_STATE 3
+
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t err__ = (expr);                                                                 \
+    if (err__ != cudaSuccess)                                                                   \
+      return fail(MG_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(err__));          \
+  } while (0)
+
+struct MgEnvs {
+  MgBatch b;
+  int device;
+  std::vector<int32_t> cfg_host;
+  std::vector<void*> allocs;
+  long long launches;
+  bool maps_loaded, buffers_bound, owns_buffers;
+  // host-buffer path (mg_step_host): device mirrors + pinned staging
+  uint8_t* h_pinned;
+  size_t h_pinned_bytes;
+  cudaStream_t stream;
+  uint8_t* d_mask;
+  int32_t* d_tmp;  // small scratch for set_inventory
+};
+
+template <typename T>
+static int dev_alloc(MgEnvs* e, T** out, size_t count, bool zero = true) {
+  void* p = nullptr;
+  size_t bytes = count * sizeof(T);
+  if (bytes == 0) bytes = 16;
+  CUDA_TRY(cudaMalloc(&p, bytes));
+  if (zero) CUDA_TRY(cudaMemset(p, 0, bytes));
+  e->allocs.push_back(p);
+  *out = reinterpret_cast<T*>(p);
+  return MG_OK;
+}
+
+// systems/packed_coordinate.hpp:74-143: offsets by Manhattan distance, dr ascending, -dc before +dc
+static std::vector<uint8_t> make_pattern(int oh, int ow) {
+  std::vector<uint8_t> out;
+  const int hr = oh / 2, wr = ow / 2;
+  for (int d = 0; d <= hr + wr; d++)
+    for (int dr = -d; dr <= d; dr++) {
+      const int adc = d - (dr < 0 ? -dr : dr);
+      for (int s = 0; s < (adc == 0 ? 1 : 2); s++) {
+        const int dc = s == 0 ? -adc : adc;
+        if (dr < -hr || dr > hr || dc < -wr || dc > wr) continue;
+        out.push_back((uint8_t)(((dr + hr) << 4) | ((dc + wr) & 0xF)));
+      }
+    }
+  return out;
+}
+
+extern "C" {
+
+const char* mg_last_error(void) { return g_err.c_str(); }
+int mg_abi_version(void) { return MG_CONFIG_VERSION; }
+
+int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t device, void** out) {
+  if (!cfg || !out || n_words < MGC_HEADER_WORDS) return fail(MG_ERR_ARG, "mg_create: null or short config");
+  if (cfg[MGC_MAGIC] != MG_CONFIG_MAGIC || cfg[MGC_VERSION] != MG_CONFIG_VERSION)
+    return fail(MG_ERR_ARG, "mg_create: config blob has the wrong magic/version");
+  if (cfg[MGC_TOTAL_WORDS] != n_words) return fail(MG_ERR_ARG, "mg_create: config length mismatch");
+  if (num_envs <= 0) return fail(MG_ERR_ARG, "mg_create: num_envs must be positive");
+  if (cfg[MGC_NUM_AGENTS] > MG_MAX_AGENTS)
+    return fail(MG_ERR_ARG, "mg_create: more than " + std::to_string(MG_MAX_AGENTS) + " agents per env");
+  if (cfg[MGC_OBS_H] * cfg[MGC_OBS_W] > 256) return fail(MG_ERR_ARG, "mg_create: observation window too large");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(MG_ERR_CUDA, "mg_create: no CUDA device (this library has no CPU path)");
+  if (device < 0 || device >= ndev) return fail(MG_ERR_ARG, "mg_create: bad device ordinal");
+  CUDA_TRY(cudaSetDevice(device));
+  // inv_update <-> inv_enforce_all_limits recurse (bounded depth 8); give device threads room for it
+  CUDA_TRY(cudaDeviceSetLimit(cudaLimitStackSize, 8192));
+  MgEnvs* e = new MgEnvs();
+  memset(&e->b, 0, sizeof(MgBatch));
+  e->device = device;
+  e->launches = 0;
+  e->maps_loaded = e->buffers_bound = e->owns_buffers = false;
+  e->h_pinned = nullptr;
+  e->h_pinned_bytes = 0;
+  e->stream = nullptr;
+  e->cfg_host.assign(cfg, cfg + n_words);
+  MgBatch& b = e->b;
+  b.num_envs = num_envs;
+  b.A = cfg[MGC_NUM_AGENTS];
+  b.H = cfg[MGC_MAP_H];
+  b.W = cfg[MGC_MAP_W];
+  b.T = cfg[MGC_NUM_TOKENS];
+  b.R = cfg[MGC_NUM_RESOURCES];
+  b.S = cfg[MGC_NUM_AGENT_STATS];
+  b.GS = cfg[MGC_NUM_GAME_STATS];
+  b.max_asm = cfg[MGC_MAX_ASSEMBLERS] > 0 ? cfg[MGC_MAX_ASSEMBLERS] : 1;
+  b.max_chest = cfg[MGC_MAX_CHESTS] > 0 ? cfg[MGC_MAX_CHESTS] : 1;
+  b.has_clipper = (cfg + cfg[MGC_OFF_CLIPPER])[MG_CLIP_ENABLED];
+  b.obs_cells = cfg[MGC_OBS_H] * cfg[MGC_OBS_W];
+  b.grid_stride = ((b.H * b.W + 7) / 8) * 8;
+  b.auto_reset = 1;
+  b.map_stride = 0;
+  const size_t N = (size_t)num_envs, A = (size_t)b.A;
+  int32_t* d_cfg = nullptr;
+  uint8_t* d_pat = nullptr;
+  int rc;
+#define TRY(x) if ((rc = (x)) != MG_OK) { return rc; }
+  TRY(dev_alloc(e, &d_cfg, (size_t)n_words));
+  CUDA_TRY(cudaMemcpy(d_cfg, cfg, sizeof(int32_t) * (size_t)n_words, cudaMemcpyHostToDevice));
+  b.cfg = d_cfg;
+  std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
+  TRY(dev_alloc(e, &d_pat, pat.size() + 64));
+  CUDA_TRY(cudaMemcpy(d_pat, pat.data(), pat.size(), cudaMemcpyHostToDevice));
+  b.pattern = d_pat;
+  TRY(dev_alloc(e, &b.env, N));
+  TRY(dev_alloc(e, &b.grid, N * (size_t)b.grid_stride));
+  TRY(dev_alloc(e, &b.agents, N * A));
+  TRY(dev_alloc(e, &b.asms, N * (size_t)b.max_asm));
+  TRY(dev_alloc(e, &b.chests, N * (size_t)b.max_chest));
+  TRY(dev_alloc(e, &b.agent_stats, N * A * (size_t)b.S));
+  TRY(dev_alloc(e, &b.game_stats, N * (size_t)b.GS));
+  TRY(dev_alloc(e, &b.rng, N * MT_N));
+  if (b.has_clipper) TRY(dev_alloc(e, &b.clip_rng, N * MT_N));
+  TRY(dev_alloc(e, &b.tok_counts, N * A * 2));
+  TRY(dev_alloc(e, &b.last_action, N * A));
+  TRY(dev_alloc(e, &b.action_success, N * A));
+  TRY(dev_alloc(e, &b.episode_accum, (size_t)(2 + b.S + b.GS)));
+  TRY(dev_alloc(e, &e->d_mask, N));
+  TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
+  CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  *out = e;
+  return MG_OK;
+}
+
+void mg_destroy(void* h) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return;
+  cudaSetDevice(e->device);
+  cudaDeviceSynchronize();
+  for (void* p : e->allocs) cudaFree(p);
+  if (e->h_pinned) cudaFreeHost(e->h_pinned);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+// Map pool, already split per kind by metta_b200/maps.py (host pointers):
+// grids u16 [M][H*W], agents i32 [M][A][3], n_asm i32 [M], asms i32 [M][max_asm][3], n_chest, chests.
+int mg_load_maps(void* h, int32_t num_maps, const uint16_t* grids, const int32_t* agents, const int32_t* n_asm,
+                 const int32_t* asms, const int32_t* n_chest, const int32_t* chests) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || num_maps <= 0 || !grids || !agents || !n_asm || !asms || !n_chest || !chests)
+    return fail(MG_ERR_ARG, "mg_load_maps: bad arguments");
+  CUDA_TRY(cudaSetDevice(e->device));
+  MgBatch& b = e->b;
+  for (int m = 0; m < num_maps; m++)
+    if (n_asm[m] > b.max_asm || n_chest[m] > b.max_chest || n_asm[m] < 0 || n_chest[m] < 0)
+      return fail(MG_ERR_ARG, "mg_load_maps: a map has more assemblers/chests than the config's capacity");
+  const size_t cells = (size_t)b.H * b.W, M = (size_t)num_maps;
+  std::vector<uint16_t> padded(M * (size_t)b.grid_stride, 0);
+  for (size_t m = 0; m < M; m++) memcpy(&padded[m * b.grid_stride], grids + m * cells, cells * sizeof(uint16_t));
+  uint16_t* d_grid; int32_t *d_ag, *d_na, *d_as, *d_nc, *d_ch;
+  int rc;
+  TRY(dev_alloc(e, &d_grid, padded.size(), false));
+  TRY(dev_alloc(e, &d_ag, M * b.A * 3, false));
+  TRY(dev_alloc(e, &d_na, M, false));
+  TRY(dev_alloc(e, &d_as, M * b.max_asm * 3, false));
+  TRY(dev_alloc(e, &d_nc, M, false));
+  TRY(dev_alloc(e, &d_ch, M * b.max_chest * 3, false));
+  CUDA_TRY(cudaMemcpy(d_grid, padded.data(), padded.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(d_ag, agents, M * b.A * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(d_na, n_asm, M * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(d_as, asms, M * b.max_asm * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(d_nc, n_chest, M * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(d_ch, chests, M * b.max_chest * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  b.pool_grid = d_grid; b.pool_agents = d_ag; b.pool_n_asm = d_na; b.pool_asm = d_as; b.pool_n_chest = d_nc; b.pool_chest = d_ch;
+  b.num_maps = num_maps;
+  e->maps_loaded = true;
+  return MG_OK;
+}
+
+// Bind caller-owned DEVICE buffers: obs u8 [N*A][T][3], terminals u8/bool [N*A], truncations, rewards f32, actions i32.
+// Passing all nulls makes the library allocate them (used by the host-buffer path).
+int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void* rewards, void* actions) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_set_buffers: null handle");
+  CUDA_TRY(cudaSetDevice(e->device));
+  MgBatch& b = e->b;
+  const size_t NA = (size_t)b.num_envs * b.A;
+  if (!obs && !terminals && !truncations && !rewards && !actions) {
+    if (!e->owns_buffers) {
+      int rc;
+      int32_t* act;
+      TRY(dev_alloc(e, &b.obs, NA * b.T * 3 + 16));
+      TRY(dev_alloc(e, &b.terminals, NA));
+      TRY(dev_alloc(e, &b.truncations, NA));
+      TRY(dev_alloc(e, &b.rewards, NA));
+      TRY(dev_alloc(e, &act, NA));
+      b.actions = act;
+      e->owns_buffers = true;
+    }
+  } else {
+    if (!obs || !terminals || !truncations || !rewards || !actions)
+      return fail(MG_ERR_ARG, "mg_set_buffers: all five buffers are required");
+    b.obs = (uint8_t*)obs; b.terminals = (uint8_t*)terminals; b.truncations = (uint8_t*)truncations;
+    b.rewards = (float*)rewards; b.actions = (const int32_t*)actions;
+  }
+  e->buffers_bound = true;
+  return MG_OK;
+}
+
+static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
+  MgBatch& b = e->b;
+  const long long agents = (long long)b.num_envs * b.A;
+  const int grid = (int)((agents + MG_OBS_WARPS - 1) / MG_OBS_WARPS);
+  const int slot = (b.T * 3 + 16 + 15) & ~15;
+  MG_LAUNCH(mg_obs_kernel, grid, MG_OBS_WARPS * 32, (size_t)slot * MG_OBS_WARPS, s, b, mask);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+// Start episodes: seeds u32 [N], map index i32 [N], optional mask u8 [N] (host pointers; null mask = all).
+// Writes the initial observation and clears rewards/terminals/truncations of the reset envs
+// (MettaGrid ctor + set_buffers/_init_buffers, mettagrid_c.cpp:46-155,264-289).
+int mg_reset(void* h, const uint32_t* seeds, const int32_t* map_idx, const uint8_t* mask) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !seeds || !map_idx) return fail(MG_ERR_ARG, "mg_reset: bad arguments");
+  if (!e->maps_loaded) return fail(MG_ERR_STATE, "mg_reset: no maps loaded");
+  if (!e->buffers_bound) return fail(MG_ERR_STATE, "mg_reset: buffers not bound (mg_set_buffers)");
+  CUDA_TRY(cudaSetDevice(e->device));
+  MgBatch& b = e->b;
+  const size_t N = (size_t)b.num_envs;
+  std::vector<EnvRec> recs(N);
+  CUDA_TRY(cudaMemcpy(recs.data(), b.env, N * sizeof(EnvRec), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++) {
+    if (mask && !mask[i]) continue;
+    if (map_idx[i] < 0 || map_idx[i] >= b.num_maps) return fail(MG_ERR_ARG, "mg_reset: map index out of range");
+    recs[i].seed = seeds[i];
+    recs[i].map_idx = map_idx[i];
+    recs[i].early_reset_step = 0;
+  }
+  CUDA_TRY(cudaMemcpy(b.env, recs.data(), N * sizeof(EnvRec), cudaMemcpyHostToDevice));
+  const uint8_t* d_mask = nullptr;
+  if (mask) {
+    CUDA_TRY(cudaMemcpy(e->d_mask, mask, N, cudaMemcpyHostToDevice));
+    d_mask = e->d_mask;
+  }
+  const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
+  MG_LAUNCH(mg_reset_kernel, grid, MG_STEP_WARPS * 32, 0, (cudaStream_t)0, b, d_mask);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  int rc;
+  TRY(launch_obs(e, (cudaStream_t)0, d_mask));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return MG_OK;
+}
+
+// One step of every env on `stream` (a cudaStream_t, may be null): reads the bound actions,
+// overwrites observations/rewards/terminals/truncations. Asynchronous.
+int mg_step(void* h, void* stream) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_step: null handle");
+  if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_step: maps or buffers missing");
+  MgBatch& b = e->b;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
+  MG_LAUNCH(mg_step_kernel, grid, MG_STEP_WARPS * 32, 0, s, b);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return launch_obs(e, s, nullptr);
+}
+
+// Recompute observations only (debugging / after mg_write).
+int mg_compute_observations(void* h, void* stream) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_compute_observations: buffers missing");
+  return launch_obs(e, (cudaStream_t)stream, nullptr);
+}
+
+// Host-buffer step: the call a numpy caller makes. actions i32 [N*A] in; obs, rewards, terminals,
+// truncations out. Copies go through pinned staging on the library's stream; returns when done.
+int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, uint8_t* terminals, uint8_t* truncations) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !actions || !obs || !rewards || !terminals || !truncations) return fail(MG_ERR_ARG, "mg_step_host: null pointer");
+  if (!e->buffers_bound) return fail(MG_ERR_STATE, "mg_step_host: call mg_set_buffers first (all nulls = library-owned)");
+  CUDA_TRY(cudaSetDevice(e->device));
+  MgBatch& b = e->b;
+  const size_t NA = (size_t)b.num_envs * b.A;
+  const size_t obs_bytes = NA * b.T * 3;
+  const size_t off_act = 0, off_rew = off_act + NA * 4, off_term = off_rew + NA * 4, off_trunc = off_term + NA;
+  const size_t off_obs = (off_trunc + NA + 255) & ~(size_t)255, total = off_obs + obs_bytes;
+  if (e->h_pinned_bytes < total) {
+    if (e->h_pinned) cudaFreeHost(e->h_pinned);
+    CUDA_TRY(cudaMallocHost((void**)&e->h_pinned, total));
+    e->h_pinned_bytes = total;
+  }
+  cudaStream_t s = e->stream;
+  memcpy(e->h_pinned + off_act, actions, NA * 4);
+  CUDA_TRY(cudaMemcpyAsync((void*)b.actions, e->h_pinned + off_act, NA * 4, cudaMemcpyHostToDevice, s));
+  int rc;
+  TRY(mg_step(h, (void*)s));
+  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_obs, b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_rew, b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_term, b.terminals, NA, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_trunc, b.truncations, NA, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  memcpy(obs, e->h_pinned + off_obs, obs_bytes);
+  memcpy(rewards, e->h_pinned + off_rew, NA * 4);
+  memcpy(terminals, e->h_pinned + off_term, NA);
+  memcpy(truncations, e->h_pinned + off_trunc, NA);
+  return MG_OK;
+}
+
+// auto_reset: 1 = MettaGridPufferEnv semantics (default), 0 = bare MettaGrid (keeps stepping past the end).
+// map_stride: on auto-reset the env moves to map (index + stride) mod pool size.
+int mg_set_options(void* h, int32_t auto_reset, int32_t map_stride) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_set_options: null handle");
+  e->b.auto_reset = auto_reset ? 1 : 0;
+  e->b.map_stride = map_stride < 0 ? 0 : map_stride;
+  return MG_OK;
+}
+
+// EarlyResetHandler: truncate the running episode of env i when current_step >= steps[i] (0 = never).
+int mg_set_early_reset(void* h, const uint32_t* steps) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !steps) return fail(MG_ERR_ARG, "mg_set_early_reset: bad arguments");
+  CUDA_TRY(cudaSetDevice(e->device));
+  const size_t N = (size_t)e->b.num_envs;
+  std::vector<EnvRec> recs(N);
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaMemcpy(recs.data(), e->b.env, N * sizeof(EnvRec), cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; i++) recs[i].early_reset_step = steps[i];
+  CUDA_TRY(cudaMemcpy(e->b.env, recs.data(), N * sizeof(EnvRec), cudaMemcpyHostToDevice));
+  return MG_OK;
+}
+
+// Raw state access for the conformance harness and infos. `what`:
+enum { MG_ST_ENV = 0, MG_ST_GRID = 1, MG_ST_AGENTS = 2, MG_ST_ASMS = 3, MG_ST_CHESTS = 4, MG_ST_AGENT_STATS = 5,
+       MG_ST_GAME_STATS = 6, MG_ST_LAST_ACTION = 7, MG_ST_ACTION_SUCCESS = 8, MG_ST_EPISODE_ACCUM = 9, MG_ST_RNG = 10,
+       MG_ST_OBS = 11, MG_ST_REWARDS = 12, MG_ST_TERMINALS = 13, MG_ST_TRUNCATIONS = 14, MG_ST_ACTIONS = 15,
+       MG_ST_COUNT = 16 };
+
+static void* state_ptr(MgEnvs* e, int what, size_t* bytes) {
+  MgBatch& b = e->b;
+  const size_t N = (size_t)b.num_envs, A = (size_t)b.A;
+  switch (what) {
+    case MG_ST_ENV: *bytes = N * sizeof(EnvRec); return b.env;
+    case MG_ST_GRID: *bytes = N * b.grid_stride * sizeof(uint16_t); return b.grid;
+    case MG_ST_AGENTS: *bytes = N * A * sizeof(AgentRec); return b.agents;
+    case MG_ST_ASMS: *bytes = N * b.max_asm * sizeof(AsmRec); return b.asms;
+    case MG_ST_CHESTS: *bytes = N * b.max_chest * sizeof(ChestRec); return b.chests;
+    case MG_ST_AGENT_STATS: *bytes = N * A * b.S * sizeof(float); return b.agent_stats;
+    case MG_ST_GAME_STATS: *bytes = N * b.GS * sizeof(float); return b.game_stats;
+    case MG_ST_LAST_ACTION: *bytes = N * A * sizeof(int32_t); return b.last_action;
+    case MG_ST_ACTION_SUCCESS: *bytes = N * A; return b.action_success;
+    case MG_ST_EPISODE_ACCUM: *bytes = (size_t)(2 + b.S + b.GS) * sizeof(double); return b.episode_accum;
+    case MG_ST_RNG: *bytes = N * MT_N * sizeof(uint32_t); return b.rng;
+    case MG_ST_OBS: *bytes = N * A * b.T * 3; return b.obs;
+    case MG_ST_REWARDS: *bytes = N * A * sizeof(float); return b.rewards;
+    case MG_ST_TERMINALS: *bytes = N * A; return b.terminals;
+    case MG_ST_TRUNCATIONS: *bytes = N * A; return b.truncations;
+    case MG_ST_ACTIONS: *bytes = N * A * sizeof(int32_t); return (void*)b.actions;
+    default: *bytes = 0; return nullptr;
+  }
+}
+
+int64_t mg_sizeof(void* h, int32_t what) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  size_t bytes = 0;
+  if (!e || !state_ptr(e, what, &bytes)) return -1;
+  return (int64_t)bytes;
+}
+
+int mg_read(void* h, int32_t what, void* host_out, int64_t nbytes) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !host_out) return fail(MG_ERR_ARG, "mg_read: bad arguments");
+  CUDA_TRY(cudaSetDevice(e->device));
+  size_t bytes = 0;
+  void* p = state_ptr(e, what, &bytes);
+  if (!p) return fail(MG_ERR_ARG, "mg_read: unknown or unbound state array");
+  if ((size_t)nbytes != bytes) return fail(MG_ERR_ARG, "mg_read: size mismatch, expected " + std::to_string(bytes));
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (what == MG_ST_GAME_STATS) {  // pending token counts of the last observation pass
+    const int grid = (e->b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
+    MG_LAUNCH(mg_fold_kernel, grid, MG_STEP_WARPS * 32, 0, (cudaStream_t)0, e->b);
+    e->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaDeviceSynchronize());
+  }
+  CUDA_TRY(cudaMemcpy(host_out, p, bytes, cudaMemcpyDeviceToHost));
+  return MG_OK;
+}
+
+int mg_write(void* h, int32_t what, const void* host_in, int64_t nbytes) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !host_in) return fail(MG_ERR_ARG, "mg_write: bad arguments");
+  CUDA_TRY(cudaSetDevice(e->device));
+  size_t bytes = 0;
+  void* p = state_ptr(e, what, &bytes);
+  if (!p) return fail(MG_ERR_ARG, "mg_write: unknown or unbound state array");
+  if ((size_t)nbytes != bytes) return fail(MG_ERR_ARG, "mg_write: size mismatch, expected " + std::to_string(bytes));
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaMemcpy(p, host_in, bytes, cudaMemcpyHostToDevice));
+  return MG_OK;
+}
+
+// MettaGrid::set_inventory (mettagrid_c.cpp:959-965): items/amounts i32[n] in the caller's dict order.
+int mg_set_inventory(void* h, int32_t env, int32_t agent, const int32_t* items_amounts /* [2][n] */, int32_t n) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || n < 0 || n > MG_RES_STRIDE || (n > 0 && !items_amounts)) return fail(MG_ERR_ARG, "mg_set_inventory: bad arguments");
+  if (env < 0 || env >= e->b.num_envs) return fail(MG_ERR_ARG, "mg_set_inventory: env out of range");
+  if (agent < 0 || agent >= e->b.A) return MG_OK;  // the reference ignores unknown agent ids
+  for (int i = 0; i < n; i++)
+    if (items_amounts[i] < 0 || items_amounts[i] >= e->b.R) return fail(MG_ERR_ARG, "mg_set_inventory: unknown resource id");
+  CUDA_TRY(cudaSetDevice(e->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (n > 0) CUDA_TRY(cudaMemcpy(e->d_tmp, items_amounts, sizeof(int32_t) * 2 * (size_t)n, cudaMemcpyHostToDevice));
+  MG_LAUNCH(mg_set_inventory_kernel, 1, 32, 0, (cudaStream_t)0, e->b, env, agent, e->d_tmp, e->d_tmp + n, n);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaDeviceSynchronize());
+  return MG_OK;
+}
+
+int64_t mg_kernel_launches(void* h) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  return e ? e->launches : -1;
+}
+
+int mg_sync(void* h) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_sync: null handle");
+  CUDA_TRY(cudaSetDevice(e->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return MG_OK;
+}
+
+}  // extern "C"

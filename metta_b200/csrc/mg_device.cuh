@@ -1,0 +1,737 @@
+// mg_device.cuh -- per-environment game rules as device functions.
+//
+// These run inside mg_step_actions_kernel (one warp per environment). The ordered action pass
+// is executed by one lane on agent records staged in shared memory; everything that touches a
+// single agent (regen, rewards) is done one agent per lane. Each function names the reference
+// code whose behaviour it reproduces.
+#ifndef MG_DEVICE_CUH_
+#define MG_DEVICE_CUH_
+
+#include "mg_platform.h"
+#include "mg_state.h"
+
+#define RS MG_RES_STRIDE
+
+struct EnvCtx {
+  const int32_t* cfg;
+  int env, H, W, A, R, S;
+  uint32_t current_step;
+  uint16_t* grid;     // global, this env
+  AgentRec* ag;       // shared memory copy of this env's agents
+  AsmRec* asms;       // global
+  ChestRec* chests;   // global
+  float* astats;      // global [A][S]
+  float* gstats;      // global [GS]
+  int n_asm;
+  int clip_enabled, clip_length_scale;
+};
+
+// ---------------------------------------------------------------- inventory
+// The reference keeps each inventory as unordered_map<item, amount> plus shared limit records
+// (objects/inventory.hpp:13-43). Here: amounts in a dense u16 array, the map's iteration order as
+// a list of 4-bit item ids in one u64, and limit totals recomputed from the amounts.
+struct InvView {
+  uint16_t* amt;
+  uint64_t* order;
+  const int32_t* invcfg;  // INVCFG record
+  int owner_kind;         // 0 agent, 1 chest
+  int owner_idx;
+};
+
+MG_DEVICE inline InvView agent_inv(const EnvCtx& e, int ai) {
+  InvView v;
+  AgentRec* a = &e.ag[ai];
+  v.amt = a->amt;
+  v.order = &a->order;
+  const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
+  v.invcfg = e.cfg + e.cfg[MGC_OFF_INVCFG] + grp[MG_GRP_INVCFG] * MG_INVCFG_WORDS;
+  v.owner_kind = 0;
+  v.owner_idx = ai;
+  return v;
+}
+
+MG_DEVICE inline InvView chest_inv(const EnvCtx& e, int ci) {
+  InvView v;
+  ChestRec* c = &e.chests[ci];
+  v.amt = c->amt;
+  v.order = &c->order;
+  const int32_t* cell = e.cfg + e.cfg[MGC_OFF_CELLTYPES] + c->cell * MG_CELL_WORDS;
+  const int32_t* ct = e.cfg + e.cfg[MGC_OFF_CHEST_TYPES] + cell[MG_CELL_PARAM] * MG_CHEST_WORDS;
+  v.invcfg = e.cfg + e.cfg[MGC_OFF_INVCFG] + ct[MG_CHEST_INVCFG] * MG_INVCFG_WORDS;
+  v.owner_kind = 1;
+  v.owner_idx = ci;
+  return v;
+}
+
+// SharedInventoryLimit::amount: kept by the reference as a running u16 sum (inventory.cpp:66-69).
+MG_DEVICE inline uint32_t inv_limit_amount(const InvView& v, int limit) {
+  uint32_t sum = 0;
+  for (int i = 0; i < MG_MAX_RESOURCES; i++)
+    if (v.invcfg[MG_INVCFG_ITEM_LIMIT + i] == limit) sum += v.amt[i];
+  return sum & 0xFFFFu;
+}
+
+// SharedInventoryLimit::effective_limit, objects/inventory.hpp:21-34
+MG_DEVICE inline int inv_effective_limit(const InvView& v, int limit) {
+  int effective = v.invcfg[MG_INVCFG_LIMIT_BASE + limit];
+  const int32_t* mod = v.invcfg + MG_INVCFG_LIMIT_MOD + limit * RS;
+  for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+    int bonus = mod[i];
+    if (bonus != 0) effective += (int)v.amt[i] * bonus;
+  }
+  effective = effective < 0 ? 0 : effective;
+  return effective > 65535 ? 65535 : effective;
+}
+
+// Inventory::free_space, inventory.cpp:95-109
+MG_DEVICE inline int inv_free_space(const InvView& v, int item) {
+  int limit = v.invcfg[MG_INVCFG_ITEM_LIMIT + item];
+  if (limit < 0) return 65535 - (int)v.amt[item];
+  int used = (int)inv_limit_amount(v, limit);
+  int effective = inv_effective_limit(v, limit);
+  return effective > used ? effective - used : 0;
+}
+
+MG_DEVICE inline void order_push_front(uint64_t* order, int item) { *order = (*order << 4) | (uint64_t)item; }
+
+MG_DEVICE inline void order_erase(uint64_t* order, int item) {
+  uint64_t o = *order;
+  for (int k = 0; k < 16; k++) {
+    if (((o >> (4 * k)) & 0xF) == (uint64_t)item) {
+      uint64_t low = k == 0 ? 0ull : (o & ((1ull << (4 * k)) - 1ull));
+      uint64_t high = (o >> (4 * (k + 1))) << (4 * k);
+      if (k == 15) high = 0;
+      *order = low | high | (0xFull << 60);
+      return;
+    }
+  }
+}
+
+MG_DEVICE int inv_update(EnvCtx& e, InvView& v, int item, int attempted_delta, bool ignore_limits, int depth);
+
+// Agent::on_inventory_change (agent.cpp:74-101), Chest::on_inventory_change (chest.hpp:54-63)
+MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item, int delta) {
+  if (v.owner_kind == 0) {
+    float* st = e.astats + (size_t)v.owner_idx * e.S;
+    AgentRec* a = &e.ag[v.owner_idx];
+    int amount = a->amt[item];
+    if (delta > 0) st[MG_AS_GAINED + item] += (float)delta;
+    else st[MG_AS_LOST + item] += (float)(-delta);
+    st[MG_AS_AMOUNT + item] = (float)amount;
+    const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
+    if (grp[MG_GRP_DIVERSITY + item]) {
+      // presence flips exactly when the amount crosses zero
+      bool has = amount > 0, had = (amount - delta) > 0;
+      if (had != has) {
+        int n = 0;
+        for (int i = 0; i < MG_MAX_RESOURCES; i++) n += (grp[MG_GRP_DIVERSITY + i] && a->amt[i] > 0) ? 1 : 0;
+        st[MG_AS_DIVERSITY] = (float)n;
+      }
+    }
+  } else {
+    if (delta > 0) e.gstats[MG_GS_CHEST_DEPOSITED + item] += (float)delta;
+    else e.gstats[MG_GS_CHEST_WITHDRAWN + item] += (float)(-delta);
+    e.gstats[MG_GS_CHEST_AMOUNT + item] = (float)v.amt[item];
+  }
+}
+
+// Inventory::enforce_all_limits, inventory.cpp:128-158 (limit_defs order; the reference's
+// pointer-ordered std::set is not reproducible)
+MG_DEVICE MG_NOINLINE void inv_enforce_all_limits(EnvCtx& e, InvView& v, int depth) {
+  int nlim = v.invcfg[MG_INVCFG_NUM_LIMITS];
+  int norder = v.invcfg[MG_INVCFG_NUM_ORDER];
+  for (int limit = 0; limit < nlim; limit++) {
+    bool reachable = false;
+    for (int k = 0; k < norder; k++)
+      if (v.invcfg[MG_INVCFG_ITEM_LIMIT + v.invcfg[MG_INVCFG_ORDER + k]] == limit) reachable = true;
+    if (!reachable) continue;
+    int excess = (int)inv_limit_amount(v, limit) - inv_effective_limit(v, limit);
+    if (excess <= 0) continue;
+    for (int k = 0; k < norder; k++) {
+      int item = v.invcfg[MG_INVCFG_ORDER + k];
+      if (v.invcfg[MG_INVCFG_ITEM_LIMIT + item] != limit) continue;
+      int current = v.amt[item];
+      int to_drop = current < excess ? current : excess;
+      if (to_drop > 0) {
+        inv_update(e, v, item, -to_drop, false, depth + 1);
+        excess = (int)inv_limit_amount(v, limit) - inv_effective_limit(v, limit);
+      }
+      if (excess <= 0) break;
+    }
+  }
+}
+
+// Inventory::update, inventory.cpp:37-85
+MG_DEVICE MG_NOINLINE int inv_update(EnvCtx& e, InvView& v, int item, int attempted_delta, bool ignore_limits, int depth) {
+  int initial = v.amt[item];
+  int new_amount = initial + attempted_delta;
+  int max = 65535;
+  int limit = v.invcfg[MG_INVCFG_ITEM_LIMIT + item];
+  if (!ignore_limits && limit >= 0) {
+    int effective = inv_effective_limit(v, limit);
+    int used_by_others = (int)inv_limit_amount(v, limit) - initial;
+    if (used_by_others < 0) used_by_others = 0;
+    int max_int = effective - used_by_others;
+    max = max_int < 0 ? 0 : max_int;
+  }
+  int clamped = new_amount < 0 ? 0 : (new_amount > max ? max : new_amount);
+  if (clamped == 0) {
+    if (initial > 0) order_erase(v.order, item);
+  } else if (initial == 0) {
+    order_push_front(v.order, item);  // new hash node: head of the list (ids < 13 never share a bucket)
+  }
+  v.amt[item] = (uint16_t)clamped;
+  int clamped_delta = clamped - initial;
+  if (clamped_delta != 0) on_inventory_change(e, v, item, clamped_delta);
+  if (clamped_delta < 0 && v.invcfg[MG_INVCFG_IS_MODIFIER + item] && depth < 8) inv_enforce_all_limits(e, v, depth);
+  return clamped_delta;
+}
+
+// HasInventory::shared_update, has_inventory.cpp:7-74
+#define MG_MAX_SHARED 40
+MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, InvView* invs, int n, int item, int delta) {
+  if (n == 0) return 0;
+  int delta_remaining = delta;
+  uint64_t active = n >= 64 ? ~0ull : ((1ull << n) - 1ull);  // inventories still to consider, in order
+  int num_remaining = n;
+  int per = delta_remaining / num_remaining;
+  for (;;) {
+    uint64_t next = 0;
+    int ncur = 0, nnext = 0;
+    for (int i = 0; i < n; i++) {
+      if (!((active >> i) & 1ull)) continue;
+      ncur++;
+      bool now;
+      if (delta_remaining > 0) now = inv_free_space(invs[i], item) <= per;
+      else now = (int)invs[i].amt[item] <= -per;
+      if (now) {
+        delta_remaining -= inv_update(e, invs[i], item, per, false, 0);
+        num_remaining--;
+        if (num_remaining > 0) per = delta_remaining / num_remaining;
+      } else {
+        next |= 1ull << i;
+        nnext++;
+      }
+    }
+    active = next;
+    if (ncur == nnext) break;
+  }
+  if (num_remaining == 0) return delta - delta_remaining;
+  int cnt = 0;
+  for (int i = 0; i < n; i++) cnt += (int)((active >> i) & 1ull);
+  for (int i = n - 1; i >= 0; i--) {  // reverse order: earlier inventories get the remainder
+    if (!((active >> i) & 1ull)) continue;
+    int d = delta_remaining / cnt;
+    delta_remaining -= inv_update(e, invs[i], item, d, false, 0);
+    cnt--;
+  }
+  return delta - delta_remaining;
+}
+
+// HasInventory::transfer_resources, has_inventory.cpp:77-108
+MG_DEVICE inline int transfer_resources(EnvCtx& e, InvView& src, InvView& dst, int item, int delta, bool destroy) {
+  if (delta <= 0) return 0;
+  int avail = src.amt[item];
+  int can_give = avail < delta ? avail : delta;
+  int can_recv = inv_free_space(dst, item);
+  int amount = can_give < can_recv ? can_give : can_recv;
+  int loss = destroy ? can_give : amount;
+  inv_update(e, src, item, -loss, false, 0);
+  inv_update(e, dst, item, amount, false, 0);
+  return amount;
+}
+
+// ---------------------------------------------------------------- grid helpers
+MG_DEVICE inline uint16_t grid_at(const EnvCtx& e, int r, int c) { return e.grid[r * e.W + c]; }
+MG_DEVICE inline const int32_t* proto_cfg(const int32_t* cfg, int p) { return cfg + cfg[MGC_OFF_PROTOCOLS] + p * MG_PROTO_WORDS; }
+MG_DEVICE inline const int32_t* cell_cfg(const int32_t* cfg, int cell) { return cfg + cfg[MGC_OFF_CELLTYPES] + cell * MG_CELL_WORDS; }
+MG_DEVICE inline const int32_t* asm_type_cfg(const int32_t* cfg, int cell) {
+  return cfg + cfg[MGC_OFF_ASM_TYPES] + cell_cfg(cfg, cell)[MG_CELL_PARAM] * MG_ASM_WORDS;
+}
+
+// Assembler::get_local_vibe + surrounding agent count (assembler.hpp:30-45,353-375)
+MG_DEVICE inline uint64_t asm_local_vibe(const EnvCtx& e, int r, int c, int* num_agents) {
+  uint32_t vibes[8];
+  int nv = 0, na = 0;
+  for (int i = -1; i <= 1; i++)
+    for (int j = -1; j <= 1; j++) {
+      if (i == 0 && j == 0) continue;
+      int rr = r + i, cc = c + j;
+      if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+      uint16_t g = grid_at(e, rr, cc);
+      if (MG_GRID_KIND(g) == MG_GK_AGENT) {
+        na++;
+        uint32_t vb = e.ag[MG_GRID_INDEX(g)].vibe;
+        if (vb != 0) vibes[nv++] = vb;
+      }
+    }
+  for (int i = 1; i < nv; i++) {
+    uint32_t x = vibes[i];
+    int j = i - 1;
+    while (j >= 0 && vibes[j] > x) { vibes[j + 1] = vibes[j]; j--; }
+    vibes[j + 1] = x;
+  }
+  uint64_t key = 0;
+  for (int i = 0; i < nv; i++) key = (key << 8) | vibes[i];
+  *num_agents = na;
+  return key;
+}
+
+MG_DEVICE inline int find_protocol(const int32_t* cfg, int first, int n, uint64_t key, int num_agents) {
+  for (int i = first; i < first + n; i++) {
+    const int32_t* p = proto_cfg(cfg, i);
+    uint64_t k = ((uint64_t)(uint32_t)p[MG_PROTO_KEY_HI] << 32) | (uint32_t)p[MG_PROTO_KEY_LO];
+    if (k == key && p[MG_PROTO_MIN_AGENTS] <= num_agents) return i;
+  }
+  return -1;
+}
+
+// Assembler::get_current_protocol, assembler.hpp:378-408
+MG_DEVICE inline int asm_current_protocol(const EnvCtx& e, const AsmRec* a) {
+  int num_agents;
+  uint64_t key = asm_local_vibe(e, a->r, a->c, &num_agents);
+  int first, n;
+  if (a->flags & MG_ASMF_CLIPPED) {
+    if (a->unclip_protocol < 0) return -1;
+    first = a->unclip_protocol;
+    n = 1;
+  } else {
+    const int32_t* t = asm_type_cfg(e.cfg, a->cell);
+    first = t[MG_ASM_FIRST_PROTOCOL];
+    n = t[MG_ASM_NUM_PROTOCOLS];
+  }
+  int p = find_protocol(e.cfg, first, n, key, num_agents);
+  if (p < 0 && key != 0) p = find_protocol(e.cfg, first, n, 0, num_agents);
+  return p;
+}
+
+// ---------------------------------------------------------------- clipper bookkeeping (systems/clipper.hpp)
+MG_DEVICE inline int asm_cheb(const AsmRec* a, const AsmRec* b) {
+  int dr = (int)a->r - (int)b->r, dc = (int)a->c - (int)b->c;
+  dr = dr < 0 ? -dr : dr;
+  dc = dc < 0 ? -dc : dc;
+  return dr > dc ? dr : dc;
+}
+MG_DEVICE inline uint32_t clip_infection_weight(const EnvCtx& e, const AsmRec* from, const AsmRec* to) {  // :93-97
+  const int32_t* cc = e.cfg + e.cfg[MGC_OFF_CLIPPER];
+  uint32_t cutoff = (uint32_t)cc[MG_CLIP_CUTOFF];
+  uint32_t scaled = (uint32_t)asm_cheb(from, to) / (uint32_t)e.clip_length_scale;
+  return scaled > cutoff ? 0u : (1u << (cutoff - scaled));
+}
+MG_DEVICE inline bool clip_adjacent(const EnvCtx& e, const AsmRec* a, const AsmRec* b) {  // compute_adjacencies :106-138
+  const int32_t* cc = e.cfg + e.cfg[MGC_OFF_CLIPPER];
+  if ((uint32_t)cc[MG_CLIP_PERIOD] == 0u) return false;
+  uint32_t lim = (uint32_t)cc[MG_CLIP_CUTOFF] * (uint32_t)e.clip_length_scale;
+  return a != b && (a->flags & MG_ASMF_TRACKED) && (b->flags & MG_ASMF_TRACKED) && (uint32_t)asm_cheb(a, b) <= lim;
+}
+// Clipper::clip_assembler :140-158 + Assembler::become_clipped (assembler.hpp:411-421); `sel` drawn by the caller
+MG_DEVICE inline void clip_assembler(EnvCtx& e, AsmRec* t, uint32_t sel) {
+  const int32_t* cc = e.cfg + e.cfg[MGC_OFF_CLIPPER];
+  for (int i = 0; i < e.n_asm; i++) {
+    AsmRec* adj = &e.asms[i];
+    if (!clip_adjacent(e, t, adj)) continue;
+    adj->infection_weight += clip_infection_weight(e, t, adj);
+    if (adj->flags & MG_ASMF_CLIPPED) continue;
+    adj->flags |= MG_ASMF_BORDER;
+  }
+  t->flags = (uint8_t)((t->flags & ~(MG_ASMF_BORDER | MG_ASMF_UNCLIPPED)) | MG_ASMF_CLIPPED);
+  t->unclip_protocol = (int16_t)(cc[MG_CLIP_FIRST_PROTOCOL] + (int)sel);
+  t->cooldown_end = e.current_step;
+  t->cooldown_duration = 0;
+}
+MG_DEVICE inline void clip_on_unclip(EnvCtx& e, AsmRec* t) {  // :160-168
+  for (int i = 0; i < e.n_asm; i++) {
+    AsmRec* adj = &e.asms[i];
+    if (clip_adjacent(e, t, adj)) adj->infection_weight -= clip_infection_weight(e, t, adj);
+  }
+  t->flags |= MG_ASMF_UNCLIPPED;
+  if (t->infection_weight > 0) t->flags |= MG_ASMF_BORDER;
+}
+
+// ---------------------------------------------------------------- assembler use (assembler.hpp:455-526)
+struct ItemList {
+  int n;
+  int item[RS];
+  int val[RS];
+};
+MG_DEVICE inline void list_load(ItemList& l, const int32_t* w) {
+  l.n = w[MG_LIST_N];
+  for (int i = 0; i < l.n; i++) {
+    l.item[i] = w[MG_LIST_ITEM(i)];
+    l.val[i] = w[MG_LIST_VAL(i)];
+  }
+}
+MG_DEVICE inline bool list_has_positive(const ItemList& l) {
+  for (int i = 0; i < l.n; i++)
+    if (l.val[i] > 0) return true;
+  return false;
+}
+
+MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
+  AsmRec* a = &e.asms[asm_idx];
+  const int32_t* t = asm_type_cfg(e.cfg, a->cell);
+  uint32_t max_uses = (uint32_t)t[MG_ASM_MAX_USES];
+  if (max_uses > 0 && a->uses_count >= max_uses) return false;
+  uint32_t remaining = a->cooldown_end <= e.current_step ? 0u : a->cooldown_end - e.current_step;  // :318-323
+  bool partial = t[MG_ASM_ALLOW_PARTIAL] != 0;
+  if (remaining > 0 && !partial) return false;
+  int pi = asm_current_protocol(e, a);
+  if (pi < 0) return false;
+  const int32_t* p = proto_cfg(e.cfg, pi);
+  bool clipped = (a->flags & MG_ASMF_CLIPPED) != 0;
+  ItemList in, out;
+  if (remaining > 0 && partial) {  // scale_protocol_for_partial_usage :427-453
+    uint32_t duration = a->cooldown_duration, elapsed = duration - remaining;
+    list_load(in, p + MG_PROTO_SCALED_INPUTS);
+    list_load(out, p + MG_PROTO_SCALED_OUTPUTS);
+    bool original_has_output = list_has_positive(out);
+    for (int i = 0; i < in.n; i++) in.val[i] = (int)(uint16_t)(((uint32_t)(uint16_t)in.val[i] * elapsed + duration - 1) / duration);
+    for (int i = 0; i < out.n; i++) out.val[i] = (int)(uint16_t)(((uint32_t)(uint16_t)out.val[i] * elapsed) / duration);
+    if (!list_has_positive(out) && original_has_output && !clipped) return false;
+  } else {
+    list_load(in, p + MG_PROTO_INPUTS);
+    list_load(out, p + MG_PROTO_OUTPUTS);
+  }
+  // get_surrounding_agents(&actor) :48-92: NW,N,NE,W,E,SW,S,SE restricted to valid cells, rotated to the actor
+  int pr[8], pc[8], npos = 0;
+  for (int i = -1; i <= 1; i++)
+    for (int j = -1; j <= 1; j++) {
+      if (i == 0 && j == 0) continue;
+      int rr = (int)a->r + i, cc = (int)a->c + j;
+      if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+      pr[npos] = rr;
+      pc[npos] = cc;
+      npos++;
+    }
+  int start = 0;
+  for (int i = 0; i < npos; i++)
+    if (pr[i] == e.ag[actor].r && pc[i] == e.ag[actor].c) { start = i; break; }
+  int sur[8], nsur = 0;
+  for (int k = 0; k < npos; k++) {
+    int i = start + k;
+    if (i >= npos) i -= npos;
+    uint16_t g = grid_at(e, pr[i], pc[i]);
+    if (MG_GRID_KIND(g) == MG_GK_AGENT) sur[nsur++] = MG_GRID_INDEX(g);
+  }
+  InvView inputs[MG_MAX_SHARED];
+  int nin = 0;
+  for (int i = 0; i < nsur; i++) inputs[nin++] = agent_inv(e, sur[i]);
+  int dist = t[MG_ASM_CHEST_DISTANCE];
+  if (dist > 0) {  // get_surrounding_chests :96-121
+    for (int dr = -dist; dr <= dist; dr++)
+      for (int dc = -dist; dc <= dist; dc++) {
+        if (dr == 0 && dc == 0) continue;
+        int rr = (int)a->r + dr, cc = (int)a->c + dc;
+        if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+        uint16_t g = grid_at(e, rr, cc);
+        if (MG_GRID_KIND(g) == MG_GK_CHEST && nin < MG_MAX_SHARED) inputs[nin++] = chest_inv(e, MG_GRID_INDEX(g));
+      }
+  }
+  for (int i = 0; i < in.n; i++) {  // can_afford_protocol :124-137 (u16 accumulation)
+    uint32_t total = 0;
+    for (int k = 0; k < nin; k++) total = (total + inputs[k].amt[in.item[i]]) & 0xFFFFu;
+    if (total < (uint32_t)(uint16_t)in.val[i]) return false;
+  }
+  InvView outputs[8];  // get_output_inventories :198-223
+  int nout = 0;
+  int nvibes = p[MG_PROTO_NUM_VIBES];
+  if (nvibes > 1) {
+    uint32_t used = 0;  // which of the protocol's vibe slots are taken
+    for (int i = 0; i < nsur && nout < nvibes; i++) {
+      int v = e.ag[sur[i]].vibe;
+      if (v == 0) continue;
+      for (int s = 0; s < nvibes; s++) {
+        if (!((used >> s) & 1u) && p[MG_PROTO_VIBES + s] == v) {
+          used |= 1u << s;
+          outputs[nout++] = agent_inv(e, sur[i]);
+          break;
+        }
+      }
+    }
+  }
+  if (nout == 0) outputs[nout++] = agent_inv(e, actor);
+  bool can_receive = true;  // can_receive_output :143-171
+  if (list_has_positive(out)) {
+    can_receive = false;
+    for (int i = 0; i < out.n && !can_receive; i++) {
+      if (out.val[i] <= 0) continue;
+      uint32_t free_total = 0;
+      for (int k = 0; k < nout; k++) free_total = (free_total + (uint32_t)inv_free_space(outputs[k], out.item[i])) & 0xFFFFu;
+      if (free_total >= 1) can_receive = true;
+    }
+  }
+  if (!can_receive && !clipped) return false;
+  for (int i = 0; i < in.n; i++) shared_update(e, inputs, nin, in.item[i], -(int)(uint16_t)in.val[i]);
+  for (int i = 0; i < out.n; i++) {  // give_output_for_protocol :174-184
+    int distributed = shared_update(e, outputs, nout, out.item[i], (int)(uint16_t)out.val[i]);
+    if (distributed > 0) e.gstats[MG_GS_ASM_CREATED + out.item[i]] += (float)distributed;
+  }
+  a->cooldown_duration = (uint32_t)(uint16_t)p[MG_PROTO_COOLDOWN];
+  a->cooldown_end = e.current_step + a->cooldown_duration;
+  if (clipped) {  // become_unclipped :581-590
+    a->flags &= (uint8_t)~MG_ASMF_CLIPPED;
+    a->unclip_protocol = -1;
+    if (e.clip_enabled && (a->flags & MG_ASMF_TRACKED)) clip_on_unclip(e, a);
+  } else {
+    a->uses_count++;
+  }
+  return true;
+}
+
+// Chest::onUse / transfer_resources, chest.hpp:31-52,103-122
+MG_DEVICE MG_NOINLINE bool chest_on_use(EnvCtx& e, int chest_idx, int actor) {
+  ChestRec* ch = &e.chests[chest_idx];
+  const int32_t* ct = e.cfg + e.cfg[MGC_OFF_CHEST_TYPES] + cell_cfg(e.cfg, ch->cell)[MG_CELL_PARAM] * MG_CHEST_WORDS;
+  int nv = ct[MG_CHEST_NUM_VIBES];
+  if (nv == 0) return false;
+  int vibe = e.ag[actor].vibe, which = -1;
+  for (int i = 0; i < nv; i++)
+    if (ct[MG_CHEST_VIBE_IDS + i] == vibe) which = i;
+  if (which < 0) return false;
+  ItemList deltas;
+  list_load(deltas, ct + MG_CHEST_VIBE_LISTS + which * MG_LIST_WORDS);
+  InvView ai = agent_inv(e, actor), ci = chest_inv(e, chest_idx);
+  float* st = e.astats + (size_t)actor * e.S;
+  bool any = false;
+  for (int i = 0; i < deltas.n; i++) {
+    int item = deltas.item[i], d = deltas.val[i];
+    if (d > 0) {
+      int moved = transfer_resources(e, ai, ci, item, d, true);
+      if (moved > 0) { any = true; st[MG_AS_CHEST_DEPOSITED + item] += (float)moved; }
+    } else if (d < 0) {
+      int moved = transfer_resources(e, ci, ai, item, -d, true);
+      if (moved > 0) { any = true; st[MG_AS_CHEST_WITHDRAWN + item] += (float)moved; }
+    }
+  }
+  return any;
+}
+
+// Attack::try_attack and helpers, attack.hpp:93-253
+MG_DEVICE MG_NOINLINE bool try_attack(EnvCtx& e, int actor, uint16_t target_cell) {
+  if (MG_GRID_KIND(target_cell) != MG_GK_AGENT) return false;
+  int target = MG_GRID_INDEX(target_cell);
+  AgentRec* ac = &e.ag[actor];
+  AgentRec* tg = &e.ag[target];
+  if (tg->frozen > 0) return false;
+  const int32_t* k = e.cfg + e.cfg[MGC_OFF_ATTACK];
+  for (int i = 0; i < MG_MAX_RESOURCES; i++)
+    if ((int)ac->amt[i] < (k[MG_ATK_CONSUMED + i] & 0xFFFF)) return false;
+  InvView ai = agent_inv(e, actor), ti = agent_inv(e, target);
+  float* ast = e.astats + (size_t)actor * e.S;
+  bool blocked = false;
+  if (k[MG_ATK_HAS_DEFENSE]) {
+    const int32_t* vb = e.cfg + e.cfg[MGC_OFF_VIBES] + tg->vibe * MG_VIBE_WORDS;
+    int weapon = 0, armor = 0;
+    for (int i = 0; i < MG_MAX_RESOURCES; i++) weapon += (int)ac->amt[i] * k[MG_ATK_WEAPON + i];
+    for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+      int w = k[MG_ATK_ARMOR + i];
+      if (w == 0) continue;
+      int amount = tg->amt[i];
+      if (vb[MG_VIBE_RESOURCE] == i) amount += vb[MG_VIBE_BONUS];
+      armor += amount * w;
+    }
+    int bonus = weapon - armor > 0 ? weapon - armor : 0;
+    ItemList defense;
+    list_load(defense, k + MG_ATK_DEFENSE);
+    bool can_defend = true;
+    for (int i = 0; i < defense.n; i++) {
+      int required = defense.val[i] + bonus;
+      if ((int)tg->amt[defense.item[i]] < (required & 0xFFFF)) { can_defend = false; break; }
+    }
+    if (can_defend) {
+      for (int i = 0; i < defense.n; i++) inv_update(e, ti, defense.item[i], -(defense.val[i] + bonus), false, 0);
+      ast[MG_AS_ATTACK_BLOCKED_BY + tg->group] += 1.0f;
+      blocked = true;
+    }
+  }
+  if (!blocked) {
+    if (k[MG_ATK_FREEZE] > 0) tg->frozen = (int16_t)k[MG_ATK_FREEZE];
+    ItemList l;
+    list_load(l, k + MG_ATK_ACTOR_DELTA);
+    for (int i = 0; i < l.n; i++) inv_update(e, ai, l.item[i], l.val[i], false, 0);
+    list_load(l, k + MG_ATK_TARGET_DELTA);
+    for (int i = 0; i < l.n; i++) inv_update(e, ti, l.item[i], l.val[i], false, 0);
+    list_load(l, k + MG_ATK_LOOT);
+    for (int i = 0; i < l.n; i++) {
+      int amount = tg->amt[l.item[i]];
+      if (amount > 0) {
+        int stolen = inv_update(e, ai, l.item[i], amount, false, 0);
+        inv_update(e, ti, l.item[i], -stolen, false, 0);
+      }
+    }
+    if (ac->group == tg->group) ast[MG_AS_ATTACK_FRIENDLY_FIRE] += 1.0f;
+    else {
+      ast[MG_AS_ATTACK_HIT + tg->group] += 1.0f;
+      e.astats[(size_t)target * e.S + MG_AS_ATTACK_HIT_BY + ac->group] += 1.0f;
+    }
+  }
+  for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+    int amt = k[MG_ATK_CONSUMED + i] & 0xFFFF;
+    if (amt > 0) inv_update(e, ai, i, -amt, false, 0);
+  }
+  return true;
+}
+
+// Transfer::try_transfer, transfer.hpp:72-150
+MG_DEVICE MG_NOINLINE bool try_transfer(EnvCtx& e, int actor, uint16_t target_cell) {
+  AgentRec* ac = &e.ag[actor];
+  const int32_t* x = e.cfg + e.cfg[MGC_OFF_TRANSFER];
+  for (int i = 0; i < MG_MAX_RESOURCES; i++)
+    if ((int)ac->amt[i] < (x[MG_XFER_REQUIRED + i] & 0xFFFF)) return false;
+  if (MG_GRID_KIND(target_cell) != MG_GK_AGENT) return false;
+  int target = MG_GRID_INDEX(target_cell);
+  AgentRec* tg = &e.ag[target];
+  if (tg->frozen > 0) return false;
+  int eidx = e.cfg[e.cfg[MGC_OFF_VIBES] + ac->vibe * MG_VIBE_WORDS + MG_VIBE_TRANSFER];
+  if (eidx < 0) return false;
+  const int32_t* eff = x + MG_XFER_EFFECTS + eidx * MG_XFER_EFFECT_WORDS;
+  ItemList ad, td;
+  list_load(ad, eff + MG_XFER_ACTOR);
+  list_load(td, eff + MG_XFER_TARGET);
+  InvView ai = agent_inv(e, actor), ti = agent_inv(e, target);
+  for (int i = 0; i < ad.n; i++)
+    if (ad.val[i] < 0 && (int)ac->amt[ad.item[i]] < -ad.val[i]) return false;
+  for (int i = 0; i < td.n; i++)
+    if (td.val[i] < 0 && (int)tg->amt[td.item[i]] < -td.val[i]) return false;
+  for (int i = 0; i < ad.n; i++)
+    if (ad.val[i] > 0 && ad.val[i] > inv_free_space(ai, ad.item[i])) return false;
+  for (int i = 0; i < td.n; i++)
+    if (td.val[i] > 0 && td.val[i] > inv_free_space(ti, td.item[i])) return false;
+  float* ast = e.astats + (size_t)actor * e.S;
+  for (int i = 0; i < ad.n; i++)
+    if (ad.val[i] != 0) {
+      int actual = inv_update(e, ai, ad.item[i], ad.val[i], false, 0);
+      if (actual != 0) ast[MG_AS_TRANSFER_SELF + ad.item[i]] += (float)actual;
+    }
+  for (int i = 0; i < td.n; i++)
+    if (td.val[i] != 0) {
+      int actual = inv_update(e, ti, td.item[i], td.val[i], false, 0);
+      if (actual != 0) ast[MG_AS_TRANSFER_TO + tg->group * RS + td.item[i]] += (float)actual;
+    }
+  ast[MG_AS_TRANSFER_COUNT] += 1.0f;
+  return true;
+}
+
+// Move::_handle_action, move.hpp:74-141
+MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
+  AgentRec* ac = &e.ag[actor];
+  // orientation.hpp:28-48: N,S,W,E,NW,NE,SW,SE packed as 2-bit (delta+1) fields
+  int dr = (int)((0xA058u >> (2 * arg)) & 3u) - 1;   // -1,+1,0,0,-1,-1,+1,+1
+  int dc = (int)((0x8885u >> (2 * arg)) & 3u) - 1;   //  0, 0,-1,+1,-1,+1,-1,+1
+  int tr = (int)ac->r + dr, tc = (int)ac->c + dc;
+  if (tr < 0 || tc < 0 || tr >= e.H || tc >= e.W) return false;  // u16 wrap + is_valid_location
+  uint16_t target = grid_at(e, tr, tc);
+  int handler = e.cfg[e.cfg[MGC_OFF_VIBES] + ac->vibe * MG_VIBE_WORDS + MG_VIBE_HANDLER];
+  if (handler == MG_HANDLER_ATTACK && try_attack(e, actor, target)) return true;
+  if (handler == MG_HANDLER_TRANSFER && try_transfer(e, actor, target)) return true;
+  if (target == 0) {  // Grid::move_object, core/grid.hpp:70-83
+    e.grid[tr * e.W + tc] = (uint16_t)(0x4000 | actor);
+    e.grid[(int)ac->r * e.W + (int)ac->c] = 0;
+    ac->r = (uint16_t)tr;
+    ac->c = (uint16_t)tc;
+    return true;
+  }
+  int kind = MG_GRID_KIND(target), idx = MG_GRID_INDEX(target);
+  if (kind == MG_GK_AGENT) {
+    AgentRec* tg = &e.ag[idx];
+    if (tg->frozen > 0) {  // Grid::swap_objects :85-94
+      e.grid[(int)ac->r * e.W + (int)ac->c] = target;
+      e.grid[tr * e.W + tc] = (uint16_t)(0x4000 | actor);
+      tg->r = ac->r;
+      tg->c = ac->c;
+      ac->r = (uint16_t)tr;
+      ac->c = (uint16_t)tc;
+      e.astats[(size_t)actor * e.S + MG_AS_SWAP] += 1.0f;
+      return true;
+    }
+    return false;  // Agent::onUse, agent.cpp:179-185
+  }
+  if (kind == MG_GK_ASM) return assembler_on_use(e, idx, actor);
+  if (kind == MG_GK_CHEST) return chest_on_use(e, idx, actor);
+  return false;  // walls are not Usable
+}
+
+// ActionHandler::handle_action, action_handler.hpp:99-153
+MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
+  AgentRec* ac = &e.ag[actor];
+  float* st = e.astats + (size_t)actor * e.S;
+  if (ac->frozen != 0) {
+    st[MG_AS_FROZEN_TICKS] += 1.0f;
+    if (ac->frozen > 0) ac->frozen -= 1;
+    return false;
+  }
+  const int32_t* res = e.cfg + e.cfg[MGC_OFF_ACTION_RES] + kind * MG_ACTRES_WORDS;
+  bool has = true;
+  for (int i = 0; i < MG_MAX_RESOURCES; i++)
+    if ((int)ac->amt[i] < (res[MG_ACTRES_REQUIRED + i] & 0xFFFF)) { has = false; break; }
+  bool success = false;
+  if (has) {
+    if (kind == MG_ACTION_NOOP) success = true;
+    else if (kind == MG_ACTION_MOVE) success = handle_move(e, actor, arg);
+    else { ac->vibe = (uint8_t)arg; success = true; }  // change_vibe.hpp:48-51
+  }
+  if (ac->r == ac->prev_r && ac->c == ac->prev_c) {
+    ac->steps_without_motion += 1;
+    if ((float)ac->steps_without_motion > st[MG_AS_MAX_STEPS_WITHOUT_MOTION])
+      st[MG_AS_MAX_STEPS_WITHOUT_MOTION] = (float)ac->steps_without_motion;
+  } else {
+    ac->steps_without_motion = 0;
+  }
+  ac->prev_r = ac->r;
+  ac->prev_c = ac->c;
+  if (success) {
+    st[MG_AS_ACTION_SUCCESS + kind] += 1.0f;
+    InvView ai = agent_inv(e, actor);
+    for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+      int amt = res[MG_ACTRES_CONSUMED + i] & 0xFFFF;
+      if (amt > 0) inv_update(e, ai, i, -amt, false, 0);
+    }
+  } else {
+    st[MG_AS_ACTION_FAILED + kind] += 1.0f;
+    st[MG_AS_ACTION_FAILED_ANY] += 1.0f;
+  }
+  return success;
+}
+
+// inventory regeneration for one agent, mettagrid_c.cpp:625-640
+MG_DEVICE inline void regen_agent(EnvCtx& e, int ai) {
+  AgentRec* a = &e.ag[ai];
+  const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
+  if (!grp[MG_GRP_HAS_REGEN]) return;
+  int which = -1, fallback = -1;
+  for (int i = 0; i < grp[MG_GRP_NUM_REGEN]; i++) {
+    if (grp[MG_GRP_REGEN_VIBE + i] == (int)a->vibe) which = i;
+    if (grp[MG_GRP_REGEN_VIBE + i] == 0) fallback = i;
+  }
+  if (which < 0) which = fallback;
+  if (which < 0) return;
+  const int32_t* l = grp + MG_GRP_REGEN_LISTS + which * MG_LIST_WORDS;
+  InvView iv = agent_inv(e, ai);
+  for (int i = 0; i < l[MG_LIST_N]; i++) inv_update(e, iv, l[MG_LIST_ITEM(i)], l[MG_LIST_VAL(i)], false, 0);
+}
+
+// Agent::compute_stat_rewards, agent.cpp:103-132. Returns the reward delta of this step.
+MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
+  AgentRec* a = &e.ag[ai];
+  const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
+  int n = grp[MG_GRP_NUM_REWARDS];
+  if (n == 0) return 0.0f;
+  const float* st = e.astats + (size_t)ai * e.S;
+  float total = 0.0f;
+  for (int i = 0; i < n; i++) {
+    const int32_t* rw = grp + MG_GRP_REWARDS + i * MG_RWD_WORDS;
+    float v = rw[MG_RWD_AGENT_STAT] >= 0 ? st[rw[MG_RWD_AGENT_STAT]] : 0.0f;
+    v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? e.gstats[rw[MG_RWD_GAME_STAT]] : 0.0f);
+    float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));
+    if (rw[MG_RWD_HAS_MAX]) {
+      float cap = MG_INT_AS_FLOAT(rw[MG_RWD_MAX]);
+      r = cap < r ? cap : r;  // std::min(stats_reward, cap)
+    }
+    total = MG_FADD(total, r);
+  }
+  float delta = MG_FADD(total, -a->current_stat_reward);
+  if (delta != 0.0f) a->current_stat_reward = total;
+  return delta;
+}
+
+#endif  // MG_DEVICE_CUH_

@@ -1,0 +1,561 @@
+// mg_kernels.cuh -- the three kernels of a simulator step.
+//
+//   mg_reset_kernel   one warp per env: (re)build an env from its pool map     (episode start)
+//   mg_step_kernel    one warp per env: MettaGrid::_step up to the observations (mettagrid_c.cpp:572-650)
+//                     plus rewards / truncation (:655-677) and the auto-reset of
+//                     MettaGridPufferEnv.step (envs/mettagrid_puffer_env.py:158-164)
+//   mg_obs_kernel     one warp per agent: _compute_observations (:557-563)
+//
+// The last_reward token is identically 0 in the reference (see mg_obs.cuh), so computing rewards
+// before the observation kernel does not change any output byte.
+#ifndef MG_KERNELS_CUH_
+#define MG_KERNELS_CUH_
+
+#include "mg_device.cuh"
+#include "mg_obs.cuh"
+#include "mg_rng.cuh"
+
+#define MG_STEP_WARPS 4    /* envs per CTA in the reset/step kernels */
+#define MG_OBS_WARPS 8     /* agents per CTA in the observation kernel */
+#define MG_MAX_AGENTS 64   /* agents per env that fit the shared-memory staging */
+
+struct StepSmem {
+  AgentRec ag[MG_MAX_AGENTS];
+  int32_t action[MG_MAX_AGENTS];
+  int32_t executed[MG_MAX_AGENTS];
+  uint8_t success[MG_MAX_AGENTS];
+  uint8_t order[MG_MAX_AGENTS];
+  int32_t scratch[2 * MG_RES_STRIDE + 8];
+};
+
+MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
+  EnvCtx e;
+  e.cfg = b.cfg;
+  e.env = env;
+  e.H = b.H; e.W = b.W; e.A = b.A; e.R = b.R; e.S = b.S;
+  e.current_step = er.current_step;
+  e.grid = b.grid + (size_t)env * b.grid_stride;
+  e.ag = ag;
+  e.asms = b.asms + (size_t)env * b.max_asm;
+  e.chests = b.chests + (size_t)env * b.max_chest;
+  e.astats = b.agent_stats + (size_t)env * b.A * b.S;
+  e.gstats = b.game_stats + (size_t)env * b.GS;
+  e.n_asm = er.n_asm;
+  e.clip_enabled = b.has_clipper;
+  e.clip_length_scale = er.clip_length_scale;
+  return e;
+}
+
+// tokens_written / tokens_dropped / tokens_free_space (mettagrid_c.cpp:552-554) are produced by the
+// observation kernel as integer counts per agent and folded into the float game stats here, agent
+// by agent, so that the float additions happen in the reference's order.
+MG_DEVICE inline void fold_token_stats_warp(const MgBatch& b, int env, int lane) {
+  uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
+  float* gs = b.game_stats + (size_t)env * b.GS;
+  if (lane < 3) {
+    float acc = gs[MG_GS_TOKENS_WRITTEN + lane];
+    bool any = false;
+    for (int ai = 0; ai < b.A; ai++) {
+      const int written = tc[ai * 2], attempted = tc[ai * 2 + 1];
+      if (attempted == 0xFFFF) continue;  // no observation was computed for this agent since the last fold
+      any = true;
+      const int v = lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written);
+      acc = MG_FADD(acc, (float)v);
+    }
+    if (any) gs[MG_GS_TOKENS_WRITTEN + lane] = acc;
+  }
+  __syncwarp();
+  for (int i = lane; i < b.A; i += 32) tc[i * 2 + 1] = 0xFFFF;
+  __syncwarp();
+}
+
+// Cache, on every assembler that has an agent next to it, the protocol observers will see this
+// step (see sink_object). One agent per lane; duplicates write identical values.
+MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
+  if (!b.cfg[MGC_HAS_VIBE_ASM] || !b.cfg[MGC_PROTOCOL_DETAILS_OBS]) return;
+  for (int ai = lane; ai < e.A; ai += 32) {
+    const int r = e.ag[ai].r, c = e.ag[ai].c;
+    for (int i = -1; i <= 1; i++)
+      for (int j = -1; j <= 1; j++) {
+        if (i == 0 && j == 0) continue;
+        const int rr = r + i, cc = c + j;
+        if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+        const uint16_t g = grid_at(e, rr, cc);
+        if (MG_GRID_KIND(g) != MG_GK_ASM) continue;
+        AsmRec* a = &e.asms[MG_GRID_INDEX(g)];
+        const int pi = asm_current_protocol(e, a);
+        a->cache_protocol = pi;
+        a->cache_step = e.current_step;
+      }
+  }
+  __syncwarp();
+}
+
+// One observation pass that only counts tokens (nothing is written): the reference runs such
+// passes on buffers nobody reads (see reset_env_warp), but their token counts stay in the stats.
+MG_DEVICE inline void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step) {
+  __syncwarp();
+  for (int ai = 0; ai < b.A; ai++) {
+    const int attempted = obs_encode_agent_warp(b, env, ai, lane, nullptr, current_step, 0);
+    if (lane == 0) {
+      uint16_t* tc = b.tok_counts + ((size_t)env * b.A + ai) * 2;
+      tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
+      tc[1] = (uint16_t)attempted;
+    }
+  }
+  __syncwarp();
+  fold_token_stats_warp(b, env, lane);
+}
+
+// ---------------------------------------------------------------- reset
+// MettaGrid::MettaGrid + _init_grid + Clipper ctor (mettagrid_c.cpp:46-245, clipper.hpp:35-91),
+// from a map that the host already split into per-kind object tables (metta_b200/maps.py).
+MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er) {
+  const int32_t* cfg = b.cfg;
+  const int map = er.map_idx;
+  // grid: 16-byte copies (grid_stride is a multiple of 8 cells)
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(b.pool_grid + (size_t)map * b.grid_stride);
+    uint4* dst = reinterpret_cast<uint4*>(b.grid + (size_t)env * b.grid_stride);
+    for (int i = lane; i < b.grid_stride / 8; i += 32) dst[i] = src[i];
+  }
+  er.current_step = 0;
+  er.done = 0;
+  er.n_asm = b.pool_n_asm[map];
+  er.n_chest = b.pool_n_chest[map];
+  er.rng_idx = MT_N;
+  er.clip_rng_idx = MT_N;
+  float* astats = b.agent_stats + (size_t)env * b.A * b.S;
+  for (int i = lane; i < b.A * b.S; i += 32) astats[i] = 0.0f;
+  float* gstats = b.game_stats + (size_t)env * b.GS;
+  for (int i = lane; i < b.GS; i += 32) gstats[i] = 0.0f;
+  uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
+  for (int i = lane; i < b.A; i += 32) { tc[i * 2] = 0; tc[i * 2 + 1] = 0xFFFF; }
+  AgentRec* agents = b.agents + (size_t)env * b.A;
+  AsmRec* asms = b.asms + (size_t)env * b.max_asm;
+  ChestRec* chests = b.chests + (size_t)env * b.max_chest;
+  const int32_t* pa = b.pool_agents + (size_t)map * b.A * 3;
+  for (int ai = lane; ai < b.A; ai += 32) {
+    AgentRec a;
+    const int32_t* cc = cell_cfg(cfg, pa[ai * 3 + 2]);
+    const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + cc[MG_CELL_PARAM] * MG_GRP_WORDS;
+    a.r = a.prev_r = (uint16_t)pa[ai * 3 + 0];
+    a.c = a.prev_c = (uint16_t)pa[ai * 3 + 1];
+    a.vibe = (uint8_t)grp[MG_GRP_INITIAL_VIBE];
+    a.group = (uint8_t)cc[MG_CELL_PARAM];
+    a.frozen = 0;
+    a.steps_without_motion = 0;
+    a.order = MG_ORDER_EMPTY;
+    for (int i = 0; i < MG_MAX_RESOURCES; i++) a.amt[i] = 0;
+    a.pad0 = 0;
+    a.current_stat_reward = 0.0f;
+    a.episode_reward = 0.0f;
+    a.pad1 = 0;
+    agents[ai] = a;
+    b.last_action[(size_t)env * b.A + ai] = 0;
+    b.action_success[(size_t)env * b.A + ai] = 0;
+  }
+  const int32_t* ps = b.pool_asm + (size_t)map * b.max_asm * 3;
+  for (int i = lane; i < er.n_asm; i += 32) {
+    AsmRec a;
+    a.r = (uint16_t)ps[i * 3 + 0];
+    a.c = (uint16_t)ps[i * 3 + 1];
+    a.cell = (uint8_t)ps[i * 3 + 2];
+    const int32_t* ty = asm_type_cfg(cfg, a.cell);
+    a.flags = (uint8_t)(ty[MG_ASM_START_CLIPPED] ? MG_ASMF_CLIPPED : 0);
+    if (b.has_clipper && !ty[MG_ASM_CLIP_IMMUNE]) a.flags |= MG_ASMF_TRACKED | MG_ASMF_UNCLIPPED;
+    a.unclip_protocol = -1;
+    a.cooldown_end = a.cooldown_duration = a.uses_count = 0;
+    a.infection_weight = 0;
+    a.cache_protocol = -1;
+    a.cache_step = 0xFFFFFFFFu;
+    asms[i] = a;
+  }
+  const int32_t* pc = b.pool_chest + (size_t)map * b.max_chest * 3;
+  for (int i = lane; i < er.n_chest; i += 32) {
+    ChestRec c;
+    c.r = (uint16_t)pc[i * 3 + 0];
+    c.c = (uint16_t)pc[i * 3 + 1];
+    c.cell = (uint8_t)pc[i * 3 + 2];
+    c.pad[0] = c.pad[1] = c.pad[2] = 0;
+    c.order = MG_ORDER_EMPTY;
+    for (int k = 0; k < MG_MAX_RESOURCES; k++) c.amt[k] = 0;
+    c.pad1[0] = c.pad1[1] = c.pad1[2] = 0;
+    chests[i] = c;
+  }
+  uint32_t* mt = b.rng + (size_t)env * MT_N;
+  if (lane == 0) mt_seed_serial(mt, er.seed);  // mettagrid_c.cpp:57
+  __syncwarp();
+  EnvCtx e = make_ctx(b, env, agents, er);
+  // initial inventories bypass the limits but still report through on_inventory_change
+  // (agent.cpp:48-52, chest.hpp:78-82)
+  for (int ai = lane; ai < b.A; ai += 32) {
+    const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + agents[ai].group * MG_GRP_WORDS;
+    const int32_t* l = grp + MG_GRP_INITIAL_INV;
+    InvView iv = agent_inv(e, ai);
+    for (int k = 0; k < l[MG_LIST_N]; k++) inv_update(e, iv, l[MG_LIST_ITEM(k)], l[MG_LIST_VAL(k)] & 0xFFFF, true, 0);
+  }
+  if (lane == 0) {  // chests share the game stat slots: one lane, creation order
+    for (int i = 0; i < er.n_chest; i++) {
+      const int32_t* ct = cfg + cfg[MGC_OFF_CHEST_TYPES] + cell_cfg(cfg, chests[i].cell)[MG_CELL_PARAM] * MG_CHEST_WORDS;
+      const int32_t* l = ct + MG_CHEST_INITIAL_INV;
+      InvView iv = chest_inv(e, i);
+      for (int k = 0; k < l[MG_LIST_N]; k++)
+        if (l[MG_LIST_VAL(k)] > 0) inv_update(e, iv, l[MG_LIST_ITEM(k)], l[MG_LIST_VAL(k)], true, 0);
+    }
+  }
+  __syncwarp();
+  // The reference's constructor ends with an observation pass on its internal buffers
+  // (_make_buffers -> set_buffers -> _init_buffers, mettagrid_c.cpp:139-140,247-262), BEFORE the
+  // clipper exists; the caller's set_buffers (simulator.py:93-100) then runs the pass whose output
+  // is kept. Both passes add to tokens_written/dropped/free_space, so the first is counted here.
+  update_protocol_cache_warp(b, e, lane);
+  count_observation_pass_warp(b, env, lane, 0u);
+  if (b.has_clipper) {
+    uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
+    for (int i = lane; i < MT_N; i += 32) cmt[i] = mt[i];  // the clipper keeps its own copy of the rng
+    const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
+    int scale = cc[MG_CLIP_LENGTH_SCALE];
+    int ntracked = 0;
+    for (int i = 0; i < er.n_asm; i++) ntracked += (asms[i].flags & MG_ASMF_TRACKED) ? 1 : 0;
+    if (scale <= 0 && ntracked > 0) {  // clipper.hpp:62-78 integer Newton square root
+      const uint32_t sparsity = (uint32_t)(b.W * b.H) / (uint32_t)ntracked;
+      int32_t root = 1, next = 10;
+      for (int i = 0; i < 10; i++) {
+        if (next == root || root == 0) break;
+        root = next;
+        next = (int32_t)((sparsity + (uint32_t)(root * root) + (uint32_t)(2 * root - 2)) / (uint32_t)(2 * root));
+      }
+      scale = root / 2 > 1 ? root / 2 : 1;
+    }
+    if (scale <= 0) scale = 1;
+    er.clip_length_scale = scale;
+    e.clip_length_scale = scale;
+    __syncwarp();
+    for (int i = 0; i < er.n_asm; i++) {  // starting_clipped_assemblers, object id order
+      const bool start = (asms[i].flags & MG_ASMF_TRACKED) && asm_type_cfg(cfg, asms[i].cell)[MG_ASM_START_CLIPPED];
+      if (!start) continue;
+      const uint32_t sel = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+      if (lane == 0) {
+        asms[i].flags &= (uint8_t)~MG_ASMF_CLIPPED;
+        clip_assembler(e, &asms[i], sel);
+      }
+      __syncwarp();
+    }
+  }
+  update_protocol_cache_warp(b, e, lane);
+}
+
+// Sum a finished episode into the batch accumulators before its state is overwritten.
+MG_DEVICE inline void accumulate_episode_warp(const MgBatch& b, int env, int lane) {
+  const AgentRec* agents = b.agents + (size_t)env * b.A;
+  const float* astats = b.agent_stats + (size_t)env * b.A * b.S;
+  const float* gstats = b.game_stats + (size_t)env * b.GS;
+  if (lane == 0) {
+    double r = 0.0;
+    for (int ai = 0; ai < b.A; ai++) r += (double)agents[ai].episode_reward;
+    atomicAdd(&b.episode_accum[0], 1.0);
+    atomicAdd(&b.episode_accum[1], r);
+  }
+  for (int s = lane; s < b.S; s += 32) {
+    double v = 0.0;
+    for (int ai = 0; ai < b.A; ai++) v += (double)astats[(size_t)ai * b.S + s];
+    if (v != 0.0) atomicAdd(&b.episode_accum[2 + s], v);
+  }
+  for (int s = lane; s < b.GS; s += 32)
+    if (gstats[s] != 0.0f) atomicAdd(&b.episode_accum[2 + b.S + s], (double)gstats[s]);
+}
+
+MG_GLOBAL void mg_reset_kernel(MgBatch b, const uint8_t* mask) {
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * MG_STEP_WARPS + (threadIdx.x >> 5);
+  if (env >= b.num_envs) return;
+  if (mask != nullptr && !mask[env]) return;
+  EnvRec er = b.env[env];
+  reset_env_warp(b, env, lane, er);
+  for (int ai = lane; ai < b.A; ai += 32) {  // _init_buffers, mettagrid_c.cpp:264-289
+    const size_t g = (size_t)env * b.A + ai;
+    b.rewards[g] = 0.0f;
+    b.terminals[g] = 0;
+    b.truncations[g] = 0;
+  }
+  if (lane == 0) b.env[env] = er;
+}
+
+// ---------------------------------------------------------------- step
+MG_GLOBAL void mg_step_kernel(MgBatch b) {
+  MG_SHARED StepSmem smem[MG_STEP_WARPS];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int env = blockIdx.x * MG_STEP_WARPS + warp;
+  if (env >= b.num_envs) return;
+  StepSmem& sm = smem[warp];
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  EnvRec er = b.env[env];
+
+  fold_token_stats_warp(b, env, lane);
+  if (er.done && b.auto_reset) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
+    accumulate_episode_warp(b, env, lane);
+    __syncwarp();
+    if (b.num_maps > 0) er.map_idx = (er.map_idx + b.map_stride) % b.num_maps;
+    er.episodes += 1;
+    reset_env_warp(b, env, lane, er);
+    __syncwarp();
+    // set_buffers of the new Simulation: the initial observation nobody sees is still counted
+    count_observation_pass_warp(b, env, lane, 0u);
+  }
+
+  // stage this env's agents in shared memory
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(b.agents + (size_t)env * A);
+    uint4* dst = reinterpret_cast<uint4*>(sm.ag);
+    for (int i = lane; i < A * 4; i += 32) dst[i] = src[i];
+    for (int ai = lane; ai < A; ai += 32) {
+      sm.action[ai] = b.actions[(size_t)env * A + ai];
+      sm.executed[ai] = 0;
+      sm.success[ai] = 0;
+    }
+  }
+  __syncwarp();
+  er.current_step += 1;
+  EnvCtx e = make_ctx(b, env, sm.ag, er);
+  uint32_t* mt = b.rng + (size_t)env * MT_N;
+
+  // random processing order (mettagrid_c.cpp:591-593)
+  std_shuffle_warp(mt, er.rng_idx, lane, sm.order, A);
+
+  // out-of-range actions: counted once per priority pass, two passes (mettagrid_c.cpp:599-608)
+  const int nact = cfg[MGC_NUM_ACTIONS];
+  for (int ai = lane; ai < A; ai += 32) {
+    const int a = sm.action[ai];
+    if (a < 0 || a >= nact) {
+      float* st = e.astats + (size_t)ai * e.S + MG_AS_INVALID_INDEX;
+      *st = MG_FADD(MG_FADD(*st, 1.0f), 1.0f);
+    }
+  }
+  __syncwarp();
+
+  // the ordered action pass: later agents see what earlier agents did
+  if (lane == 0) {
+    const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+    for (int k = 0; k < A; k++) {
+      const int ai = sm.order[k];
+      const int a = sm.action[ai];
+      if (a < 0 || a >= nact) continue;
+      const bool ok = handle_action(e, ai, acts[a * MG_ACT_WORDS + MG_ACT_KIND], acts[a * MG_ACT_WORDS + MG_ACT_ARG]);
+      sm.success[ai] = ok ? 1 : 0;
+      if (ok) sm.executed[ai] = a;
+    }
+  }
+  __syncwarp();
+
+  // inventory regeneration (mettagrid_c.cpp:625-640): independent per agent
+  const uint32_t regen = (uint32_t)cfg[MGC_REGEN_INTERVAL];
+  if (regen > 0u && er.current_step % regen == 0u) {
+    for (int ai = lane; ai < A; ai += 32) regen_agent(e, ai);
+    __syncwarp();
+  }
+
+  // damage (agent.cpp:134-177): agent order, draws from the env rng
+  for (int base = 0; base < A; base += 32) {
+    const int ai = base + lane;
+    bool met = false;
+    if (ai < A) {
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
+      if (grp[MG_GRP_DAMAGE_ENABLED]) {
+        met = true;
+        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
+        for (int i = 0; i < th[MG_LIST_N]; i++)
+          if ((int)sm.ag[ai].amt[th[MG_LIST_ITEM(i)]] < (th[MG_LIST_VAL(i)] & 0xFFFF)) { met = false; break; }
+      }
+    }
+    uint32_t todo = __ballot_sync(MG_FULL_MASK, met);
+    while (todo) {
+      const int who = base + (__ffs((int)todo) - 1);
+      todo &= todo - 1u;
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[who].group * MG_GRP_WORDS;
+      if (lane == 0) {
+        InvView iv = agent_inv(e, who);
+        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
+        for (int i = 0; i < th[MG_LIST_N]; i++) inv_update(e, iv, th[MG_LIST_ITEM(i)], -th[MG_LIST_VAL(i)], false, 0);
+        const int32_t* rs = grp + MG_GRP_DAMAGE_RESOURCES;
+        int n = 0;
+        for (int i = 0; i < rs[MG_LIST_N]; i++) {
+          const int removable = (int)sm.ag[who].amt[rs[MG_LIST_ITEM(i)]] - rs[MG_LIST_VAL(i)];
+          if (removable > 0) { sm.scratch[1 + n] = rs[MG_LIST_ITEM(i)]; sm.scratch[1 + MG_RES_STRIDE + n] = removable; n++; }
+        }
+        sm.scratch[0] = n;
+      }
+      __syncwarp();
+      const int n = sm.scratch[0];
+      if (n > 0) {
+        int weights[MG_RES_STRIDE];
+        for (int i = 0; i < n; i++) weights[i] = sm.scratch[1 + MG_RES_STRIDE + i];
+        const int sel = discrete_pick_warp(mt, er.rng_idx, lane, weights, n);
+        if (lane == 0) {
+          InvView iv = agent_inv(e, who);
+          const int item = sm.scratch[1 + sel];
+          inv_update(e, iv, item, -1, false, 0);
+          float* st = e.astats + (size_t)who * e.S;
+          st[MG_AS_DAMAGE_ITEMS_LOST] += 1.0f;
+          st[MG_AS_DAMAGED + item] += 1.0f;
+        }
+      }
+      if (lane == 0) e.astats[(size_t)who * e.S + MG_AS_DAMAGE_TRIGGERED] += 1.0f;
+      __syncwarp();
+    }
+  }
+
+  // clipper (clipper.hpp:203-238): draws from its private rng copy
+  if (b.has_clipper) {
+    const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
+    uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
+    const uint32_t period = (uint32_t)cc[MG_CLIP_PERIOD];
+    bool fire;
+    if (period == 0u) {
+      // uniform_int_distribution<uint32_t>(1, 0): the 64-bit range wraps, libstdc++ composes two draws
+      // (uniform_int_dist.h:331-356) and truncates: the result is 1 only when the second word is 0.
+      (void)mt_next_warp(cmt, er.clip_rng_idx, lane);
+      fire = mt_next_warp(cmt, er.clip_rng_idx, lane) == 0u;
+    } else {
+      fire = uniform_below_warp(cmt, er.clip_rng_idx, lane, period) == 0u;
+    }
+    if (fire) {
+      if (lane == 0) {
+        int nun = 0;
+        uint32_t total = 0;
+        for (int i = 0; i < e.n_asm; i++) {
+          nun += (e.asms[i].flags & MG_ASMF_UNCLIPPED) ? 1 : 0;
+          if (e.asms[i].flags & MG_ASMF_BORDER) total += e.asms[i].infection_weight;
+        }
+        sm.scratch[0] = nun;
+        sm.scratch[1] = (int32_t)total;
+      }
+      __syncwarp();
+      const int nun = sm.scratch[0];
+      const uint32_t total = (uint32_t)sm.scratch[1];
+      __syncwarp();
+      if (nun > 0) {
+        int pick = -1;
+        if (total == 0u) {
+          uint32_t k = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)nun);
+          for (int i = 0; i < e.n_asm && pick < 0; i++)
+            if (e.asms[i].flags & MG_ASMF_UNCLIPPED) { if (k == 0u) pick = i; else k--; }
+        } else {
+          uint32_t rw = uniform_below_warp(cmt, er.clip_rng_idx, lane, total) + 1u;
+          for (int i = 0; i < e.n_asm && pick < 0; i++) {
+            if (!(e.asms[i].flags & MG_ASMF_BORDER)) continue;
+            if (rw <= e.asms[i].infection_weight) pick = i; else rw -= e.asms[i].infection_weight;
+          }
+        }
+        if (pick >= 0) {
+          const uint32_t sel = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+          if (lane == 0) clip_assembler(e, &e.asms[pick], sel);
+          __syncwarp();
+        }
+      }
+    }
+  }
+
+  update_protocol_cache_warp(b, e, lane);
+
+  // rewards, episode totals, truncation (mettagrid_c.cpp:655-677) and the write-back
+  const uint32_t max_steps = (uint32_t)cfg[MGC_MAX_STEPS];
+  bool term = false, trunc = false;
+  if (max_steps > 0u && er.current_step >= max_steps) {
+    if (cfg[MGC_EPISODE_TRUNCATES]) trunc = true; else term = true;
+  }
+  if (er.early_reset_step != 0u && er.current_step >= er.early_reset_step) {  // Simulation.end_episode
+    trunc = true;
+    er.early_reset_step = 0u;
+  }
+  // flags are sticky within an episode (the reference only ever sets them) and cleared by reset
+  er.done = (uint8_t)(er.done | (term ? 1 : 0) | (trunc ? 2 : 0));
+  for (int ai = lane; ai < A; ai += 32) {
+    const size_t g = (size_t)env * A + ai;
+    const float delta = stat_reward_delta(e, ai);
+    sm.ag[ai].episode_reward = MG_FADD(sm.ag[ai].episode_reward, delta);
+    b.rewards[g] = delta;
+    b.terminals[g] = (uint8_t)(er.done & 1);
+    b.truncations[g] = (uint8_t)((er.done >> 1) & 1);
+    b.last_action[g] = sm.executed[ai];
+    b.action_success[g] = sm.success[ai];
+  }
+  __syncwarp();
+  {
+    uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
+    const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
+    for (int i = lane; i < A * 4; i += 32) dst[i] = src[i];
+  }
+  if (lane == 0) b.env[env] = er;
+}
+
+// ---------------------------------------------------------------- observations
+MG_GLOBAL void mg_obs_kernel(MgBatch b, const uint8_t* mask) {
+  MG_DYN_SMEM(dyn);
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const long long g = (long long)blockIdx.x * MG_OBS_WARPS + warp;  // global agent index
+  if (g >= (long long)b.num_envs * b.A) return;
+  const int env = (int)(g / b.A), ai = (int)(g % b.A);
+  if (mask != nullptr && !mask[env]) return;
+  const int row_bytes = b.T * 3;
+  const int slot = (row_bytes + 16 + 15) & ~15;  // room to mirror the row's misalignment
+  uint8_t* out = b.obs + (size_t)g * row_bytes;
+  const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
+  uint8_t* base = dyn + (size_t)warp * slot;     // 16-byte aligned
+  uint8_t* row = base + mis;                     // row and out are congruent mod 16
+  {
+    uint4 ff;
+    ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
+    uint4* p = reinterpret_cast<uint4*>(base);
+    for (int i = lane; i < slot / 16; i += 32) p[i] = ff;
+  }
+  __syncwarp();
+  const uint32_t current_step = b.env[env].current_step;
+  const int attempted = obs_encode_agent_warp(b, env, ai, lane, row, current_step, b.last_action[g]);
+  __syncwarp();
+  // store: bytes up to the first 16-byte boundary, 16-byte body, byte tail
+  const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
+  const int body = (row_bytes - head) & ~15;
+  for (int i = lane; i < head; i += 32) out[i] = row[i];
+  {
+    const uint4* s = reinterpret_cast<const uint4*>(row + head);
+    uint4* d = reinterpret_cast<uint4*>(out + head);
+    for (int i = lane; i < body / 16; i += 32) d[i] = s[i];
+  }
+  for (int i = head + body + lane; i < row_bytes; i += 32) out[i] = row[i];
+  if (lane == 0) {
+    uint16_t* tc = b.tok_counts + (size_t)g * 2;
+    tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
+    tc[1] = (uint16_t)attempted;
+  }
+}
+
+// Folds pending token counts so that game stats can be read out (mg_read).
+MG_GLOBAL void mg_fold_kernel(MgBatch b) {
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * MG_STEP_WARPS + (threadIdx.x >> 5);
+  if (env >= b.num_envs) return;
+  fold_token_stats_warp(b, env, lane);
+}
+
+// Agent::set_inventory (agent.cpp:54-72) for one agent; a test/tooling entry point of the reference API.
+MG_GLOBAL void mg_set_inventory_kernel(MgBatch b, int env, int ai, const int32_t* items, const int32_t* amounts, int n) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  EnvRec er = b.env[env];
+  AgentRec* agents = b.agents + (size_t)env * b.A;
+  EnvCtx e = make_ctx(b, env, agents, er);
+  InvView iv = agent_inv(e, ai);
+  int existing[16], ne = 0;
+  uint64_t o = agents[ai].order;
+  while ((o & 0xFull) != 0xFull && ne < 16) { existing[ne++] = (int)(o & 0xFull); o >>= 4; }
+  for (int i = 0; i < ne; i++) {
+    inv_update(e, iv, existing[i], -(int)agents[ai].amt[existing[i]], false, 0);
+    e.astats[(size_t)ai * e.S + MG_AS_AMOUNT + existing[i]] = 0.0f;
+  }
+  for (int i = 0; i < n; i++) inv_update(e, iv, items[i], amounts[i] - (int)agents[ai].amt[items[i]], false, 0);
+}
+
+#endif  // MG_KERNELS_CUH_

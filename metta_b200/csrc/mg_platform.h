@@ -1,0 +1,27 @@
+// mg_platform.h -- CUDA qualifiers and the handful of intrinsics the simulator uses.
+//
+// The product is compiled by nvcc for sm_100a only. Defining MG_SIMT_EMU swaps in
+// tests/simt_emu/simt_emu.h, a fiber-based SIMT emulator used by the CPU test-suite to execute
+// these same kernel sources without a GPU (debugging aid; it is never built into, loaded by or
+// reachable from the metta_b200 package).
+#ifndef MG_PLATFORM_H_
+#define MG_PLATFORM_H_
+
+#ifdef MG_SIMT_EMU
+#include "simt_emu.h"
+#else
+#include <cuda_runtime.h>
+#define MG_DEVICE __device__
+#define MG_GLOBAL __global__
+#define MG_NOINLINE __noinline__
+#define MG_SHARED __shared__
+#define MG_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#define MG_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define MG_FADD(a, b) __fadd_rn((a), (b))
+#define MG_FMUL(a, b) __fmul_rn((a), (b))
+#define MG_INT_AS_FLOAT(x) __int_as_float(x)
+#endif
+
+#define MG_FULL_MASK 0xFFFFFFFFu
+
+#endif  // MG_PLATFORM_H_

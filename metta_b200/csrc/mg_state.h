@@ -1,0 +1,128 @@
+// mg_state.h -- how a batch of environments lives in HBM.
+//
+// One record array per entity kind, indexed [env][instance]; records are small fixed-size
+// structs so that a warp loads an env's agents with a few 16-byte loads per lane, and the
+// observation kernel reaches any visible object with one or two sector reads.
+//
+// What the reference keeps per env -> where it lives here:
+//   Grid::grid (core/grid.hpp:23)                     -> grid[env][H*W] u16 (encoding below)
+//   Agent (objects/agent.hpp:23-79) + Inventory        -> AgentRec, 64 B
+//   Assembler (objects/assembler.hpp:239-279)          -> AsmRec, 32 B
+//   Chest (objects/chest.hpp) + Inventory              -> ChestRec, 48 B
+//   MettaGrid scalars (bindings/mettagrid_c.hpp:60-143)-> EnvRec, 64 B
+//   std::mt19937 _rng (+ the Clipper's private copy)   -> rng[env][624] u32
+//   StatsTracker maps (systems/stats_tracker.hpp)      -> dense float slots (mg_config.h MG_AS_*/MG_GS_*)
+#ifndef MG_STATE_H_
+#define MG_STATE_H_
+
+#include <stdint.h>
+
+#include "../../include/mg_config.h"
+
+// grid cell encoding (u16): 0 = empty, 1..0x3FFF = cell code of a static object (walls),
+// 0x4000|i agent i, 0x8000|i assembler instance i, 0xC000|i chest instance i.
+#define MG_GRID_KIND(v) ((v) >> 14)
+#define MG_GRID_INDEX(v) ((v) & 0x3FFF)
+#define MG_GK_STATIC 0
+#define MG_GK_AGENT 1
+#define MG_GK_ASM 2
+#define MG_GK_CHEST 3
+
+#define MG_ORDER_EMPTY 0xFFFFFFFFFFFFFFFFull /* inventory order list: 4-bit item ids, 0xF ends the list */
+
+struct alignas(16) AgentRec {
+  uint16_t r, c, prev_r, prev_c;
+  uint8_t vibe;
+  uint8_t group;  // index of the agent config (GROUPS section)
+  int16_t frozen;
+  uint32_t steps_without_motion;
+  uint64_t order;  // iteration order of the reference's unordered_map<item, amount>
+  uint16_t amt[MG_MAX_RESOURCES];
+  uint16_t pad0;
+  float current_stat_reward;
+  float episode_reward;
+  uint32_t pad1;
+};
+static_assert(sizeof(AgentRec) == 64, "AgentRec must be 64 bytes");
+
+#define MG_ASMF_CLIPPED 1
+#define MG_ASMF_TRACKED 2
+#define MG_ASMF_BORDER 4
+#define MG_ASMF_UNCLIPPED 8 /* member of Clipper::unclipped_assemblers */
+
+struct alignas(16) AsmRec {
+  uint16_t r, c;
+  uint8_t cell;   // cell code -> tags, type id, assembler type
+  uint8_t flags;  // MG_ASMF_*
+  int16_t unclip_protocol;  // protocol index while clipped, -1 none
+  uint32_t cooldown_end, cooldown_duration, uses_count;
+  uint32_t infection_weight;
+  int32_t cache_protocol;  // current protocol as seen by observers, valid when cache_step == current_step
+  uint32_t cache_step;
+};
+static_assert(sizeof(AsmRec) == 32, "AsmRec must be 32 bytes");
+
+struct alignas(16) ChestRec {
+  uint16_t r, c;
+  uint8_t cell;
+  uint8_t pad[3];
+  uint64_t order;
+  uint16_t amt[MG_MAX_RESOURCES];
+  uint16_t pad1[3];
+};
+static_assert(sizeof(ChestRec) == 48, "ChestRec must be 48 bytes");
+
+struct alignas(16) EnvRec {
+  uint32_t current_step;
+  uint32_t rng_idx;       // std::mt19937::_M_p
+  uint32_t clip_rng_idx;
+  uint32_t seed;
+  int32_t map_idx;
+  int32_t n_asm, n_chest;
+  int32_t clip_length_scale;
+  uint32_t early_reset_step;  // EarlyResetHandler (envs/early_reset_handler.py:12-20); 0 = none
+  uint32_t episodes;          // episodes completed so far
+  uint8_t done;               // bit 0: terminals set, bit 1: truncations set (for all agents of the env)
+  uint8_t pad[3];
+  uint32_t spare[5];
+};
+static_assert(sizeof(EnvRec) == 64, "EnvRec must be 64 bytes");
+
+// Everything a kernel needs, passed by value.
+struct MgBatch {
+  int32_t num_envs, A, H, W, T, R, S, GS, max_asm, max_chest, num_maps, has_clipper;
+  int32_t obs_cells;           // obs_h * obs_w
+  int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
+  int32_t auto_reset, map_stride;
+  const int32_t* cfg;          // lowered config
+  const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
+  // map pool
+  const uint16_t* pool_grid;   // [M][H*W]
+  const int32_t* pool_agents;  // [M][A][3]
+  const int32_t* pool_n_asm;   // [M]
+  const int32_t* pool_asm;     // [M][max_asm][3]
+  const int32_t* pool_n_chest; // [M]
+  const int32_t* pool_chest;   // [M][max_chest][3]
+  // state
+  EnvRec* env;
+  uint16_t* grid;              // [N][H*W]
+  AgentRec* agents;            // [N][A]
+  AsmRec* asms;                // [N][max_asm]
+  ChestRec* chests;            // [N][max_chest]
+  float* agent_stats;          // [N][A][S]
+  float* game_stats;           // [N][GS]
+  uint32_t* rng;               // [N][624]
+  uint32_t* clip_rng;          // [N][624] (only with a clipper)
+  uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
+  int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
+  uint8_t* action_success;     // [N][A]
+  double* episode_accum;       // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce)
+  // caller-owned buffers (set_buffers)
+  uint8_t* obs;                // [N*A][T][3]
+  uint8_t* terminals;          // [N*A]
+  uint8_t* truncations;        // [N*A]
+  float* rewards;              // [N*A]
+  const int32_t* actions;      // [N*A]
+};
+
+#endif  // MG_STATE_H_

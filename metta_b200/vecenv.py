@@ -1,0 +1,194 @@
+"""GpuMettaGridVecEnv: thousands of MettaGrid envs on one B200 behind the reference's env API.
+
+What it stands in for:
+  * pufferlib's vec-env contract (packages/pufferlib-core/src/pufferlib/vector.py:121-183):
+    ``async_reset / recv / send / close``, ``num_agents``, ``single_observation_space``,
+    ``single_action_space``, ``driver_env``;
+  * MettaGridPufferEnv's step semantics (mettagrid/envs/mettagrid_puffer_env.py:149-183):
+    shared buffers, auto-reset at the start of the step after an episode ended, same seed;
+  * metta/rl's TrainingEnvironment (metta/rl/training/training_environment.py:85-119,253-275):
+    ``get_observations / send_actions``, with a contiguous env slice.
+
+State stays in HBM; observations, rewards, terminals and truncations are torch CUDA tensors that
+the kernels write in place, so a policy can read them without a host round trip. ``host=True``
+gives numpy arrays instead (the drop-in path for code that expects the reference's arrays).
+There is no CPU implementation: without the CUDA library or a GPU, construction raises.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Optional, Sequence
+
+import numpy as np
+
+from .batch import Batch
+from .config import MettaGridConfig
+from .layout import L
+from .lowering import LoweredConfig, lower_game_config
+from .maps import MapPool, build_pool, names_to_codes
+from .stats import agent_stat_names, game_stat_names
+
+
+@dataclass
+class Box:  # gymnasium.spaces.Box stand-in (gymnasium is not a dependency)
+    low: int
+    high: int
+    shape: tuple
+    dtype: Any
+
+
+@dataclass
+class Discrete:
+    n: int
+    dtype: Any = np.int32
+
+
+class GpuMettaGridVecEnv:
+    def __init__(
+        self,
+        cfg: MettaGridConfig | Any,
+        num_envs: int,
+        maps: Optional[Sequence] = None,
+        map_codes: Optional[np.ndarray] = None,
+        seed: int = 0,
+        device: int | str = 0,
+        host: bool = False,
+        map_stride: int = 0,
+    ):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise RuntimeError("GpuMettaGridVecEnv needs a CUDA device; there is no CPU simulator in this package")
+        self.cfg = MettaGridConfig.from_reference(cfg)
+        game = self.cfg.game
+        if map_codes is None:
+            if maps is None:
+                raise ValueError("pass `maps` (cell-name grids, as the reference's map builders produce) or `map_codes`")
+            first = np.asarray(maps[0])
+            lowered = lower_game_config(game, first.shape[0], first.shape[1])
+            map_codes = np.stack([names_to_codes(lowered, m) for m in maps])
+        else:
+            map_codes = np.asarray(map_codes, dtype=np.uint8)
+            lowered = lower_game_config(game, map_codes.shape[1], map_codes.shape[2])
+        self.lowered: LoweredConfig = lowered
+        self.pool: MapPool = build_pool(lowered, map_codes)
+        self.num_envs = int(num_envs)
+        self.agents_per_env = game.num_agents
+        self.num_agents = self.num_envs * self.agents_per_env
+        dev = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.device = dev
+        self._torch = torch
+        self.batch = Batch(lowered, self.pool, self.num_envs, device=dev.index or 0)
+        self.batch.set_options(auto_reset=True, map_stride=map_stride)
+        T = game.obs.num_tokens
+        self.single_observation_space = Box(0, 255, (T, 3), np.uint8)
+        self.single_action_space = Discrete(len(lowered.action_names))
+        self.action_names = list(lowered.action_names)
+        self.host = host
+        NA = self.num_agents
+        self.observations = torch.full((NA, T, 3), 255, dtype=torch.uint8, device=dev)
+        self.rewards = torch.zeros(NA, dtype=torch.float32, device=dev)
+        self.terminals = torch.zeros(NA, dtype=torch.bool, device=dev)
+        self.truncations = torch.zeros(NA, dtype=torch.bool, device=dev)
+        self.actions = torch.zeros(NA, dtype=torch.int32, device=dev)
+        self.teacher_actions = torch.zeros(NA, dtype=torch.int32, device=dev)
+        self.masks = torch.ones(NA, dtype=torch.bool, device=dev)
+        self.agent_ids = np.arange(NA)
+        self.batch.set_buffers(
+            self.observations.data_ptr(), self.terminals.data_ptr(), self.truncations.data_ptr(),
+            self.rewards.data_ptr(), self.actions.data_ptr(),
+        )
+        if host:
+            self._h_obs = np.full((NA, T, 3), 255, dtype=np.uint8)
+            self._h_rew = np.zeros(NA, dtype=np.float32)
+            self._h_term = np.zeros(NA, dtype=np.bool_)
+            self._h_trunc = np.zeros(NA, dtype=np.bool_)
+        self._seed = seed
+        self._episodes_reported = 0.0
+        self._accum_prev: Optional[np.ndarray] = None
+        self.driver_env = self
+
+    # ---- pufferlib contract
+    def async_reset(self, seed: Optional[int] = None) -> None:
+        if seed is not None:
+            self._seed = seed
+        seeds = (np.arange(self.num_envs, dtype=np.int64) + int(self._seed)) & 0xFFFFFFFF
+        maps = np.arange(self.num_envs) % len(self.pool.codes)
+        self.batch.reset(seeds.astype(np.uint32), maps.astype(np.int32))
+        self._accum_prev = None
+        if self.host:
+            self._download()
+
+    def reset(self, seed: Optional[int] = None):
+        self.async_reset(seed)
+        return self.recv()[0], {}
+
+    def send(self, actions) -> None:
+        torch = self._torch
+        if self.host:
+            a = np.ascontiguousarray(np.asarray(actions).reshape(-1), dtype=np.int32)
+            self.batch.step_host(a, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
+            return
+        if isinstance(actions, np.ndarray):
+            actions = torch.from_numpy(np.ascontiguousarray(actions.reshape(-1), dtype=np.int32))
+        self.actions.copy_(actions.reshape(-1).to(torch.int32), non_blocking=True)
+        self.batch.step(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def recv(self):
+        infos = self._infos()
+        if self.host:
+            return (self._h_obs, self._h_rew, self._h_term, self._h_trunc, None, infos, self.agent_ids, None)
+        return (self.observations, self.rewards, self.terminals, self.truncations, self.teacher_actions, infos,
+                self.agent_ids, self.masks)
+
+    def step(self, actions):
+        self.send(actions)
+        o, r, d, t, _, infos, _, _ = self.recv()
+        return o, r, d, t, infos
+
+    def close(self) -> None:
+        self.batch.close()
+
+    # ---- metta/rl TrainingEnvironment surface
+    def get_observations(self):
+        o, r, d, t, ta, infos, ids, mask = self.recv()
+        return o, r, d, t, ta, infos, slice(0, self.num_agents), mask, self.num_agents
+
+    def send_actions(self, actions) -> None:
+        self.send(actions)
+
+    # ---- helpers
+    def _download(self) -> None:
+        self._h_obs[...] = self.observations.cpu().numpy()
+        self._h_rew[...] = self.rewards.cpu().numpy()
+        self._h_term[...] = self.terminals.cpu().numpy()
+        self._h_trunc[...] = self.truncations.cpu().numpy()
+
+    def episode_stats(self) -> dict[str, float]:
+        """Sums over all episodes finished on this GPU since construction (a dense vector that
+        ``reduce_episode_stats`` all-reduces across ranks)."""
+        acc = self.batch.read_episode_accum()
+        names_a = agent_stat_names(self.lowered, 0)
+        names_g = game_stat_names(self.lowered)
+        out = {"episodes": float(acc[0]), "episode_reward_sum": float(acc[1])}
+        S = L.MG_AS_COUNT
+        for s in np.nonzero(acc[2 : 2 + S])[0]:
+            for n in names_a.get(int(s), []):
+                out["agent/" + n] = float(acc[2 + s])
+        for s in np.nonzero(acc[2 + S :])[0]:
+            if int(s) in names_g:
+                out["game/" + names_g[int(s)]] = float(acc[2 + S + s])
+        return out
+
+    def _infos(self) -> list[dict]:
+        return []
+
+    def reduce_episode_stats(self):
+        """All-reduce (SUM) the episode accumulators over the process group: the only collective of
+        the env path. Returns a float64 tensor on this rank's GPU."""
+        torch = self._torch
+        acc = torch.from_numpy(self.batch.read_episode_accum()).to(self.device)
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.all_reduce(acc, op=torch.distributed.ReduceOp.SUM)
+        return acc

@@ -1,0 +1,99 @@
+"""Generates tests/golden/*.npz + *.json by RUNNING THE REFERENCE in the build container.
+
+Needs /root/reference (Python package) and oracle/_ref (compiled core). Run:
+    python tests/golden/make_golden.py
+Each fixture holds the config (reference schema, JSON), the map (cell names), the env seed, the
+action sequence and everything the reference produced: observations (initial + every step),
+rewards, terminals, truncations, action_success, episode rewards and the final inventories in
+the reference's own iteration order (grid_objects()[id]["inventory"]).
+The arena fixture is produced through the reference's OWN Python lowering
+(mettagrid_c_config.convert_to_cpp_game_config) and map builder; the others through
+oracle/ref_bridge.py, which tests/test_oracle_vs_reference.py checks against that lowering.
+"""
+
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from oracle.ref_loader import load_reference_python  # noqa: E402
+
+load_reference_python()
+
+from harness import random_actions  # noqa: E402
+from scenarios import SCENARIOS  # noqa: E402
+
+from metta_b200.config import MettaGridConfig  # noqa: E402
+from metta_b200.lowering import lower_game_config  # noqa: E402
+from oracle.ref_bridge import RefEnv  # noqa: E402
+
+
+def run(name, cfg, grid, seed, steps, c_cfg=None, restarts=False, invalid_every=0):
+    lowered = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    env = RefEnv(cfg.game, grid.tolist(), seed, c_cfg=c_cfg)
+    A = cfg.game.num_agents
+    rng = np.random.RandomState(seed + 1000)
+    obs = [env.observations.copy()]
+    rew, term, trunc, succ, acts, eprew = [], [], [], [], [], []
+    for s in range(steps):
+        if restarts and (env.terminals.all() or env.truncations.all()):
+            env = RefEnv(cfg.game, grid.tolist(), seed, c_cfg=c_cfg)  # mettagrid_puffer_env.py:158-164
+        a = random_actions(rng, cfg, lowered, A, invalid_every=invalid_every, step=s)
+        env.step(a)
+        acts.append(a)
+        obs.append(env.observations.copy())
+        rew.append(env.rewards.copy())
+        term.append(env.terminals.copy())
+        trunc.append(env.truncations.copy())
+        succ.append(env.action_success())
+        eprew.append(env.episode_rewards().copy())
+    objs = env.grid_objects()
+    inv_items = np.full((A, 16), -1, np.int32)
+    inv_amounts = np.zeros((A, 16), np.int32)
+    pos = np.zeros((A, 2), np.int32)
+    for o in objs.values():
+        if "agent_id" in o:
+            k = o["agent_id"]
+            pos[k] = (o["r"], o["c"])
+            for j, (item, amount) in enumerate(o["inventory"].items()):
+                inv_items[k, j] = item
+                inv_amounts[k, j] = amount
+    np.savez_compressed(
+        os.path.join(HERE, name + ".npz"),
+        grid=grid, seed=np.int64(seed), actions=np.array(acts, np.int32), obs=np.array(obs, np.uint8),
+        rewards=np.array(rew, np.float32), terminals=np.array(term), truncations=np.array(trunc),
+        success=np.array(succ), episode_rewards=np.array(eprew, np.float32),
+        final_pos=pos, final_inv_items=inv_items, final_inv_amounts=inv_amounts, restarts=np.bool_(restarts),
+    )
+    with open(os.path.join(HERE, name + ".json"), "w") as f:
+        json.dump(cfg.model_dump(), f, indent=1, sort_keys=False, default=str)
+    print(name, "steps", steps, "obs", np.array(obs).shape, "nonzero rewards", int((np.array(rew) != 0).sum()))
+
+
+def main():
+    # arena: the reference's own config, lowering and map builder
+    from mettagrid.builder.envs import make_arena
+    from mettagrid.config.mettagrid_c_config import convert_to_cpp_game_config
+
+    ref_cfg = make_arena(24)
+    ref_cfg.game.map_builder.seed = 1000
+    grid = ref_cfg.game.map_builder.create().build_for_num_agents(24).grid
+    c_cfg = convert_to_cpp_game_config(ref_cfg.game.model_dump())
+    dump = ref_cfg.model_dump()
+    dump["game"]["map_builder"] = None  # map builders are out of scope; the grid is stored instead
+    cfg = MettaGridConfig.from_reference(dump)
+    run("arena", cfg, grid, 42, 120, c_cfg=c_cfg)
+
+    for name, steps, restarts, inv in (("kitchen_sink", 250, False, 40), ("tiny_truncating", 23, True, 0), ("clipped_start", 150, False, 0)):
+        cfg, grid = SCENARIOS[name]()
+        run(name, cfg, grid, 7, steps, restarts=restarts, invalid_every=inv)
+
+
+if __name__ == "__main__":
+    main()

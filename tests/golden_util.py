@@ -1,0 +1,16 @@
+import json
+import os
+
+import numpy as np
+
+from metta_b200.config import MettaGridConfig
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+NAMES = ["arena", "kitchen_sink", "tiny_truncating", "clipped_start"]
+
+
+def load(name: str):
+    with open(os.path.join(GOLDEN, name + ".json")) as f:
+        cfg = MettaGridConfig.from_reference(json.load(f))
+    data = np.load(os.path.join(GOLDEN, name + ".npz"))
+    return cfg, data["grid"], data
