@@ -1,0 +1,98 @@
+/* mettagrid_b200.h -- C-ABI of libmettagrid_b200.so: a batched MettaGrid simulator for B200.
+ *
+ * This is the boundary a maintainer of the reference binds instead of the pybind11 class
+ * `MettaGrid` (packages/mettagrid/cpp/bindings/mettagrid_c.cpp:1007-1041). One handle holds N
+ * environments of one lowered game config (include/mg_config.h) on one GPU. All entry points
+ * return 0 on success; otherwise mg_last_error() holds the message (the reference throws
+ * std::runtime_error at the same places, mettagrid_c.cpp:65-70,191-193,680-719,743-749).
+ * Pointers named *_dev are device memory owned by the caller; *_host are host memory.
+ * Not thread-safe per handle, like the reference core (SURVEY.md 8b "threading").
+ */
+#ifndef METTAGRID_B200_H_
+#define METTAGRID_B200_H_
+
+#include <stdint.h>
+
+#include "mg_config.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* mg_last_error(void);
+int mg_abi_version(void); /* == MG_CONFIG_VERSION */
+
+/* Host helpers used while lowering a config: iteration order of the libstdc++ unordered_map the
+ * reference would hold for these keys (replaces nothing in the reference: it *is* the reference's
+ * container, see metta_b200/csrc/mg_host_order.cpp; pybind11/stl.h map_caster::load reserves first). */
+int mg_umap_order_u8(const uint8_t* keys, int n, int reserve_first, int32_t* out_positions);
+int mg_umap_order_str(const char* keys_nul_separated, int n, int reserve_first, int32_t* out_positions);
+
+/* MettaGrid::MettaGrid(GameConfig, map, seed) (mettagrid_c.cpp:46-155), for num_envs environments.
+ * config: lowered blob; maps and seeds are supplied by mg_load_maps / mg_reset. */
+int mg_create(const int32_t* config_words, int64_t n_words, int32_t num_envs, int32_t device, void** out_handle);
+void mg_destroy(void* handle);
+
+/* The `map` constructor argument (list[list[str]], mettagrid_c.cpp:159-245), as a pool of maps
+ * pre-split per object kind (metta_b200/maps.py build_pool); kept in HBM for auto-reset
+ * (replaces SharedMapCache, mettagrid/simulator/map_cache.py). */
+int mg_load_maps(void* handle, int32_t num_maps, const uint16_t* grids_host, const int32_t* agents_host,
+                 const int32_t* n_assemblers_host, const int32_t* assemblers_host, const int32_t* n_chests_host,
+                 const int32_t* chests_host);
+
+/* MettaGrid::set_buffers (mettagrid_c.cpp:721-738): bind caller-owned buffers for all N*A agents:
+ * observations u8[N*A][T][3], terminals u8[N*A], truncations u8[N*A], rewards f32[N*A],
+ * actions i32[N*A]. All NULL = let the library own them (for mg_step_host). */
+int mg_set_buffers(void* handle, void* obs_dev, void* terminals_dev, void* truncations_dev, void* rewards_dev,
+                   void* actions_dev);
+
+/* New episodes: the constructor's seed argument and map choice per env, then the initial
+ * observation of _init_buffers (mettagrid_c.cpp:264-289). mask_host may be NULL (= all envs). */
+int mg_reset(void* handle, const uint32_t* seeds_host, const int32_t* map_index_host, const uint8_t* mask_host);
+
+/* MettaGrid::step (mettagrid_c.cpp:572-678,740-752) for every env, including the auto-reset of
+ * MettaGridPufferEnv.step (mettagrid/envs/mettagrid_puffer_env.py:158-164). Asynchronous on
+ * `cuda_stream` (a cudaStream_t, may be NULL). */
+int mg_step(void* handle, void* cuda_stream);
+
+/* The same step for callers holding host (numpy) buffers, as MettaGridPufferEnv.step does:
+ * copies actions in and observations/rewards/terminals/truncations out, then returns. */
+int mg_step_host(void* handle, const int32_t* actions_host, uint8_t* obs_host, float* rewards_host,
+                 uint8_t* terminals_host, uint8_t* truncations_host);
+
+/* One synchronous step with CUDA events around each kernel (no counterpart in the reference; the
+ * reference times its step with a host Stopwatch, mettagrid/simulator/simulator.py:138-160).
+ * out_ms_host[0] = action kernel, out_ms_host[1] = observation kernel, in milliseconds. */
+int mg_profile_step(void* handle, void* cuda_stream, float* out_ms_host);
+
+/* MettaGrid::_compute_observations (mettagrid_c.cpp:557-563) alone. */
+int mg_compute_observations(void* handle, void* cuda_stream);
+
+/* auto_reset: 1 = MettaGridPufferEnv semantics (default), 0 = bare MettaGrid. map_stride: which pool
+ * map an env moves to on auto-reset ((index + stride) mod pool size). */
+int mg_set_options(void* handle, int32_t auto_reset, int32_t map_stride);
+
+/* EarlyResetHandler (mettagrid/envs/early_reset_handler.py:12-20): truncate env i's running episode
+ * once current_step >= steps[i] (0 = never). */
+int mg_set_early_reset(void* handle, const uint32_t* steps_host);
+
+/* State access for the conformance harness and for infos: the counterpart of grid_objects(),
+ * get_episode_stats(), get_episode_rewards(), action_success() (mettagrid_c.cpp:754-957).
+ * `what` selects a raw array (record layouts: metta_b200/csrc/mg_state.h):
+ * 0 env scalars, 1 grid, 2 agents, 3 assemblers, 4 chests, 5 agent stats, 6 game stats,
+ * 7 last executed action, 8 action success, 9 finished-episode accumulators, 10 rng state,
+ * 11 observations, 12 rewards, 13 terminals, 14 truncations, 15 actions. */
+int64_t mg_sizeof(void* handle, int32_t what);
+int mg_read(void* handle, int32_t what, void* out_host, int64_t nbytes);
+int mg_write(void* handle, int32_t what, const void* in_host, int64_t nbytes);
+
+/* MettaGrid::set_inventory (mettagrid_c.cpp:959-965): items_amounts = n item ids followed by n amounts. */
+int mg_set_inventory(void* handle, int32_t env, int32_t agent, const int32_t* items_amounts_host, int32_t n);
+
+int64_t mg_kernel_launches(void* handle); /* kernels launched through this handle so far */
+int mg_sync(void* handle);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* METTAGRID_B200_H_ */

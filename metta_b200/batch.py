@@ -155,6 +155,11 @@ class Batch:
             )
         )
 
+    def profile_step(self, stream: int = 0) -> tuple[float, float]:
+        ms = np.zeros(2, dtype=np.float32)
+        self._check(self._c.mg_profile_step(self._h, stream, ms.ctypes.data))
+        return float(ms[0]), float(ms[1])
+
     def compute_observations(self, stream: int = 0) -> None:
         self._check(self._c.mg_compute_observations(self._h, stream))
 

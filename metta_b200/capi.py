@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmettagrid_b200.so")
 # every symbol include/mettagrid_b200.h declares
 SYMBOLS = [
     "mg_last_error", "mg_abi_version", "mg_umap_order_u8", "mg_umap_order_str", "mg_create", "mg_destroy",
-    "mg_load_maps", "mg_set_buffers", "mg_reset", "mg_step", "mg_step_host", "mg_compute_observations",
+    "mg_load_maps", "mg_set_buffers", "mg_reset", "mg_step", "mg_step_host", "mg_profile_step", "mg_compute_observations",
     "mg_set_options", "mg_set_early_reset", "mg_sizeof", "mg_read", "mg_write", "mg_set_inventory",
     "mg_kernel_launches", "mg_sync",
 ]  # fmt: skip
@@ -49,6 +49,8 @@ def _declare(l: ctypes.CDLL) -> ctypes.CDLL:
     l.mg_step.restype = c_int
     l.mg_step_host.argtypes = [c_void_p] * 6
     l.mg_step_host.restype = c_int
+    l.mg_profile_step.argtypes = [c_void_p, c_void_p, c_void_p]
+    l.mg_profile_step.restype = c_int
     l.mg_compute_observations.argtypes = [c_void_p, c_void_p]
     l.mg_compute_observations.restype = c_int
     l.mg_set_options.argtypes = [c_void_p, c_int32, c_int32]

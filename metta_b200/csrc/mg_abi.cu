@@ -293,6 +293,31 @@ int mg_step(void* h, void* stream) {
   return launch_obs(e, s, nullptr);
 }
 
+// One synchronous step with CUDA events around each kernel, for roofline measurements:
+// out_ms[0] = action/step kernel, out_ms[1] = observation kernel (milliseconds).
+int mg_profile_step(void* h, void* stream, float* out_ms) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !out_ms) return fail(MG_ERR_ARG, "mg_profile_step: bad arguments");
+  if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_profile_step: maps or buffers missing");
+  MgBatch& b = e->b;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaEvent_t ev[3];
+  for (int i = 0; i < 3; i++) CUDA_TRY(cudaEventCreate(&ev[i]));
+  const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
+  CUDA_TRY(cudaEventRecord(ev[0], s));
+  MG_LAUNCH(mg_step_kernel, grid, MG_STEP_WARPS * 32, 0, s, b);
+  e->launches++;
+  CUDA_TRY(cudaEventRecord(ev[1], s));
+  int rc;
+  TRY(launch_obs(e, s, nullptr));
+  CUDA_TRY(cudaEventRecord(ev[2], s));
+  CUDA_TRY(cudaEventSynchronize(ev[2]));
+  CUDA_TRY(cudaEventElapsedTime(&out_ms[0], ev[0], ev[1]));
+  CUDA_TRY(cudaEventElapsedTime(&out_ms[1], ev[1], ev[2]));
+  for (int i = 0; i < 3; i++) cudaEventDestroy(ev[i]);
+  return MG_OK;
+}
+
 // Recompute observations only (debugging / after mg_write).
 int mg_compute_observations(void* h, void* stream) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);

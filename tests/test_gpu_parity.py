@@ -1,0 +1,165 @@
+"""GPU parity: the compiled sm_100a kernels, called through the C-ABI, against the oracle, the
+reference-generated fixtures and (where the compiled reference travelled) the reference itself.
+Bit-exact on every observation byte, reward, flag, inventory and stat."""
+
+import numpy as np
+import pytest
+from golden_util import NAMES, load
+from harness import HostBuffers, Lockstep, random_actions
+from scenarios import SCENARIOS
+
+from metta_b200.builders import make_arena
+from metta_b200.batch import Batch, order_list
+from metta_b200.layout import L
+from metta_b200.lowering import lower_game_config
+from metta_b200.maps import arena_maps, build_pool, names_to_codes
+from oracle import ref_loader
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib(product_lib):
+    import torch
+
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return product_lib
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_cuda_reproduces_reference_fixture(name, lib):
+    cfg, grid, d = load(name)
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    pool = build_pool(low, names_to_codes(low, grid))
+    A, T = cfg.game.num_agents, cfg.game.obs.num_tokens
+    b = Batch(low, pool, 1)
+    b.set_options(auto_reset=bool(d["restarts"]))
+    buf = HostBuffers(A, T, cuda=True)
+    b.set_buffers(*buf.ptrs)
+    b.reset(np.array([int(d["seed"])], np.uint32), np.array([0], np.int32))
+    obs, rew, term, trunc = buf.fetch()
+    assert np.array_equal(obs, d["obs"][0]), "initial observation"
+    for s, a in enumerate(d["actions"]):
+        buf.set_actions(a)
+        b.step()
+        obs, rew, term, trunc = buf.fetch()
+        assert np.array_equal(obs, d["obs"][s + 1]), f"{name}: observation at step {s}"
+        assert np.array_equal(rew, d["rewards"][s]), f"{name}: rewards at step {s}"
+        assert np.array_equal(term.astype(bool), d["terminals"][s]) and np.array_equal(trunc.astype(bool), d["truncations"][s])
+        assert np.array_equal(b.read_action_success()[0], d["success"][s]), f"{name}: success at step {s}"
+        assert np.array_equal(b.read_episode_rewards()[0], d["episode_rewards"][s])
+    ag = b.read_agents()[0]
+    assert np.array_equal(np.stack([ag["r"], ag["c"]], 1), d["final_pos"])
+    for k in range(A):
+        items = [int(x) for x in d["final_inv_items"][k] if x >= 0]
+        assert order_list(ag["order"][k]) == items
+        assert [int(ag["amt"][k][i]) for i in items] == [int(x) for x in d["final_inv_amounts"][k][: len(items)]]
+    b.close()
+
+
+@pytest.mark.parametrize("name,steps", [("kitchen_sink", 400), ("tiny_truncating", 40), ("clipped_start", 200)])
+def test_scenarios_vs_oracle(name, steps, lib):
+    cfg, grid = SCENARIOS[name]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    n = 33  # not a multiple of the warps per CTA: exercises the ragged last CTA
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=n, seeds=np.arange(n) + 100, cuda=True)
+    ls.compare_outputs()
+    rng = np.random.RandomState(5)
+    for s in range(steps):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=31, step=s))
+        if name != "tiny_truncating" and s % 100 == 99:
+            ls.compare_state()
+    ls.close()
+
+
+def test_arena_vs_oracle_with_state(lib):
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 64
+    ls = Lockstep(cfg, arena_maps(low, 16, seed=1), num_envs=n, seeds=np.arange(n) + 42, cuda=True)
+    ls.compare_outputs()
+    rng = np.random.RandomState(0)
+    for s in range(300):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.compare_state()
+    ls.close()
+
+
+def test_arena_auto_reset_and_map_rotation(lib):
+    """Episodes end by truncation every 20 steps; envs restart from their pool map with the same seed."""
+    cfg = make_arena(24, max_steps=20)
+    cfg.game.episode_truncates = True
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 8
+    ls = Lockstep(cfg, arena_maps(low, 4, seed=2), num_envs=n, seeds=np.arange(n) + 7, cuda=True)
+    rng = np.random.RandomState(3)
+    for s in range(65):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    env = ls.batch.read_env()
+    assert np.all(env["episodes"] == 3) and np.all(env["current_step"] == 5)
+    acc = ls.batch.read_episode_accum()
+    assert acc[0] == 3 * n
+    ls.close()
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="compiled reference (oracle/_ref) not present")
+def test_arena_vs_compiled_reference(lib):
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 6
+    ls = Lockstep(cfg, arena_maps(low, n, seed=11), num_envs=n, seeds=np.arange(n) + 1, cuda=True, checker="reference")
+    ls.compare_outputs()
+    rng = np.random.RandomState(4)
+    for s in range(200):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.close()
+
+
+def test_full_size_properties(lib):
+    """BASELINE config 2 (4096 envs x 24 agents): size-independent checks plus a sampled lockstep."""
+    import torch
+
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n, A, T = 4096, 24, 200
+    codes = arena_maps(low, 256, seed=0)
+    pool = build_pool(low, codes)
+    b = Batch(low, pool, n)
+    buf = HostBuffers(n * A, T, cuda=True)
+    b.set_buffers(*buf.ptrs)
+    seeds = (np.arange(n) + 42).astype(np.uint32)
+    maps = (np.arange(n) % 256).astype(np.int32)
+    b.reset(seeds, maps)
+    from oracle.oracle import OracleEnv
+
+    sample = [0, 1, 255, 256, 2047, 4095]
+    orcs = {i: OracleEnv(low.words, codes[maps[i]], int(seeds[i])) for i in sample}
+    g = torch.Generator().manual_seed(0)
+    for s in range(60):
+        a = torch.randint(0, 5, (n * A,), generator=g, dtype=torch.int32)
+        buf.t_act.copy_(a)
+        b.step()
+        an = a.numpy().reshape(n, A)
+        for i, o in orcs.items():
+            o.step(an[i])
+    obs, rew, term, trunc = buf.fetch()
+    for i, o in orcs.items():
+        assert np.array_equal(obs[i * A : (i + 1) * A], o.observations), f"env {i}"
+        assert np.array_equal(rew[i * A : (i + 1) * A], o.rewards)
+    # properties over all 98304 agents
+    grid = b.read_grid()
+    ag = b.read_agents()
+    kinds = grid >> 14
+    assert np.all((kinds == 1).sum(axis=(1, 2)) == A), "every env still has exactly A agents on its grid"
+    e = np.repeat(np.arange(n), A)
+    k = np.tile(np.arange(A), n)
+    assert np.array_equal(grid[e, ag["r"].reshape(-1), ag["c"].reshape(-1)], (0x4000 | k).astype(np.uint16)), "cell<->agent consistency"
+    o3 = obs.reshape(n * A, T, 3)
+    empty = (o3 == 255).all(axis=2)
+    assert np.all(np.diff(empty.astype(np.int8), axis=1) >= 0), "written tokens form a prefix, the rest is 0xFF"
+    assert np.all(o3[:, 0, 0] == 0x55) and np.all(o3[:, 0, 1] == low.feature_ids["episode_completion_pct"])
+    # same (map, seed, actions) => same result: env i and env i+256 share a map; re-run env 0's twin
+    gs = b.read_game_stats()
+    written = (~empty).sum(axis=1).reshape(n, A).sum(axis=1)
+    assert np.all(gs[:, L.MG_GS_TOKENS_WRITTEN] > 0) and written.min() > 0
+    b.close()
