@@ -11,7 +11,8 @@ import os
 from ctypes import POINTER, c_char_p, c_int, c_int32, c_int64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libmettagrid_b200.so")
+# MG_LIB_PATH selects another nvcc build of the same library (tuning experiments); there is no non-CUDA build.
+LIB_PATH = os.environ.get("MG_LIB_PATH") or os.path.join(_HERE, "csrc", "libmettagrid_b200.so")
 
 # every symbol include/mettagrid_b200.h declares
 SYMBOLS = [

@@ -25,13 +25,13 @@ def stale() -> bool:
     return any(os.path.getmtime(os.path.join(HERE, d)) > t for d in DEPS)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not stale():
+def build(force: bool = False, verbose: bool = False, out: str = OUT, extra: list[str] | None = None) -> str:
+    if out == OUT and not force and not stale():
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SOURCES
+    cmd = [nvcc] + FLAGS + (extra or []) + (["-Xptxas", "-v"] if verbose else []) + ["-o", out] + SOURCES
     subprocess.check_call(cmd, cwd=HERE)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

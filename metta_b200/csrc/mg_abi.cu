@@ -144,6 +144,60 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &b.game_stats, N * (size_t)b.GS));
   TRY(dev_alloc(e, &b.rng, N * MT_N));
   if (b.has_clipper) TRY(dev_alloc(e, &b.clip_rng, N * MT_N));
+  {
+    // static token templates (see mg_obs.cuh): cells, then protocols, then agent groups
+    std::vector<uint16_t> tok;
+    std::vector<uint32_t> ix;
+    auto tk = [](int feature, int value) { return (uint16_t)((feature & 0xFF) | ((value & 0xFF) << 8)); };
+    const int ncell = cfg[MGC_NUM_CELLTYPES], nproto = cfg[MGC_NUM_PROTOCOLS], ngroup = cfg[MGC_NUM_GROUPS];
+    int max_tags = 0;
+    for (int c = 0; c < ncell; c++) {
+      const int32_t* cc = cfg + cfg[MGC_OFF_CELLTYPES] + c * MG_CELL_WORDS;
+      const size_t off = tok.size();
+      if (c > 0 && cc[MG_CELL_KIND] != MG_KIND_AGENT) {
+        for (int i = 0; i < cc[MG_CELL_NUM_TAGS]; i++) tok.push_back(tk(cfg[MGC_FEAT_TAG], cc[MG_CELL_TAGS + i]));
+        // walls and assemblers end with their vibe (wall.hpp:26-38, assembler.hpp:570-575); a chest's vibe comes first
+        if (cc[MG_CELL_KIND] != MG_KIND_CHEST && cc[MG_CELL_VIBE] != 0) tok.push_back(tk(cfg[MGC_FEAT_VIBE], cc[MG_CELL_VIBE]));
+        if (cc[MG_CELL_NUM_TAGS] > max_tags) max_tags = cc[MG_CELL_NUM_TAGS];
+      }
+      ix.push_back((uint32_t)(off << 8) | (uint32_t)(tok.size() - off));
+    }
+    b.ix_proto = (int32_t)ix.size();
+    const int32_t* pf = cfg + cfg[MGC_OFF_PROTO_FEATURES];
+    for (int p = 0; p < nproto; p++) {  // assembler.hpp:553-564: inputs then outputs with amount > 0
+      const int32_t* pc = cfg + cfg[MGC_OFF_PROTOCOLS] + p * MG_PROTO_WORDS;
+      const size_t off = tok.size();
+      const int32_t* l = pc + MG_PROTO_INPUTS;
+      for (int i = 0; i < l[MG_LIST_N]; i++)
+        if (l[MG_LIST_VAL(i)] > 0) tok.push_back(tk(pf[l[MG_LIST_ITEM(i)]], l[MG_LIST_VAL(i)]));
+      l = pc + MG_PROTO_OUTPUTS;
+      for (int i = 0; i < l[MG_LIST_N]; i++)
+        if (l[MG_LIST_VAL(i)] > 0) tok.push_back(tk(pf[MG_RES_STRIDE + l[MG_LIST_ITEM(i)]], l[MG_LIST_VAL(i)]));
+      ix.push_back((uint32_t)(off << 8) | (uint32_t)(tok.size() - off));
+    }
+    b.ix_group = (int32_t)ix.size();
+    for (int g = 0; g < ngroup; g++) {
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + g * MG_GRP_WORDS;
+      const size_t off = tok.size();
+      for (int i = 0; i < grp[MG_GRP_NUM_TAGS]; i++) tok.push_back(tk(cfg[MGC_FEAT_TAG], grp[MG_GRP_TAGS + i]));
+      if (grp[MG_GRP_NUM_TAGS] > max_tags) max_tags = grp[MG_GRP_NUM_TAGS];
+      ix.push_back((uint32_t)(off << 8) | (uint32_t)(tok.size() - off));
+    }
+    tok.resize(tok.size() + 8, 0);
+    uint16_t* d_tok; uint32_t* d_ix;
+    TRY(dev_alloc(e, &d_tok, tok.size()));
+    TRY(dev_alloc(e, &d_ix, ix.size()));
+    CUDA_TRY(cudaMemcpy(d_tok, tok.data(), tok.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(d_ix, ix.data(), ix.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    b.tmpl_tok = d_tok; b.tmpl_ix = d_ix;
+    // per-entity token records: count byte + pad + the most tokens an agent / chest can show
+    const int max_entity_tokens = 3 + b.R * cfg[MGC_NUM_INV_TOKENS] + max_tags;
+    if (max_entity_tokens > 255) return fail(MG_ERR_ARG, "mg_create: an object could show more than 255 tokens");
+    b.atok_stride = (2 + 2 * max_entity_tokens + 15) & ~15;
+    b.ctok_stride = b.atok_stride;
+    TRY(dev_alloc(e, &b.agent_tok, N * A * (size_t)b.atok_stride));
+    TRY(dev_alloc(e, &b.chest_tok, N * (size_t)b.max_chest * (size_t)b.ctok_stride));
+  }
   TRY(dev_alloc(e, &b.tok_counts, N * A * 2));
   TRY(dev_alloc(e, &b.last_action, N * A));
   TRY(dev_alloc(e, &b.action_success, N * A));
@@ -236,7 +290,12 @@ static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
   const long long agents = (long long)b.num_envs * b.A;
   const int grid = (int)((agents + MG_OBS_WARPS - 1) / MG_OBS_WARPS);
   const int slot = (b.T * 3 + 16 + 15) & ~15;
-  MG_LAUNCH(mg_obs_kernel, grid, MG_OBS_WARPS * 32, (size_t)slot * MG_OBS_WARPS, s, b, mask);
+  const size_t smem = (size_t)slot * MG_OBS_WARPS;
+  const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
+  if (cpl <= 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  else if (cpl <= 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  else if (cpl <= 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   return MG_OK;

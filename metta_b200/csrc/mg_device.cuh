@@ -21,10 +21,21 @@ struct EnvCtx {
   AsmRec* asms;       // global
   ChestRec* chests;   // global
   float* astats;      // global [A][S]
+  float* hot;         // shared copy of the first MG_HOT_STATS slots of every agent (null: use astats)
   float* gstats;      // global [GS]
   int n_asm;
   int clip_enabled, clip_length_scale;
+  uint32_t req_mask[3], con_mask[3];  // per action kind: which resources are required / consumed
 };
+
+// The per-step counters of an agent (action success/failure, frozen ticks, motion) live in the first
+// MG_HOT_STATS slots; the step kernel stages them in shared memory so that the ordered action pass
+// does not wait on HBM for every agent.
+#define MG_HOT_STATS 16
+MG_DEVICE inline float* agent_stat(const EnvCtx& e, int ai, int slot) {
+  if (slot < MG_HOT_STATS && e.hot != nullptr) return e.hot + ai * MG_HOT_STATS + slot;
+  return e.astats + (size_t)ai * e.S + slot;
+}
 
 // ---------------------------------------------------------------- inventory
 // The reference keeps each inventory as unordered_map<item, amount> plus shared limit records
@@ -125,7 +136,7 @@ MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item,
       if (had != has) {
         int n = 0;
         for (int i = 0; i < MG_MAX_RESOURCES; i++) n += (grp[MG_GRP_DIVERSITY + i] && a->amt[i] > 0) ? 1 : 0;
-        st[MG_AS_DIVERSITY] = (float)n;
+        *agent_stat(e, v.owner_idx, MG_AS_DIVERSITY) = (float)n;
       }
     }
   } else {
@@ -517,7 +528,6 @@ MG_DEVICE MG_NOINLINE bool try_attack(EnvCtx& e, int actor, uint16_t target_cell
   for (int i = 0; i < MG_MAX_RESOURCES; i++)
     if ((int)ac->amt[i] < (k[MG_ATK_CONSUMED + i] & 0xFFFF)) return false;
   InvView ai = agent_inv(e, actor), ti = agent_inv(e, target);
-  float* ast = e.astats + (size_t)actor * e.S;
   bool blocked = false;
   if (k[MG_ATK_HAS_DEFENSE]) {
     const int32_t* vb = e.cfg + e.cfg[MGC_OFF_VIBES] + tg->vibe * MG_VIBE_WORDS;
@@ -540,7 +550,7 @@ MG_DEVICE MG_NOINLINE bool try_attack(EnvCtx& e, int actor, uint16_t target_cell
     }
     if (can_defend) {
       for (int i = 0; i < defense.n; i++) inv_update(e, ti, defense.item[i], -(defense.val[i] + bonus), false, 0);
-      ast[MG_AS_ATTACK_BLOCKED_BY + tg->group] += 1.0f;
+      *agent_stat(e, actor, MG_AS_ATTACK_BLOCKED_BY + tg->group) += 1.0f;
       blocked = true;
     }
   }
@@ -559,10 +569,10 @@ MG_DEVICE MG_NOINLINE bool try_attack(EnvCtx& e, int actor, uint16_t target_cell
         inv_update(e, ti, l.item[i], -stolen, false, 0);
       }
     }
-    if (ac->group == tg->group) ast[MG_AS_ATTACK_FRIENDLY_FIRE] += 1.0f;
+    if (ac->group == tg->group) *agent_stat(e, actor, MG_AS_ATTACK_FRIENDLY_FIRE) += 1.0f;
     else {
-      ast[MG_AS_ATTACK_HIT + tg->group] += 1.0f;
-      e.astats[(size_t)target * e.S + MG_AS_ATTACK_HIT_BY + ac->group] += 1.0f;
+      *agent_stat(e, actor, MG_AS_ATTACK_HIT + tg->group) += 1.0f;
+      *agent_stat(e, target, MG_AS_ATTACK_HIT_BY + ac->group) += 1.0f;
     }
   }
   for (int i = 0; i < MG_MAX_RESOURCES; i++) {
@@ -608,7 +618,7 @@ MG_DEVICE MG_NOINLINE bool try_transfer(EnvCtx& e, int actor, uint16_t target_ce
       int actual = inv_update(e, ti, td.item[i], td.val[i], false, 0);
       if (actual != 0) ast[MG_AS_TRANSFER_TO + tg->group * RS + td.item[i]] += (float)actual;
     }
-  ast[MG_AS_TRANSFER_COUNT] += 1.0f;
+  *agent_stat(e, actor, MG_AS_TRANSFER_COUNT) += 1.0f;
   return true;
 }
 
@@ -641,7 +651,7 @@ MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
       tg->c = ac->c;
       ac->r = (uint16_t)tr;
       ac->c = (uint16_t)tc;
-      e.astats[(size_t)actor * e.S + MG_AS_SWAP] += 1.0f;
+      *agent_stat(e, actor, MG_AS_SWAP) += 1.0f;
       return true;
     }
     return false;  // Agent::onUse, agent.cpp:179-185
@@ -654,16 +664,17 @@ MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
 // ActionHandler::handle_action, action_handler.hpp:99-153
 MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
   AgentRec* ac = &e.ag[actor];
-  float* st = e.astats + (size_t)actor * e.S;
   if (ac->frozen != 0) {
-    st[MG_AS_FROZEN_TICKS] += 1.0f;
+    *agent_stat(e, actor, MG_AS_FROZEN_TICKS) += 1.0f;
     if (ac->frozen > 0) ac->frozen -= 1;
     return false;
   }
   const int32_t* res = e.cfg + e.cfg[MGC_OFF_ACTION_RES] + kind * MG_ACTRES_WORDS;
   bool has = true;
-  for (int i = 0; i < MG_MAX_RESOURCES; i++)
+  for (uint32_t m = e.req_mask[kind]; m != 0u; m &= m - 1u) {
+    const int i = __ffs((int)m) - 1;
     if ((int)ac->amt[i] < (res[MG_ACTRES_REQUIRED + i] & 0xFFFF)) { has = false; break; }
+  }
   bool success = false;
   if (has) {
     if (kind == MG_ACTION_NOOP) success = true;
@@ -672,23 +683,25 @@ MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
   }
   if (ac->r == ac->prev_r && ac->c == ac->prev_c) {
     ac->steps_without_motion += 1;
-    if ((float)ac->steps_without_motion > st[MG_AS_MAX_STEPS_WITHOUT_MOTION])
-      st[MG_AS_MAX_STEPS_WITHOUT_MOTION] = (float)ac->steps_without_motion;
+    float* mx = agent_stat(e, actor, MG_AS_MAX_STEPS_WITHOUT_MOTION);
+    if ((float)ac->steps_without_motion > *mx) *mx = (float)ac->steps_without_motion;
   } else {
     ac->steps_without_motion = 0;
   }
   ac->prev_r = ac->r;
   ac->prev_c = ac->c;
   if (success) {
-    st[MG_AS_ACTION_SUCCESS + kind] += 1.0f;
-    InvView ai = agent_inv(e, actor);
-    for (int i = 0; i < MG_MAX_RESOURCES; i++) {
-      int amt = res[MG_ACTRES_CONSUMED + i] & 0xFFFF;
-      if (amt > 0) inv_update(e, ai, i, -amt, false, 0);
+    *agent_stat(e, actor, MG_AS_ACTION_SUCCESS + kind) += 1.0f;
+    if (e.con_mask[kind] != 0u) {
+      InvView ai = agent_inv(e, actor);
+      for (uint32_t m = e.con_mask[kind]; m != 0u; m &= m - 1u) {
+        const int i = __ffs((int)m) - 1;
+        inv_update(e, ai, i, -(res[MG_ACTRES_CONSUMED + i] & 0xFFFF), false, 0);
+      }
     }
   } else {
-    st[MG_AS_ACTION_FAILED + kind] += 1.0f;
-    st[MG_AS_ACTION_FAILED_ANY] += 1.0f;
+    *agent_stat(e, actor, MG_AS_ACTION_FAILED + kind) += 1.0f;
+    *agent_stat(e, actor, MG_AS_ACTION_FAILED_ANY) += 1.0f;
   }
   return success;
 }
@@ -716,11 +729,10 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
   const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
   int n = grp[MG_GRP_NUM_REWARDS];
   if (n == 0) return 0.0f;
-  const float* st = e.astats + (size_t)ai * e.S;
   float total = 0.0f;
   for (int i = 0; i < n; i++) {
     const int32_t* rw = grp + MG_GRP_REWARDS + i * MG_RWD_WORDS;
-    float v = rw[MG_RWD_AGENT_STAT] >= 0 ? st[rw[MG_RWD_AGENT_STAT]] : 0.0f;
+    float v = rw[MG_RWD_AGENT_STAT] >= 0 ? *agent_stat(e, ai, rw[MG_RWD_AGENT_STAT]) : 0.0f;
     v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? e.gstats[rw[MG_RWD_GAME_STAT]] : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));
     if (rw[MG_RWD_HAS_MAX]) {

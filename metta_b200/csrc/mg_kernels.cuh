@@ -18,9 +18,16 @@
 #define MG_STEP_WARPS 4    /* envs per CTA in the reset/step kernels */
 #define MG_OBS_WARPS 8     /* agents per CTA in the observation kernel */
 #define MG_MAX_AGENTS 64   /* agents per env that fit the shared-memory staging */
+#ifndef MG_OBS_MIN_CTAS
+#define MG_OBS_MIN_CTAS 4 /* CTAs of the observation kernel resident per SM */
+#endif
+#ifndef MG_STEP_MIN_CTAS
+#define MG_STEP_MIN_CTAS 4 /* CTAs of the step kernel resident per SM (register cap = 65536 / (4*128) = 128) */
+#endif
 
 struct StepSmem {
   AgentRec ag[MG_MAX_AGENTS];
+  float hot[MG_MAX_AGENTS * MG_HOT_STATS];
   int32_t action[MG_MAX_AGENTS];
   int32_t executed[MG_MAX_AGENTS];
   uint8_t success[MG_MAX_AGENTS];
@@ -39,6 +46,8 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
   e.asms = b.asms + (size_t)env * b.max_asm;
   e.chests = b.chests + (size_t)env * b.max_chest;
   e.astats = b.agent_stats + (size_t)env * b.A * b.S;
+  e.hot = nullptr;
+  for (int k = 0; k < 3; k++) e.req_mask[k] = e.con_mask[k] = 0x1FFFu;
   e.gstats = b.game_stats + (size_t)env * b.GS;
   e.n_asm = er.n_asm;
   e.clip_enabled = b.has_clipper;
@@ -96,7 +105,7 @@ MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, in
 MG_DEVICE inline void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step) {
   __syncwarp();
   for (int ai = 0; ai < b.A; ai++) {
-    const int attempted = obs_encode_agent_warp(b, env, ai, lane, nullptr, current_step, 0);
+    const int attempted = obs_count_agent_warp(b, env, ai, lane, current_step);
     if (lane == 0) {
       uint16_t* tc = b.tok_counts + ((size_t)env * b.A + ai) * 2;
       tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
@@ -205,6 +214,11 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
     }
   }
   __syncwarp();
+  for (int ai = lane; ai < b.A; ai += 32)
+    write_agent_tokens(b, agents[ai], b.agent_tok + ((size_t)env * b.A + ai) * b.atok_stride);
+  for (int i = lane; i < er.n_chest; i += 32)
+    write_chest_tokens(b, chests[i], b.chest_tok + ((size_t)env * b.max_chest + i) * b.ctok_stride);
+  __syncwarp();
   // The reference's constructor ends with an observation pass on its internal buffers
   // (_make_buffers -> set_buffers -> _init_buffers, mettagrid_c.cpp:139-140,247-262), BEFORE the
   // clipper exists; the caller's set_buffers (simulator.py:93-100) then runs the pass whose output
@@ -283,7 +297,7 @@ MG_GLOBAL void mg_reset_kernel(MgBatch b, const uint8_t* mask) {
 }
 
 // ---------------------------------------------------------------- step
-MG_GLOBAL void mg_step_kernel(MgBatch b) {
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_kernel(MgBatch b) {
   MG_SHARED StepSmem smem[MG_STEP_WARPS];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -316,21 +330,55 @@ MG_GLOBAL void mg_step_kernel(MgBatch b) {
       sm.executed[ai] = 0;
       sm.success[ai] = 0;
     }
+    // the per-step counters of every agent (first MG_HOT_STATS slots): 16-byte loads, 4 per agent
+    const float* gst = b.agent_stats + (size_t)env * A * b.S;
+    for (int i = lane; i < A * (MG_HOT_STATS / 4); i += 32) {
+      const int ai = i / (MG_HOT_STATS / 4), q = i % (MG_HOT_STATS / 4);
+      reinterpret_cast<uint4*>(sm.hot)[i] = *reinterpret_cast<const uint4*>(gst + (size_t)ai * b.S + q * 4);
+    }
   }
   __syncwarp();
   er.current_step += 1;
   EnvCtx e = make_ctx(b, env, sm.ag, er);
+  e.hot = sm.hot;
+  {
+    // which resources each action kind requires / consumes: most configs name none or one, so the
+    // per-action checks iterate set bits instead of all resources
+    const int32_t* res = cfg + cfg[MGC_OFF_ACTION_RES];
+    for (int k = 0; k < 3; k++) {
+      const bool rq = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_REQUIRED + lane] & 0xFFFF) != 0;
+      const bool cn = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_CONSUMED + lane] & 0xFFFF) != 0;
+      e.req_mask[k] = __ballot_sync(MG_FULL_MASK, rq);
+      e.con_mask[k] = __ballot_sync(MG_FULL_MASK, cn);
+    }
+  }
   uint32_t* mt = b.rng + (size_t)env * MT_N;
+  const int nact = cfg[MGC_NUM_ACTIONS];
+  // Pull what the ordered pass will touch into L1 now, all agents at once: the cell each agent
+  // moves into and, when that is an assembler or a chest, its record. The pass itself re-reads the
+  // cells (it must see earlier agents' moves) but then hits L1 instead of waiting on HBM per agent.
+  for (int ai = lane; ai < A; ai += 32) {
+    const int a = sm.action[ai];
+    if (a < 0 || a >= nact) continue;
+    const int32_t* act = cfg + cfg[MGC_OFF_ACTIONS] + a * MG_ACT_WORDS;
+    if (act[MG_ACT_KIND] != MG_ACTION_MOVE) continue;
+    const int arg = act[MG_ACT_ARG];
+    const int tr = (int)sm.ag[ai].r + (int)((0xA058u >> (2 * arg)) & 3u) - 1;
+    const int tc = (int)sm.ag[ai].c + (int)((0x8885u >> (2 * arg)) & 3u) - 1;
+    if (tr < 0 || tc < 0 || tr >= b.H || tc >= b.W) continue;
+    const uint16_t g = e.grid[tr * b.W + tc];
+    if (MG_GRID_KIND(g) == MG_GK_ASM) MG_PREFETCH_L1(&e.asms[MG_GRID_INDEX(g)]);
+    else if (MG_GRID_KIND(g) == MG_GK_CHEST) MG_PREFETCH_L1(&e.chests[MG_GRID_INDEX(g)]);
+  }
 
   // random processing order (mettagrid_c.cpp:591-593)
   std_shuffle_warp(mt, er.rng_idx, lane, sm.order, A);
 
   // out-of-range actions: counted once per priority pass, two passes (mettagrid_c.cpp:599-608)
-  const int nact = cfg[MGC_NUM_ACTIONS];
   for (int ai = lane; ai < A; ai += 32) {
     const int a = sm.action[ai];
     if (a < 0 || a >= nact) {
-      float* st = e.astats + (size_t)ai * e.S + MG_AS_INVALID_INDEX;
+      float* st = agent_stat(e, ai, MG_AS_INVALID_INDEX);
       *st = MG_FADD(MG_FADD(*st, 1.0f), 1.0f);
     }
   }
@@ -358,7 +406,10 @@ MG_GLOBAL void mg_step_kernel(MgBatch b) {
   }
 
   // damage (agent.cpp:134-177): agent order, draws from the env rng
-  for (int base = 0; base < A; base += 32) {
+  bool any_damage = false;
+  for (int gidx = 0; gidx < cfg[MGC_NUM_GROUPS]; gidx++)
+    any_damage = any_damage || cfg[cfg[MGC_OFF_GROUPS] + gidx * MG_GRP_WORDS + MG_GRP_DAMAGE_ENABLED] != 0;
+  for (int base = 0; any_damage && base < A; base += 32) {
     const int ai = base + lane;
     bool met = false;
     if (ai < A) {
@@ -397,12 +448,11 @@ MG_GLOBAL void mg_step_kernel(MgBatch b) {
           InvView iv = agent_inv(e, who);
           const int item = sm.scratch[1 + sel];
           inv_update(e, iv, item, -1, false, 0);
-          float* st = e.astats + (size_t)who * e.S;
-          st[MG_AS_DAMAGE_ITEMS_LOST] += 1.0f;
-          st[MG_AS_DAMAGED + item] += 1.0f;
+          *agent_stat(e, who, MG_AS_DAMAGE_ITEMS_LOST) += 1.0f;
+          *agent_stat(e, who, MG_AS_DAMAGED + item) += 1.0f;
         }
       }
-      if (lane == 0) e.astats[(size_t)who * e.S + MG_AS_DAMAGE_TRIGGERED] += 1.0f;
+      if (lane == 0) *agent_stat(e, who, MG_AS_DAMAGE_TRIGGERED) += 1.0f;
       __syncwarp();
     }
   }
@@ -481,18 +531,27 @@ MG_GLOBAL void mg_step_kernel(MgBatch b) {
     b.truncations[g] = (uint8_t)((er.done >> 1) & 1);
     b.last_action[g] = sm.executed[ai];
     b.action_success[g] = sm.success[ai];
+    write_agent_tokens(b, sm.ag[ai], b.agent_tok + g * b.atok_stride);  // what observers will see of this agent
   }
+  for (int i = lane; i < er.n_chest; i += 32)
+    write_chest_tokens(b, e.chests[i], b.chest_tok + ((size_t)env * b.max_chest + i) * b.ctok_stride);
   __syncwarp();
   {
     uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
     const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
     for (int i = lane; i < A * 4; i += 32) dst[i] = src[i];
+    float* gst = b.agent_stats + (size_t)env * A * b.S;
+    for (int i = lane; i < A * (MG_HOT_STATS / 4); i += 32) {
+      const int ai = i / (MG_HOT_STATS / 4), q = i % (MG_HOT_STATS / 4);
+      *reinterpret_cast<uint4*>(gst + (size_t)ai * b.S + q * 4) = reinterpret_cast<const uint4*>(sm.hot)[i];
+    }
   }
   if (lane == 0) b.env[env] = er;
 }
 
 // ---------------------------------------------------------------- observations
-MG_GLOBAL void mg_obs_kernel(MgBatch b, const uint8_t* mask) {
+template <int CPL>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -514,7 +573,7 @@ MG_GLOBAL void mg_obs_kernel(MgBatch b, const uint8_t* mask) {
   }
   __syncwarp();
   const uint32_t current_step = b.env[env].current_step;
-  const int attempted = obs_encode_agent_warp(b, env, ai, lane, row, current_step, b.last_action[g]);
+  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, current_step, b.last_action[g]);
   __syncwarp();
   // store: bytes up to the first 16-byte boundary, 16-byte body, byte tail
   const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
@@ -556,6 +615,7 @@ MG_GLOBAL void mg_set_inventory_kernel(MgBatch b, int env, int ai, const int32_t
     e.astats[(size_t)ai * e.S + MG_AS_AMOUNT + existing[i]] = 0.0f;
   }
   for (int i = 0; i < n; i++) inv_update(e, iv, items[i], amounts[i] - (int)agents[ai].amt[items[i]], false, 0);
+  write_agent_tokens(b, agents[ai], b.agent_tok + ((size_t)env * b.A + ai) * b.atok_stride);
 }
 
 #endif  // MG_KERNELS_CUH_

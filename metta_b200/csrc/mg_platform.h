@@ -20,6 +20,9 @@
 #define MG_FADD(a, b) __fadd_rn((a), (b))
 #define MG_FMUL(a, b) __fmul_rn((a), (b))
 #define MG_INT_AS_FLOAT(x) __int_as_float(x)
+#define MG_LAUNCH_BOUNDS(t, b) __launch_bounds__(t, b)
+#define MG_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
+#define MG_LDG(p) __ldg(p)
 #endif
 
 #define MG_FULL_MASK 0xFFFFFFFFu

@@ -96,6 +96,12 @@ struct MgBatch {
   int32_t auto_reset, map_stride;
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
+  // static token templates, built once per config on the host (mg_abi.cu build_templates):
+  // a token is feature | value << 8; an index entry is offset << 8 | count
+  const uint16_t* tmpl_tok;
+  const uint32_t* tmpl_ix;     // [cells: full list for walls, tags+vibe tail for assemblers, tags for chests][protocols][groups: tags]
+  int32_t ix_proto, ix_group;  // section starts inside tmpl_ix
+  int32_t atok_stride, ctok_stride;  // bytes per agent / chest token record
   // map pool
   const uint16_t* pool_grid;   // [M][H*W]
   const int32_t* pool_agents;  // [M][A][3]
@@ -113,6 +119,8 @@ struct MgBatch {
   float* game_stats;           // [N][GS]
   uint32_t* rng;               // [N][624]
   uint32_t* clip_rng;          // [N][624] (only with a clipper)
+  uint8_t* agent_tok;          // [N][A][atok_stride]: byte 0 = token count, u16 tokens from byte 2: what observers see of an agent
+  uint8_t* chest_tok;          // [N][max_chest][ctok_stride]
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]

@@ -26,6 +26,9 @@
 #define MG_NOINLINE __attribute__((noinline))
 #define MG_SHARED static
 #define MG_DYN_SMEM(name) unsigned char* name = simt_emu::dyn_smem()
+#define MG_LAUNCH_BOUNDS(t, b)
+#define MG_PREFETCH_L1(p) ((void)(p))
+#define MG_LDG(p) (*(p))
 #define MG_FADD(a, b) ((float)(a) + (float)(b))
 #define MG_FMUL(a, b) ((float)(a) * (float)(b))
 #define MG_LAUNCH(kernel, grid, block, smem, stream, ...) \
