@@ -89,6 +89,21 @@ int mg_write(void* handle, int32_t what, const void* in_host, int64_t nbytes);
 /* MettaGrid::set_inventory (mettagrid_c.cpp:959-965): items_amounts = n item ids followed by n amounts. */
 int mg_set_inventory(void* handle, int32_t env, int32_t agent, const int32_t* items_amounts_host, int32_t n);
 
+/* No counterpart in the reference (its core runs on the host and allocates freely).
+ * Writes the observations of the CURRENT state of every env into obs_out_dev (u8[N*A][T][3], device
+ * memory of the caller) without allocating anything: no cudaMalloc/cudaFree, no allocating library
+ * call. For callers that must not allocate device memory while a rollout is running, e.g. a monitor
+ * or replay thread peeking at a training run whose framework has reserved the whole GPU, or a
+ * latency-bound thread that cannot take cudaMalloc's implicit synchronisation. Unlike
+ * mg_compute_observations it leaves the handle's bound buffers and token statistics untouched: the
+ * kernel's per-agent token-count scratch lives in a static 1 MiB device array instead.
+ * Limits and rules: at most 262144 agents (N*A) per call, larger batches are rejected with an
+ * error; every call on a GPU shares that array, which keeps the last call's contents (nothing in it
+ * needs clearing), so calls that overlap on the GPU race and must be serialised by the caller; the
+ * first call on each device looks up the array's device address (cudaGetSymbolAddress) and should
+ * be made before any stream capture begins. Asynchronous on `cuda_stream`. */
+int mg_peek_observations_noalloc(void* handle, void* obs_out_dev, void* cuda_stream);
+
 int64_t mg_kernel_launches(void* handle); /* kernels launched through this handle so far */
 int mg_sync(void* handle);
 

@@ -163,6 +163,13 @@ class Batch:
     def compute_observations(self, stream: int = 0) -> None:
         self._check(self._c.mg_compute_observations(self._h, stream))
 
+    def peek_observations(self, obs_out: int, stream: int = 0) -> None:
+        """Observations of the current state into a caller-owned device buffer (address `obs_out`,
+        u8[N*A][T][3]) through the allocation-free entry point: for code that may not allocate GPU
+        memory mid-rollout (monitors, replay writers). At most 262144 agents; calls sharing a GPU
+        must not overlap; make the first call on a device before any stream capture."""
+        self._check(self._c.mg_peek_observations_noalloc(self._h, obs_out, stream))
+
     def set_options(self, auto_reset: bool = True, map_stride: int = 0) -> None:
         self._check(self._c.mg_set_options(self._h, int(auto_reset), int(map_stride)))
 

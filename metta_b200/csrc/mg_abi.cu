@@ -544,3 +544,68 @@ int mg_sync(void* h) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// mg_peek_observations_noalloc: observations of the current state into a caller's side buffer,
+// without allocating anything and without disturbing the episode's token statistics.
+//
+// Who needs this: a monitor, evaluator or replay writer that wants to look at what the agents see
+// in the middle of a rollout while the trainer owns the GPU. Such a caller often may not allocate
+// device memory at all: the training framework's caching allocator has reserved nearly all of it
+// (a foreign cudaMalloc fails or forces a device-wide synchronisation), or the caller runs in a
+// thread whose latency budget forbids the implicit sync of cudaMalloc/cudaFree. The regular
+// observation pass cannot simply be pointed at another output either, because it leaves per-agent
+// token counts in scratch memory that the next step folds into tokens_written / tokens_dropped /
+// tokens_free_space; a second pass would be counted twice.
+//
+// So this variant of the observation kernel keeps that scratch (two u16 counts per agent) in the
+// file-scope device array below instead of cudaMalloc'ed memory. The array exists once per GPU
+// that loads this library and stays until the process exits: MG_PEEK_MAX_AGENTS * 4 bytes = 1 MiB.
+// Larger batches are refused. All calls on a device share the array and it keeps whatever the
+// last call wrote; nothing in it has to start at zero, because every slot a call reads was written
+// earlier in that same call. Two calls that overlap on the GPU (different streams, or different
+// handles on one device) race on it: serialise them.
+//
+// The name `g_peek_scratch` is only a host-side stand-in in host code, not a device address. The
+// first call on each device therefore asks the runtime for the real address
+// (cudaGetSymbolAddress, with that device current) and remembers it; make that first call before
+// starting any stream capture.
+#define MG_PEEK_MAX_AGENTS 262144
+#define MG_PEEK_MAX_DEVICES 64
+static __device__ __align__(256) uint16_t g_peek_scratch[MG_PEEK_MAX_AGENTS * 2];
+static uint16_t* g_peek_addr[MG_PEEK_MAX_DEVICES];  // device address of g_peek_scratch, per device ordinal
+
+extern "C" int mg_peek_observations_noalloc(void* h, void* obs_out_dev, void* stream) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !obs_out_dev) return fail(MG_ERR_ARG, "mg_peek_observations_noalloc: null handle or output buffer");
+  if (!e->maps_loaded) return fail(MG_ERR_STATE, "mg_peek_observations_noalloc: no maps loaded, nothing to observe");
+  const MgBatch& b = e->b;
+  const long long agents = (long long)b.num_envs * b.A;
+  if (agents > MG_PEEK_MAX_AGENTS)
+    return fail(MG_ERR_ARG, "mg_peek_observations_noalloc: " + std::to_string(agents) + " agents exceed the static scratch of " +
+                                std::to_string(MG_PEEK_MAX_AGENTS) + " agents; use mg_compute_observations on a bound buffer");
+  if (e->device < 0 || e->device >= MG_PEEK_MAX_DEVICES) return fail(MG_ERR_ARG, "mg_peek_observations_noalloc: device ordinal out of range");
+  CUDA_TRY(cudaSetDevice(e->device));
+  uint16_t* scratch = g_peek_addr[e->device];
+  if (scratch == nullptr) {  // once per device, with that device current
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_peek_scratch));
+    if (p == nullptr) return fail(MG_ERR_CUDA, "mg_peek_observations_noalloc: cudaGetSymbolAddress returned no address");
+    scratch = g_peek_addr[e->device] = reinterpret_cast<uint16_t*>(p);
+  }
+  MgBatch view = b;              // same state, other destinations
+  view.obs = reinterpret_cast<uint8_t*>(obs_out_dev);
+  view.tok_counts = scratch;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (int)((agents + MG_OBS_WARPS - 1) / MG_OBS_WARPS);
+  const int slot = (view.T * 3 + 16 + 15) & ~15;
+  const size_t smem = (size_t)slot * MG_OBS_WARPS;
+  const int cpl = (view.obs_cells + 31) / 32;
+  if (cpl <= 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
+  else if (cpl <= 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
+  else if (cpl <= 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
+  else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}

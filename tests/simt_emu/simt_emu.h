@@ -143,6 +143,10 @@ static inline cudaError_t cudaDeviceSynchronize() { return 0; }
 static inline cudaError_t cudaGetLastError() { return 0; }
 static inline cudaError_t cudaSetDevice(int) { return 0; }
 static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return 0; }
+#define __device__
+#define __align__(n) __attribute__((aligned(n)))
+template <typename T>
+static inline cudaError_t cudaGetSymbolAddress(void** p, const T& symbol) { *p = (void*)&symbol; return 0; }
 typedef void* cudaEvent_t;
 static inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = nullptr; return 0; }
 static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0; }
