@@ -195,8 +195,23 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
     if (max_entity_tokens > 255) return fail(MG_ERR_ARG, "mg_create: an object could show more than 255 tokens");
     b.atok_stride = (2 + 2 * max_entity_tokens + 15) & ~15;
     b.ctok_stride = b.atok_stride;
+    b.mtok_stride = (2 + 2 * (3 + 2 * b.R + max_tags + 1) + 15) & ~15;
+    b.stok_stride = (2 + 2 * (max_tags + 1) + 15) & ~15;
     TRY(dev_alloc(e, &b.agent_tok, N * A * (size_t)b.atok_stride));
     TRY(dev_alloc(e, &b.chest_tok, N * (size_t)b.max_chest * (size_t)b.ctok_stride));
+    TRY(dev_alloc(e, &b.asm_tok, N * (size_t)b.max_asm * (size_t)b.mtok_stride));
+    {  // static objects as token records (byte 0 = count, u16 tokens from byte 2), indexed by cell code
+      std::vector<uint8_t> srec((size_t)ncell * b.stok_stride, 0);
+      for (int c = 0; c < ncell; c++) {
+        const uint32_t en = ix[c];
+        srec[(size_t)c * b.stok_stride] = (uint8_t)(en & 0xFF);
+        memcpy(&srec[(size_t)c * b.stok_stride + 2], &tok[en >> 8], (en & 0xFF) * sizeof(uint16_t));
+      }
+      uint8_t* d_srec;
+      TRY(dev_alloc(e, &d_srec, srec.size()));
+      CUDA_TRY(cudaMemcpy(d_srec, srec.data(), srec.size(), cudaMemcpyHostToDevice));
+      b.static_tok = d_srec;
+    }
   }
   TRY(dev_alloc(e, &b.tok_counts, N * A * 2));
   TRY(dev_alloc(e, &b.last_action, N * A));

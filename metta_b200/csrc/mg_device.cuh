@@ -26,6 +26,7 @@ struct EnvCtx {
   int n_asm;
   int clip_enabled, clip_length_scale;
   uint32_t req_mask[3], con_mask[3];  // per action kind: which resources are required / consumed
+  bool concurrent;    // several lanes of the warp are running handle_action for different agents
 };
 
 // The per-step counters of an agent (action success/failure, frozen ticks, motion) live in the first
@@ -475,7 +476,11 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   for (int i = 0; i < in.n; i++) shared_update(e, inputs, nin, in.item[i], -(int)(uint16_t)in.val[i]);
   for (int i = 0; i < out.n; i++) {  // give_output_for_protocol :174-184
     int distributed = shared_update(e, outputs, nout, out.item[i], (int)(uint16_t)out.val[i]);
-    if (distributed > 0) e.gstats[MG_GS_ASM_CREATED + out.item[i]] += (float)distributed;
+    if (distributed > 0) {
+      // integer-valued float counter: the sum does not depend on the order of the additions
+      if (e.concurrent) atomicAdd(&e.gstats[MG_GS_ASM_CREATED + out.item[i]], (float)distributed);
+      else e.gstats[MG_GS_ASM_CREATED + out.item[i]] += (float)distributed;
+    }
   }
   a->cooldown_duration = (uint32_t)(uint16_t)p[MG_PROTO_COOLDOWN];
   a->cooldown_end = e.current_step + a->cooldown_duration;

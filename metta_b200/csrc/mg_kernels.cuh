@@ -47,6 +47,7 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
   e.chests = b.chests + (size_t)env * b.max_chest;
   e.astats = b.agent_stats + (size_t)env * b.A * b.S;
   e.hot = nullptr;
+  e.concurrent = false;
   for (int k = 0; k < 3; k++) e.req_mask[k] = e.con_mask[k] = 0x1FFFu;
   e.gstats = b.game_stats + (size_t)env * b.GS;
   e.n_asm = er.n_asm;
@@ -97,6 +98,14 @@ MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, in
         a->cache_step = e.current_step;
       }
   }
+  __syncwarp();
+}
+
+// What observers will see of every assembler this step (see write_asm_tokens).
+MG_DEVICE inline void write_all_asm_tokens_warp(const MgBatch& b, int env, int lane, int n_asm, uint32_t current_step) {
+  const AsmRec* asms = b.asms + (size_t)env * b.max_asm;
+  uint8_t* out = b.asm_tok + (size_t)env * b.max_asm * b.mtok_stride;
+  for (int i = lane; i < n_asm; i += 32) write_asm_tokens(b, &asms[i], current_step, out + (size_t)i * b.mtok_stride);
   __syncwarp();
 }
 
@@ -224,6 +233,7 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
   // clipper exists; the caller's set_buffers (simulator.py:93-100) then runs the pass whose output
   // is kept. Both passes add to tokens_written/dropped/free_space, so the first is counted here.
   update_protocol_cache_warp(b, e, lane);
+  write_all_asm_tokens_warp(b, env, lane, er.n_asm, 0u);
   count_observation_pass_warp(b, env, lane, 0u);
   if (b.has_clipper) {
     uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
@@ -258,6 +268,7 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
     }
   }
   update_protocol_cache_warp(b, e, lane);
+  write_all_asm_tokens_warp(b, env, lane, er.n_asm, 0u);
 }
 
 // Sum a finished episode into the batch accumulators before its state is overwritten.
@@ -384,11 +395,73 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   __syncwarp();
 
+  // ---- which agents can act independently of the processing order?
+  // An action reads and writes a small set of cells (and the agents standing on them): the mover's
+  // cell and the cell it moves into; for an assembler the 3x3 block around it (whose agents pay the
+  // inputs). If the bounding box of that footprint overlaps no other agent's box, nothing another
+  // agent does this step can change this action's outcome or see its effects, so the reference's
+  // shuffled order is irrelevant for it and one lane per agent can run them all at once. Agents
+  // whose boxes overlap (and everything touching chests or the clipper, whose stats are
+  // last-writer-wins) go through the ordered pass below, in the shuffled order.
+  const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+  uint32_t ordered_mask;
+  if (A <= 32) {
+    int r0 = 0, r1 = -1, c0 = 0, c1 = -1;  // empty box for lanes without an agent
+    bool ordered = false, valid = false;
+    int kind = 0, arg = 0;
+    if (lane < A) {
+      const AgentRec& me = sm.ag[lane];
+      r0 = r1 = me.r;
+      c0 = c1 = me.c;
+      const int a = sm.action[lane];
+      valid = a >= 0 && a < nact;
+      if (valid) {
+        kind = acts[a * MG_ACT_WORDS + MG_ACT_KIND];
+        arg = acts[a * MG_ACT_WORDS + MG_ACT_ARG];
+      }
+      if (valid && kind == MG_ACTION_MOVE && me.frozen == 0) {
+        const int tr = (int)me.r + (int)((0xA058u >> (2 * arg)) & 3u) - 1;
+        const int tc = (int)me.c + (int)((0x8885u >> (2 * arg)) & 3u) - 1;
+        if (tr >= 0 && tc >= 0 && tr < b.H && tc < b.W) {
+          r0 = tr < r0 ? tr : r0; r1 = tr > r1 ? tr : r1;
+          c0 = tc < c0 ? tc : c0; c1 = tc > c1 ? tc : c1;
+          const uint16_t g = e.grid[tr * b.W + tc];
+          const uint32_t gk = MG_GRID_KIND(g);
+          if (gk == MG_GK_CHEST) ordered = true;  // chest.<res>.amount is set, not added: order matters
+          if (gk == MG_GK_ASM) {
+            const AsmRec* ar = &e.asms[MG_GRID_INDEX(g)];
+            const int dist = asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE];
+            if (dist > 0 || b.has_clipper) ordered = true;
+            r0 = tr - 1 < r0 ? tr - 1 : r0; r1 = tr + 1 > r1 ? tr + 1 : r1;
+            c0 = tc - 1 < c0 ? tc - 1 : c0; c1 = tc + 1 > c1 ? tc + 1 : c1;
+          }
+        }
+      }
+    }
+    const uint32_t rr = (uint32_t)(r0 + 1) | ((uint32_t)(r1 + 1) << 16), cc = (uint32_t)(c0 + 1) | ((uint32_t)(c1 + 1) << 16);
+    for (int k = 0; k < A; k++) {
+      const uint32_t orr = __shfl_sync(MG_FULL_MASK, rr, k), occ = __shfl_sync(MG_FULL_MASK, cc, k);
+      const int kr0 = (int)(orr & 0xFFFFu) - 1, kr1 = (int)(orr >> 16) - 1, kc0 = (int)(occ & 0xFFFFu) - 1, kc1 = (int)(occ >> 16) - 1;
+      if (k != lane && !(r1 < kr0 || kr1 < r0 || c1 < kc0 || kc1 < c0)) ordered = true;
+    }
+    ordered_mask = __ballot_sync(MG_FULL_MASK, ordered && lane < A);
+    if (lane < A && valid && !ordered) {
+      e.concurrent = true;
+      const bool ok = handle_action(e, lane, kind, arg);
+      e.concurrent = false;
+      sm.success[lane] = ok ? 1 : 0;
+      if (ok) sm.executed[lane] = sm.action[lane];
+    }
+  } else {
+    ordered_mask = 0xFFFFFFFFu;
+  }
+  __syncwarp();
+
   // the ordered action pass: later agents see what earlier agents did
-  if (lane == 0) {
-    const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+  if (lane == 0 && ordered_mask != 0u) {
     for (int k = 0; k < A; k++) {
       const int ai = sm.order[k];
+      if (A <= 32 && !((ordered_mask >> ai) & 1u)) continue;
       const int a = sm.action[ai];
       if (a < 0 || a >= nact) continue;
       const bool ok = handle_action(e, ai, acts[a * MG_ACT_WORDS + MG_ACT_KIND], acts[a * MG_ACT_WORDS + MG_ACT_ARG]);
@@ -509,6 +582,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
 
   update_protocol_cache_warp(b, e, lane);
+  write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);
 
   // rewards, episode totals, truncation (mettagrid_c.cpp:655-677) and the write-back
   const uint32_t max_steps = (uint32_t)cfg[MGC_MAX_STEPS];

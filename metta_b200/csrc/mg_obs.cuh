@@ -85,6 +85,13 @@ MG_DEVICE inline void write_chest_tokens(const MgBatch& b, const ChestRec& c, ui
   rec[0] = (uint8_t)w.n;
 }
 
+// Assembler::obs_features (assembler.hpp:528-578): cooldown_remaining, clipped, remaining_uses, the
+// current protocol's inputs and outputs, tags, vibe. Rewritten every step by the action kernel
+// because cooldown_remaining changes with time.
+struct AsmView;
+MG_DEVICE inline void asm_view(const MgBatch& b, const int32_t* cfg, const AsmRec* a, uint32_t current_step, AsmView& v);
+MG_DEVICE inline void write_asm_tokens(const MgBatch& b, const AsmRec* a, uint32_t current_step, uint8_t* rec);
+
 // ---------------------------------------------------------------- per-observer encoding
 // What an assembler shows (assembler.hpp:528-578): [cooldown_remaining][clipped][remaining_uses]
 // computed here, then the current protocol's inputs/outputs (template), then tags and vibe (template).
@@ -134,6 +141,20 @@ MG_DEVICE inline void asm_view(const MgBatch& b, const int32_t* cfg, const AsmRe
   v.tail_ix = MG_LDG(&b.tmpl_ix[cell]);
 }
 
+MG_DEVICE inline void write_asm_tokens(const MgBatch& b, const AsmRec* a, uint32_t current_step, uint8_t* rec) {
+  AsmView v;
+  asm_view(b, b.cfg, a, current_step, v);
+  uint16_t* out = reinterpret_cast<uint16_t*>(rec + 2);
+  const int cap = (b.mtok_stride - 2) >> 1;
+  int n = 0;
+  for (int k = 0; k < v.ndyn; k++) { if (n < cap) out[n] = (uint16_t)v.dyn[k]; n++; }
+  const uint16_t* ps = b.tmpl_tok + (v.proto_ix >> 8);
+  for (uint32_t k = 0; k < (v.proto_ix & 0xFFu); k++) { if (n < cap) out[n] = MG_LDG(&ps[k]); n++; }
+  const uint16_t* ts = b.tmpl_tok + (v.tail_ix >> 8);
+  for (uint32_t k = 0; k < (v.tail_ix & 0xFFu); k++) { if (n < cap) out[n] = MG_LDG(&ts[k]); n++; }
+  rec[0] = (uint8_t)n;
+}
+
 MG_DEVICE inline int warp_exclusive_scan(int v, int lane, int* total) {
   int x = v;
   for (int d = 1; d < 32; d <<= 1) {
@@ -163,9 +184,6 @@ MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, in
   const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
   const AgentRec* me = b.agents + (size_t)env * b.A + ai;
-  const AsmRec* asms = b.asms + (size_t)env * b.max_asm;
-  const uint8_t* atok = b.agent_tok + (size_t)env * b.A * b.atok_stride;
-  const uint8_t* ctok = b.chest_tok + (size_t)env * b.max_chest * b.ctok_stride;
   const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(me);  // r | c << 16
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
   const int oh = cfg[MGC_OBS_H], ow = cfg[MGC_OBS_W];
@@ -206,9 +224,17 @@ MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, in
   }
   const int n_global = gpos;
 
-  // ---- pass 1: my cells' grid values and token counts
+  // ---- pass 1: my cells' grid values and token counts. Every object, static or not, shows a token
+  // record: byte 0 = count, u16 tokens from byte 2.
+  const uint8_t* rec_base[4];
+  int rec_stride[4];
+  rec_base[MG_GK_STATIC] = b.static_tok;                                            rec_stride[MG_GK_STATIC] = b.stok_stride;
+  rec_base[MG_GK_AGENT] = b.agent_tok + (size_t)env * b.A * b.atok_stride;          rec_stride[MG_GK_AGENT] = b.atok_stride;
+  rec_base[MG_GK_ASM] = b.asm_tok + (size_t)env * b.max_asm * b.mtok_stride;        rec_stride[MG_GK_ASM] = b.mtok_stride;
+  rec_base[MG_GK_CHEST] = b.chest_tok + (size_t)env * b.max_chest * b.ctok_stride;  rec_stride[MG_GK_CHEST] = b.ctok_stride;
   const int ncells = b.obs_cells;
-  uint32_t gv[CPL], cnt[CPL];
+  const uint8_t* rec[CPL];
+  uint32_t cnt[CPL];
   int mine = 0;
 #pragma unroll
   for (int j = 0; j < CPL; j++) {
@@ -219,18 +245,14 @@ MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, in
       const int r = my_r + (int)(loc >> 4) - hr, c = my_c + (int)(loc & 0xF) - wr;
       if (r >= 0 && r < b.H && c >= 0 && c < b.W) g = grid[r * b.W + c];
     }
-    gv[j] = g;
     uint32_t n = 0;
+    rec[j] = nullptr;
     if (g != 0) {
       const uint32_t kind = MG_GRID_KIND(g), idx = MG_GRID_INDEX(g);
-      if (kind == MG_GK_STATIC) n = MG_LDG(&b.tmpl_ix[idx]) & 0xFFu;
-      else if (kind == MG_GK_AGENT) n = atok[(size_t)idx * b.atok_stride];
-      else if (kind == MG_GK_CHEST) n = ctok[(size_t)idx * b.ctok_stride];
-      else {
-        AsmView v;
-        asm_view(b, cfg, &asms[idx], current_step, v);
-        n = (uint32_t)v.ndyn + (v.proto_ix & 0xFFu) + (v.tail_ix & 0xFFu);
-      }
+      const uint8_t* base = kind == MG_GK_STATIC ? rec_base[0] : (kind == MG_GK_AGENT ? rec_base[1] : (kind == MG_GK_ASM ? rec_base[2] : rec_base[3]));
+      const int stride = kind == MG_GK_STATIC ? rec_stride[0] : (kind == MG_GK_AGENT ? rec_stride[1] : (kind == MG_GK_ASM ? rec_stride[2] : rec_stride[3]));
+      rec[j] = base + (size_t)idx * stride;
+      n = rec[j][0];
     }
     cnt[j] = n;
     mine += (int)n;
@@ -243,24 +265,9 @@ MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, in
 #pragma unroll
     for (int j = 0; j < CPL; j++) {
       if (cnt[j] == 0 || pos >= T) continue;
-      const uint32_t g = gv[j];
       const uint32_t loc = b.pattern[lane * CPL + j];
-      const uint32_t kind = MG_GRID_KIND(g), idx = MG_GRID_INDEX(g);
-      if (kind == MG_GK_ASM) {
-        AsmView v;
-        asm_view(b, cfg, &asms[idx], current_step, v);
-        for (int k = 0; k < v.ndyn; k++) row_put(row, pos, T, loc, v.dyn[k]);
-        const uint16_t* ps = b.tmpl_tok + (v.proto_ix >> 8);
-        for (uint32_t k = 0; k < (v.proto_ix & 0xFFu); k++) row_put(row, pos, T, loc, MG_LDG(&ps[k]));
-        const uint16_t* ts = b.tmpl_tok + (v.tail_ix >> 8);
-        for (uint32_t k = 0; k < (v.tail_ix & 0xFFu); k++) row_put(row, pos, T, loc, MG_LDG(&ts[k]));
-      } else {
-        const uint16_t* src;
-        if (kind == MG_GK_STATIC) src = b.tmpl_tok + (MG_LDG(&b.tmpl_ix[idx]) >> 8);
-        else if (kind == MG_GK_AGENT) src = reinterpret_cast<const uint16_t*>(atok + (size_t)idx * b.atok_stride + 2);
-        else src = reinterpret_cast<const uint16_t*>(ctok + (size_t)idx * b.ctok_stride + 2);
-        for (uint32_t k = 0; k < cnt[j]; k++) row_put(row, pos, T, loc, src[k]);
-      }
+      const uint16_t* src = reinterpret_cast<const uint16_t*>(rec[j] + 2);
+      for (uint32_t k = 0; k < cnt[j]; k++) row_put(row, pos, T, loc, src[k]);
     }
   }
   return n_global + total;

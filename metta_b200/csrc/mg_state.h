@@ -101,7 +101,8 @@ struct MgBatch {
   const uint16_t* tmpl_tok;
   const uint32_t* tmpl_ix;     // [cells: full list for walls, tags+vibe tail for assemblers, tags for chests][protocols][groups: tags]
   int32_t ix_proto, ix_group;  // section starts inside tmpl_ix
-  int32_t atok_stride, ctok_stride;  // bytes per agent / chest token record
+  int32_t atok_stride, ctok_stride, mtok_stride, stok_stride;  // bytes per agent / chest / assembler / static token record
+  const uint8_t* static_tok;   // [cell codes][stok_stride]: token records of static objects (walls), same format as the entity records
   // map pool
   const uint16_t* pool_grid;   // [M][H*W]
   const int32_t* pool_agents;  // [M][A][3]
@@ -121,6 +122,7 @@ struct MgBatch {
   uint32_t* clip_rng;          // [N][624] (only with a clipper)
   uint8_t* agent_tok;          // [N][A][atok_stride]: byte 0 = token count, u16 tokens from byte 2: what observers see of an agent
   uint8_t* chest_tok;          // [N][max_chest][ctok_stride]
+  uint8_t* asm_tok;            // [N][max_asm][mtok_stride]: rewritten every step (cooldown_remaining changes with time)
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]
