@@ -192,15 +192,25 @@ def run_ours(args):
     g = torch.Generator().manual_seed(rank)
     ring = 16
     act_ring = torch.randint(0, 5, (ring, N * A), generator=g, dtype=torch.int32).to(dev)
-    batch.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act_ring[0].data_ptr())
+    act = act_ring[0].clone()  # the bound action buffer; every step starts by refreshing it from the ring (device copy)
+    batch.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act.data_ptr())
     seeds = ((np.arange(N) + first + 42) & 0xFFFFFFFF).astype(np.uint32)
     maps = ((np.arange(N) + first) % MAP_POOL).astype(np.int32)
     batch.reset(seeds, maps)
     stream = torch.cuda.current_stream(dev).cuda_stream
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB of L2
+    flush_rd = torch.zeros(64 * 1024 * 1024, dtype=torch.int32, device=dev)  # 256 MiB, only ever read
+
+    def flush_l2(i):
+        # write a buffer larger than L2, then stream another one through: the write evicts everything
+        # the simulator touched, the read pushes the dirty lines of the write out to HBM so that the
+        # timed step does not pay for writing back the flush itself
+        flush.fill_(i & 0xFF)
+        if args.flush == "write+read":
+            flush_rd.sum()
 
     def one_step(i):
-        batch.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act_ring[i % ring].data_ptr())
+        act.copy_(act_ring[i % ring], non_blocking=True)  # what a policy's sampling kernel would write
         batch.step(stream)
 
     for i in range(args.warmup):
@@ -217,7 +227,7 @@ def run_ours(args):
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     torch.cuda.synchronize()
     for i in range(args.steps):
-        flush.fill_(i & 0xFF)
+        flush_l2(i)
         starts[i].record()
         one_step(args.warmup + i)
         ends[i].record()
@@ -237,7 +247,8 @@ def run_ours(args):
     # ---- per-kernel durations for the roofline (events on the launch stream, L2 flushed)
     act_ms, obs_ms = [], []
     for i in range(min(args.steps, 50)):
-        flush.fill_(i & 0xFF)
+        act.copy_(act_ring[i % ring])
+        flush_l2(i)
         torch.cuda.synchronize()
         a_ms, o_ms = batch.profile_step(stream)
         act_ms.append(a_ms); obs_ms.append(o_ms)
@@ -282,7 +293,7 @@ def run_ours(args):
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
             "config": {"workload": f"arena, {N} envs x {A} agents per GPU, random actions, 62x62 synthetic maps, 11x11 window, {T} tokens",
-                       "envs_per_gpu": N, "agents_per_env": A, "l2": "flushed between timed steps (256 MiB fill)",
+                       "envs_per_gpu": N, "agents_per_env": A, "l2": "flushed between timed steps (256 MiB fill" + (", then 256 MiB streamed read)" if args.flush == "write+read" else ")"),
                        "parallelism": f"env shards x{world}, no data-path collective"},
             "clocks": clocks,
             "e2e": {"value": world * N * A * e2e_steps / e2e_s, "unit": "agent-steps/s",
@@ -311,6 +322,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--flush", default="write+read", choices=["write", "write+read"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

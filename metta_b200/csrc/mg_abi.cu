@@ -17,6 +17,7 @@
 
 static thread_local std::string g_err;
 
+#define MG_MAX_CHUNKS 16
 #define MG_OK 0
 #define MG_ERR_ARG 1
 #define MG_ERR_CUDA 2
@@ -45,6 +46,15 @@ struct MgEnvs {
   uint8_t* h_pinned;
   size_t h_pinned_bytes;
   cudaStream_t stream;
+  // the step is launched as MG_CHUNKS independent slices of envs on internal streams, so that the
+  // observation kernel of one slice overlaps the (latency-bound) step kernel of the others; the whole
+  // fork/join pattern is captured once in a CUDA graph and replayed
+  cudaStream_t chunk_stream[MG_MAX_CHUNKS], capture_stream;
+  cudaEvent_t ev_fork, ev_join[MG_MAX_CHUNKS];
+  int chunks;
+  bool graph_dirty;
+  cudaGraph_t graph;
+  cudaGraphExec_t graph_exec;
   uint8_t* d_mask;
   int32_t* d_tmp;  // small scratch for set_inventory
 };
@@ -106,6 +116,13 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   e->h_pinned = nullptr;
   e->h_pinned_bytes = 0;
   e->stream = nullptr;
+  e->chunks = 1;
+  e->graph_dirty = true;
+  e->graph = nullptr;
+  e->graph_exec = nullptr;
+  e->ev_fork = nullptr;
+  e->capture_stream = nullptr;
+  for (int i = 0; i < MG_MAX_CHUNKS; i++) { e->chunk_stream[i] = nullptr; e->ev_join[i] = nullptr; }
   e->cfg_host.assign(cfg, cfg + n_words);
   MgBatch& b = e->b;
   b.num_envs = num_envs;
@@ -123,6 +140,8 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   b.grid_stride = ((b.H * b.W + 7) / 8) * 8;
   b.auto_reset = 1;
   b.map_stride = 0;
+  b.env_begin = 0;
+  b.env_end = num_envs;
   const size_t N = (size_t)num_envs, A = (size_t)b.A;
   int32_t* d_cfg = nullptr;
   uint8_t* d_pat = nullptr;
@@ -190,27 +209,36 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
     CUDA_TRY(cudaMemcpy(d_tok, tok.data(), tok.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(d_ix, ix.data(), ix.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     b.tmpl_tok = d_tok; b.tmpl_ix = d_ix;
-    // per-entity token records: count byte + pad + the most tokens an agent / chest can show
-    const int max_entity_tokens = 3 + b.R * cfg[MGC_NUM_INV_TOKENS] + max_tags;
-    if (max_entity_tokens > 255) return fail(MG_ERR_ARG, "mg_create: an object could show more than 255 tokens");
-    b.atok_stride = (2 + 2 * max_entity_tokens + 15) & ~15;
-    b.ctok_stride = b.atok_stride;
-    b.mtok_stride = (2 + 2 * (3 + 2 * b.R + max_tags + 1) + 15) & ~15;
-    b.stok_stride = (2 + 2 * (max_tags + 1) + 15) & ~15;
-    TRY(dev_alloc(e, &b.agent_tok, N * A * (size_t)b.atok_stride));
-    TRY(dev_alloc(e, &b.chest_tok, N * (size_t)b.max_chest * (size_t)b.ctok_stride));
-    TRY(dev_alloc(e, &b.asm_tok, N * (size_t)b.max_asm * (size_t)b.mtok_stride));
-    {  // static objects as token records (byte 0 = count, u16 tokens from byte 2), indexed by cell code
-      std::vector<uint8_t> srec((size_t)ncell * b.stok_stride, 0);
+    // token records (format: MgBatch in mg_state.h): one power-of-two stride fits the largest list
+    // any object can show: agent = group, frozen, vibe + inventory digits + tags; assembler =
+    // clipped, remaining_uses + protocol inputs/outputs + tags + vibe (cooldown is added by observers)
+    const int max_agent_tokens = 3 + b.R * cfg[MGC_NUM_INV_TOKENS] + max_tags;
+    const int max_asm_tokens = 2 + 2 * b.R + max_tags + 1;
+    const int max_tokens = max_agent_tokens > max_asm_tokens ? max_agent_tokens : max_asm_tokens;
+    if (max_tokens > 254) return fail(MG_ERR_ARG, "mg_create: an object could show more than 254 tokens");
+    b.rec_shift = 5;
+    while ((1 << b.rec_shift) < MG_REC_TOKENS + 2 * max_tokens) b.rec_shift++;
+    const int stride = 1 << b.rec_shift;
+    const int base_agent = ncell, base_asm = ncell + b.A, base_chest = ncell + b.A + b.max_asm;
+    b.rec_slots = base_chest + b.max_chest;
+    if (b.rec_slots > 0xFFFF) return fail(MG_ERR_ARG, "mg_create: too many objects per env for the token record index");
+    b.rec_kind_base_lo = (uint32_t)0 | ((uint32_t)base_agent << 16);   // grid kinds 0 static, 1 agent
+    b.rec_kind_base_hi = (uint32_t)base_asm | ((uint32_t)base_chest << 16);  // 2 assembler, 3 chest
+    TRY(dev_alloc(e, &b.etok, (N * (size_t)b.rec_slots) << b.rec_shift));
+    TRY(dev_alloc(e, &b.gtok, N * A * (size_t)MG_GTOK_STRIDE));
+    if (3 + cfg[MGC_GOBS_COMPASS] + MG_MAX_GOALS > (MG_GTOK_STRIDE - 1) / 3)
+      return fail(MG_ERR_ARG, "mg_create: internal: global token record too small");
+    {  // static objects as token records, indexed by cell code; copied into every env at reset
+      std::vector<uint8_t> srec((size_t)ncell * stride, 0);
       for (int c = 0; c < ncell; c++) {
         const uint32_t en = ix[c];
-        srec[(size_t)c * b.stok_stride] = (uint8_t)(en & 0xFF);
-        memcpy(&srec[(size_t)c * b.stok_stride + 2], &tok[en >> 8], (en & 0xFF) * sizeof(uint16_t));
+        srec[(size_t)c * stride] = (uint8_t)(en & 0xFF);
+        memcpy(&srec[(size_t)c * stride + MG_REC_TOKENS], &tok[en >> 8], (en & 0xFF) * sizeof(uint16_t));
       }
       uint8_t* d_srec;
       TRY(dev_alloc(e, &d_srec, srec.size()));
       CUDA_TRY(cudaMemcpy(d_srec, srec.data(), srec.size(), cudaMemcpyHostToDevice));
-      b.static_tok = d_srec;
+      b.static_rec = d_srec;
     }
   }
   TRY(dev_alloc(e, &b.tok_counts, N * A * 2));
@@ -220,6 +248,18 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &e->d_mask, N));
   TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  // slices of about 512 envs (128 CTAs of the step kernel, a little under one per SM)
+  e->chunks = (num_envs + 511) / 512;
+  if (e->chunks > 8) e->chunks = 8;
+  if (const char* env_chunks = getenv("MG_CHUNKS")) e->chunks = atoi(env_chunks);  // tuning knob
+  if (e->chunks < 1) e->chunks = 1;
+  if (e->chunks > MG_MAX_CHUNKS) e->chunks = MG_MAX_CHUNKS;
+  CUDA_TRY(cudaStreamCreateWithFlags(&e->capture_stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+  for (int i = 0; i < e->chunks; i++) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&e->chunk_stream[i], cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
+  }
   *out = e;
   return MG_OK;
 }
@@ -232,6 +272,14 @@ void mg_destroy(void* h) {
   for (void* p : e->allocs) cudaFree(p);
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
   if (e->stream) cudaStreamDestroy(e->stream);
+  if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+  if (e->graph) cudaGraphDestroy(e->graph);
+  if (e->capture_stream) cudaStreamDestroy(e->capture_stream);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  for (int i = 0; i < MG_MAX_CHUNKS; i++) {
+    if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
+    if (e->chunk_stream[i]) cudaStreamDestroy(e->chunk_stream[i]);
+  }
   delete e;
 }
 
@@ -267,6 +315,7 @@ int mg_load_maps(void* h, int32_t num_maps, const uint16_t* grids, const int32_t
   b.pool_grid = d_grid; b.pool_agents = d_ag; b.pool_n_asm = d_na; b.pool_asm = d_as; b.pool_n_chest = d_nc; b.pool_chest = d_ch;
   b.num_maps = num_maps;
   e->maps_loaded = true;
+  e->graph_dirty = true;
   return MG_OK;
 }
 
@@ -297,13 +346,12 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
     b.rewards = (float*)rewards; b.actions = (const int32_t*)actions;
   }
   e->buffers_bound = true;
+  e->graph_dirty = true;
   return MG_OK;
 }
 
-static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
-  MgBatch& b = e->b;
-  const long long agents = (long long)b.num_envs * b.A;
-  const int grid = (int)((agents + MG_OBS_WARPS - 1) / MG_OBS_WARPS);
+static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask) {
+  const dim3 grid((unsigned)(b.env_end - b.env_begin), (unsigned)((b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
   const int slot = (b.T * 3 + 16 + 15) & ~15;
   const size_t smem = (size_t)slot * MG_OBS_WARPS;
   const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
@@ -313,6 +361,37 @@ static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
   else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   e->launches++;
   CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) { return launch_obs_slice(e, e->b, s, mask); }
+
+static int launch_step_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
+  const int grid = (b.env_end - b.env_begin + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
+  if (b.A <= 32) { MG_LAUNCH(mg_step_kernel<32>, grid, MG_STEP_WARPS * 32, 0, s, b); }
+  else { MG_LAUNCH(mg_step_kernel<MG_MAX_AGENTS>, grid, MG_STEP_WARPS * 32, 0, s, b); }
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+// Fork from `s` to the chunk streams, run step + observation kernel of each env slice, join back.
+static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s) {
+  const int n = e->b.num_envs, per = (n + e->chunks - 1) / e->chunks;
+  int rc;
+  CUDA_TRY(cudaEventRecord(e->ev_fork, s));
+  for (int c = 0; c < e->chunks; c++) {
+    MgBatch slice = e->b;
+    slice.env_begin = c * per;
+    slice.env_end = (c + 1) * per < n ? (c + 1) * per : n;
+    if (slice.env_begin >= slice.env_end) continue;
+    cudaStream_t cs = e->chunk_stream[c];
+    CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_fork, 0));
+    if ((rc = launch_step_slice(e, slice, cs)) != MG_OK) return rc;
+    if ((rc = launch_obs_slice(e, slice, cs, nullptr)) != MG_OK) return rc;
+    CUDA_TRY(cudaEventRecord(e->ev_join[c], cs));
+    CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[c], 0));
+  }
   return MG_OK;
 }
 
@@ -358,13 +437,31 @@ int mg_step(void* h, void* stream) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e) return fail(MG_ERR_ARG, "mg_step: null handle");
   if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_step: maps or buffers missing");
-  MgBatch& b = e->b;
   cudaStream_t s = (cudaStream_t)stream;
-  const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
-  MG_LAUNCH(mg_step_kernel, grid, MG_STEP_WARPS * 32, 0, s, b);
-  e->launches++;
-  CUDA_TRY(cudaGetLastError());
-  return launch_obs(e, s, nullptr);
+  if (e->chunks <= 1) {
+    int rc = launch_step_slice(e, e->b, s);
+    return rc != MG_OK ? rc : launch_obs(e, s, nullptr);
+  }
+#ifdef MG_SIMT_EMU
+  return enqueue_chunked_step(e, s);
+#else
+  if (e->graph_dirty) {  // (re)capture: buffers, options or maps changed since the last capture
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
+    const long long before = e->launches;
+    CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
+    int rc = enqueue_chunked_step(e, e->capture_stream);
+    cudaError_t end = cudaStreamEndCapture(e->capture_stream, &e->graph);
+    e->launches = before;
+    if (rc != MG_OK) return rc;
+    if (end != cudaSuccess) return fail(MG_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(end));
+    CUDA_TRY(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
+    e->graph_dirty = false;
+  }
+  CUDA_TRY(cudaGraphLaunch(e->graph_exec, s));
+  e->launches += 2LL * e->chunks;
+  return MG_OK;
+#endif
 }
 
 // One synchronous step with CUDA events around each kernel, for roofline measurements:
@@ -377,12 +474,10 @@ int mg_profile_step(void* h, void* stream, float* out_ms) {
   cudaStream_t s = (cudaStream_t)stream;
   cudaEvent_t ev[3];
   for (int i = 0; i < 3; i++) CUDA_TRY(cudaEventCreate(&ev[i]));
-  const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
-  CUDA_TRY(cudaEventRecord(ev[0], s));
-  MG_LAUNCH(mg_step_kernel, grid, MG_STEP_WARPS * 32, 0, s, b);
-  e->launches++;
-  CUDA_TRY(cudaEventRecord(ev[1], s));
   int rc;
+  CUDA_TRY(cudaEventRecord(ev[0], s));
+  TRY(launch_step_slice(e, b, s));
+  CUDA_TRY(cudaEventRecord(ev[1], s));
   TRY(launch_obs(e, s, nullptr));
   CUDA_TRY(cudaEventRecord(ev[2], s));
   CUDA_TRY(cudaEventSynchronize(ev[2]));
@@ -440,6 +535,7 @@ int mg_set_options(void* h, int32_t auto_reset, int32_t map_stride) {
   if (!e) return fail(MG_ERR_ARG, "mg_set_options: null handle");
   e->b.auto_reset = auto_reset ? 1 : 0;
   e->b.map_stride = map_stride < 0 ? 0 : map_stride;
+  e->graph_dirty = true;
   return MG_OK;
 }
 
@@ -612,7 +708,7 @@ extern "C" int mg_peek_observations_noalloc(void* h, void* obs_out_dev, void* st
   view.obs = reinterpret_cast<uint8_t*>(obs_out_dev);
   view.tok_counts = scratch;
   cudaStream_t s = (cudaStream_t)stream;
-  const int grid = (int)((agents + MG_OBS_WARPS - 1) / MG_OBS_WARPS);
+  const dim3 grid((unsigned)view.num_envs, (unsigned)((view.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
   const int slot = (view.T * 3 + 16 + 15) & ~15;
   const size_t smem = (size_t)slot * MG_OBS_WARPS;
   const int cpl = (view.obs_cells + 31) / 32;

@@ -9,6 +9,7 @@
 
 #include "mg_platform.h"
 #include "mg_state.h"
+#include "mg_tokens.cuh"
 
 #define RS MG_RES_STRIDE
 
@@ -27,6 +28,8 @@ struct EnvCtx {
   int clip_enabled, clip_length_scale;
   uint32_t req_mask[3], con_mask[3];  // per action kind: which resources are required / consumed
   bool concurrent;    // several lanes of the warp are running handle_action for different agents
+  const MgBatch* batch;
+  bool asm_records_on_use;  // assembler token records are rewritten where an assembler changes (else: all, every step)
 };
 
 // The per-step counters of an agent (action success/failure, frozen ticks, motion) live in the first
@@ -126,6 +129,7 @@ MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item,
   if (v.owner_kind == 0) {
     float* st = e.astats + (size_t)v.owner_idx * e.S;
     AgentRec* a = &e.ag[v.owner_idx];
+    a->pad0 = 1;  // token record is stale
     int amount = a->amt[item];
     if (delta > 0) st[MG_AS_GAINED + item] += (float)delta;
     else st[MG_AS_LOST + item] += (float)(-delta);
@@ -491,6 +495,7 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   } else {
     a->uses_count++;
   }
+  if (e.asm_records_on_use) write_asm_tokens(*e.batch, a, e.current_step, token_record(*e.batch, e.env, MG_GK_ASM, (uint32_t)asm_idx));
   return true;
 }
 
@@ -560,7 +565,7 @@ MG_DEVICE MG_NOINLINE bool try_attack(EnvCtx& e, int actor, uint16_t target_cell
     }
   }
   if (!blocked) {
-    if (k[MG_ATK_FREEZE] > 0) tg->frozen = (int16_t)k[MG_ATK_FREEZE];
+    if (k[MG_ATK_FREEZE] > 0) { tg->frozen = (int16_t)k[MG_ATK_FREEZE]; tg->pad0 = 1; }
     ItemList l;
     list_load(l, k + MG_ATK_ACTOR_DELTA);
     for (int i = 0; i < l.n; i++) inv_update(e, ai, l.item[i], l.val[i], false, 0);
@@ -667,11 +672,11 @@ MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
 }
 
 // ActionHandler::handle_action, action_handler.hpp:99-153
-MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
+MG_DEVICE MG_NOINLINE bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
   AgentRec* ac = &e.ag[actor];
   if (ac->frozen != 0) {
     *agent_stat(e, actor, MG_AS_FROZEN_TICKS) += 1.0f;
-    if (ac->frozen > 0) ac->frozen -= 1;
+    if (ac->frozen > 0) { ac->frozen -= 1; ac->pad0 = 1; }
     return false;
   }
   const int32_t* res = e.cfg + e.cfg[MGC_OFF_ACTION_RES] + kind * MG_ACTRES_WORDS;
@@ -684,7 +689,7 @@ MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
   if (has) {
     if (kind == MG_ACTION_NOOP) success = true;
     else if (kind == MG_ACTION_MOVE) success = handle_move(e, actor, arg);
-    else { ac->vibe = (uint8_t)arg; success = true; }  // change_vibe.hpp:48-51
+    else { ac->vibe = (uint8_t)arg; ac->pad0 = 1; success = true; }  // change_vibe.hpp:48-51
   }
   if (ac->r == ac->prev_r && ac->c == ac->prev_c) {
     ac->steps_without_motion += 1;

@@ -15,24 +15,33 @@
 #include "mg_obs.cuh"
 #include "mg_rng.cuh"
 
+// -DMG_TIMING: per-env cycle counts of the step kernel's phases in EnvRec::spare (tuning builds only)
+#ifdef MG_TIMING
+#define MG_TICK(i) do { const long long now__ = clock64(); tick_acc[i] += (uint32_t)(now__ - tick_last); tick_last = now__; } while (0)
+#else
+#define MG_TICK(i) do { } while (0)
+#endif
+
 #define MG_STEP_WARPS 4    /* envs per CTA in the reset/step kernels */
 #define MG_OBS_WARPS 8     /* agents per CTA in the observation kernel */
 #define MG_MAX_AGENTS 64   /* agents per env that fit the shared-memory staging */
 #ifndef MG_OBS_MIN_CTAS
-#define MG_OBS_MIN_CTAS 4 /* CTAs of the observation kernel resident per SM */
+#define MG_OBS_MIN_CTAS 8 /* CTAs of the observation kernel resident per SM (measured: 4 -> 135 us, 6 -> 111 us, 8 -> 103 us) */
 #endif
 #ifndef MG_STEP_MIN_CTAS
-#define MG_STEP_MIN_CTAS 4 /* CTAs of the step kernel resident per SM (register cap = 65536 / (4*128) = 128) */
+#define MG_STEP_MIN_CTAS 8 /* CTAs of the step kernel resident per SM: all 1024 CTAs of 4096 envs in one wave */
 #endif
 
+template <int MAXA>
 struct StepSmem {
-  AgentRec ag[MG_MAX_AGENTS];
-  float hot[MG_MAX_AGENTS * MG_HOT_STATS];
-  int32_t action[MG_MAX_AGENTS];
-  int32_t executed[MG_MAX_AGENTS];
-  uint8_t success[MG_MAX_AGENTS];
-  uint8_t order[MG_MAX_AGENTS];
+  AgentRec ag[MAXA];
+  float hot[MAXA * MG_HOT_STATS];
+  int32_t action[MAXA];
+  int32_t executed[MAXA];
+  uint8_t success[MAXA];
+  uint8_t order[MAXA];
   int32_t scratch[2 * MG_RES_STRIDE + 8];
+  uint32_t rngbuf[32];
 };
 
 MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
@@ -48,6 +57,8 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
   e.astats = b.agent_stats + (size_t)env * b.A * b.S;
   e.hot = nullptr;
   e.concurrent = false;
+  e.batch = &b;
+  e.asm_records_on_use = false;
   for (int k = 0; k < 3; k++) e.req_mask[k] = e.con_mask[k] = 0x1FFFu;
   e.gstats = b.game_stats + (size_t)env * b.GS;
   e.n_asm = er.n_asm;
@@ -62,17 +73,36 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
 MG_DEVICE inline void fold_token_stats_warp(const MgBatch& b, int env, int lane) {
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
   float* gs = b.game_stats + (size_t)env * b.GS;
+  // All counts are small integers. While a total stays below 2^24 every float addition is exact, so
+  // the sum of the counts can be added in one step; only beyond that does the reference's
+  // agent-by-agent rounding matter, and then the additions are replayed in its order.
+  int w = 0, d = 0, f = 0, any = 0;
+  for (int ai = lane; ai < b.A; ai += 32) {
+    const uint32_t pair = *reinterpret_cast<const uint32_t*>(tc + ai * 2);
+    const int written = (int)(pair & 0xFFFFu), attempted = (int)(pair >> 16);
+    if (attempted != 0xFFFF) { any = 1; w += written; d += attempted - written; f += b.T - written; }  // 0xFFFF: nothing pending
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    w += __shfl_xor_sync(MG_FULL_MASK, w, off);
+    d += __shfl_xor_sync(MG_FULL_MASK, d, off);
+    f += __shfl_xor_sync(MG_FULL_MASK, f, off);
+    any |= __shfl_xor_sync(MG_FULL_MASK, any, off);
+  }
+  if (!any) return;
   if (lane < 3) {
+    const int total = lane == 0 ? w : (lane == 1 ? d : f);
     float acc = gs[MG_GS_TOKENS_WRITTEN + lane];
-    bool any = false;
-    for (int ai = 0; ai < b.A; ai++) {
-      const int written = tc[ai * 2], attempted = tc[ai * 2 + 1];
-      if (attempted == 0xFFFF) continue;  // no observation was computed for this agent since the last fold
-      any = true;
-      const int v = lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written);
-      acc = MG_FADD(acc, (float)v);
+    if (acc + (float)total < 16777216.0f) {
+      acc = MG_FADD(acc, (float)total);
+    } else {
+      for (int ai = 0; ai < b.A; ai++) {
+        const int written = tc[ai * 2], attempted = tc[ai * 2 + 1];
+        if (attempted == 0xFFFF) continue;
+        const int v = lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written);
+        acc = MG_FADD(acc, (float)v);
+      }
     }
-    if (any) gs[MG_GS_TOKENS_WRITTEN + lane] = acc;
+    gs[MG_GS_TOKENS_WRITTEN + lane] = acc;
   }
   __syncwarp();
   for (int i = lane; i < b.A; i += 32) tc[i * 2 + 1] = 0xFFFF;
@@ -104,8 +134,7 @@ MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, in
 // What observers will see of every assembler this step (see write_asm_tokens).
 MG_DEVICE inline void write_all_asm_tokens_warp(const MgBatch& b, int env, int lane, int n_asm, uint32_t current_step) {
   const AsmRec* asms = b.asms + (size_t)env * b.max_asm;
-  uint8_t* out = b.asm_tok + (size_t)env * b.max_asm * b.mtok_stride;
-  for (int i = lane; i < n_asm; i += 32) write_asm_tokens(b, &asms[i], current_step, out + (size_t)i * b.mtok_stride);
+  for (int i = lane; i < n_asm; i += 32) write_asm_tokens(b, &asms[i], current_step, token_record(b, env, MG_GK_ASM, (uint32_t)i));
   __syncwarp();
 }
 
@@ -223,10 +252,17 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
     }
   }
   __syncwarp();
-  for (int ai = lane; ai < b.A; ai += 32)
-    write_agent_tokens(b, agents[ai], b.agent_tok + ((size_t)env * b.A + ai) * b.atok_stride);
-  for (int i = lane; i < er.n_chest; i += 32)
-    write_chest_tokens(b, chests[i], b.chest_tok + ((size_t)env * b.max_chest + i) * b.ctok_stride);
+  {  // token records: static objects from the per-config templates, then agents, chests, global tokens
+    const uint4* src = reinterpret_cast<const uint4*>(b.static_rec);
+    uint4* dst = reinterpret_cast<uint4*>(token_record(b, env, MG_GK_STATIC, 0u));
+    const int n16 = (cfg[MGC_NUM_CELLTYPES] << b.rec_shift) >> 4;
+    for (int i = lane; i < n16; i += 32) dst[i] = src[i];
+  }
+  for (int ai = lane; ai < b.A; ai += 32) {
+    write_agent_tokens(b, agents[ai], token_record(b, env, MG_GK_AGENT, (uint32_t)ai));
+    write_global_tokens(b, agents[ai], 0u, 0, b.gtok + ((size_t)env * b.A + ai) * MG_GTOK_STRIDE);
+  }
+  for (int i = lane; i < er.n_chest; i += 32) write_chest_tokens(b, chests[i], token_record(b, env, MG_GK_CHEST, (uint32_t)i));
   __syncwarp();
   // The reference's constructor ends with an observation pass on its internal buffers
   // (_make_buffers -> set_buffers -> _init_buffers, mettagrid_c.cpp:139-140,247-262), BEFORE the
@@ -259,7 +295,9 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
     for (int i = 0; i < er.n_asm; i++) {  // starting_clipped_assemblers, object id order
       const bool start = (asms[i].flags & MG_ASMF_TRACKED) && asm_type_cfg(cfg, asms[i].cell)[MG_ASM_START_CLIPPED];
       if (!start) continue;
-      const uint32_t sel = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+      MtStream cs = mt_stream(cmt, er.clip_rng_idx);
+      const uint32_t sel = uniform_below_warp(cs, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+      er.clip_rng_idx = cs.idx;
       if (lane == 0) {
         asms[i].flags &= (uint8_t)~MG_ASMF_CLIPPED;
         clip_assembler(e, &asms[i], sel);
@@ -308,50 +346,130 @@ MG_GLOBAL void mg_reset_kernel(MgBatch b, const uint8_t* mask) {
 }
 
 // ---------------------------------------------------------------- step
+// MAXA: agents per env the shared-memory staging is sized for (32 or MG_MAX_AGENTS)
+template <int MAXA>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_kernel(MgBatch b) {
-  MG_SHARED StepSmem smem[MG_STEP_WARPS];
+  MG_SHARED StepSmem<MAXA> smem[MG_STEP_WARPS];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const int env = blockIdx.x * MG_STEP_WARPS + warp;
-  if (env >= b.num_envs) return;
-  StepSmem& sm = smem[warp];
+  const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
+  if (env >= b.env_end) return;
+  StepSmem<MAXA>& sm = smem[warp];
   const int32_t* cfg = b.cfg;
   const int A = b.A;
   EnvRec er = b.env[env];
+#ifdef MG_TIMING
+  long long tick_last = clock64();
+  uint32_t tick_acc[5] = {0, 0, 0, 0, 0};
+#endif
 
-  fold_token_stats_warp(b, env, lane);
-  if (er.done && b.auto_reset) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
-    accumulate_episode_warp(b, env, lane);
-    __syncwarp();
-    if (b.num_maps > 0) er.map_idx = (er.map_idx + b.map_stride) % b.num_maps;
-    er.episodes += 1;
-    reset_env_warp(b, env, lane, er);
-    __syncwarp();
-    // set_buffers of the new Simulation: the initial observation nobody sees is still counted
-    count_observation_pass_warp(b, env, lane, 0u);
-  }
+  // ---- bring the env in. Every load that does not depend on another is issued before the first
+  // use, so the whole stage costs about one HBM round trip instead of one per array: agent records
+  // and their 16 per-step stat slots (16-byte loads), actions, the pending token counts of the last
+  // observation pass and the three float totals they are folded into.
+  constexpr int NV = MAXA * 4 / 32;  // 16-byte loads per lane for records (and for hot stats)
+  constexpr int NA = (MAXA + 31) / 32;
+  const size_t abase = (size_t)env * A;
+  for (bool fresh = false;;) {
+    uint4 ag_v[NV], hot_v[NV];
+    int32_t act_v[NA];
+    uint32_t tc_v[NA];
+    const uint4* ag_src = reinterpret_cast<const uint4*>(b.agents + abase);
+    const float* gst = b.agent_stats + abase * b.S;
+    uint16_t* tc = b.tok_counts + abase * 2;
+    float* gs = b.game_stats + (size_t)env * b.GS;
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      const int i = lane + 32 * k;
+      if (i < A * 4) {
+        ag_v[k] = ag_src[i];
+        hot_v[k] = *reinterpret_cast<const uint4*>(gst + (size_t)(i >> 2) * b.S + (i & 3) * 4);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NA; k++) {
+      const int ai = lane + 32 * k;
+      act_v[k] = ai < A ? b.actions[abase + ai] : 0;
+      tc_v[k] = ai < A ? *reinterpret_cast<const uint32_t*>(tc + ai * 2) : 0xFFFF0000u;
+    }
+    float gs3 = lane < 3 ? gs[MG_GS_TOKENS_WRITTEN + lane] : 0.0f;
 
-  // stage this env's agents in shared memory
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(b.agents + (size_t)env * A);
-    uint4* dst = reinterpret_cast<uint4*>(sm.ag);
-    for (int i = lane; i < A * 4; i += 32) dst[i] = src[i];
-    for (int ai = lane; ai < A; ai += 32) {
-      sm.action[ai] = b.actions[(size_t)env * A + ai];
-      sm.executed[ai] = 0;
-      sm.success[ai] = 0;
+    // fold the pending token counts (written | attempted << 16; attempted 0xFFFF = nothing pending)
+    {
+      int w = 0, d = 0, f = 0, any = 0;
+#pragma unroll
+      for (int k = 0; k < NA; k++) {
+        const int written = (int)(tc_v[k] & 0xFFFFu), attempted = (int)(tc_v[k] >> 16);
+        if (attempted != 0xFFFF) { any = 1; w += written; d += attempted - written; f += b.T - written; }
+      }
+      for (int off = 16; off > 0; off >>= 1) {
+        w += __shfl_xor_sync(MG_FULL_MASK, w, off);
+        d += __shfl_xor_sync(MG_FULL_MASK, d, off);
+        f += __shfl_xor_sync(MG_FULL_MASK, f, off);
+        any |= __shfl_xor_sync(MG_FULL_MASK, any, off);
+      }
+      if (any) {
+        const int total = lane == 0 ? w : (lane == 1 ? d : f);
+        const bool exact = gs3 + (float)total < 16777216.0f;  // see fold_token_stats_warp
+        if (__ballot_sync(MG_FULL_MASK, lane < 3 && !exact) != 0u) {
+          fold_token_stats_warp(b, env, lane);
+        } else {
+          if (lane < 3) gs[MG_GS_TOKENS_WRITTEN + lane] = MG_FADD(gs3, (float)total);
+#pragma unroll
+          for (int k = 0; k < NA; k++) {
+            const int ai = lane + 32 * k;
+            if (ai < A) tc[ai * 2 + 1] = 0xFFFF;
+          }
+        }
+      }
     }
-    // the per-step counters of every agent (first MG_HOT_STATS slots): 16-byte loads, 4 per agent
-    const float* gst = b.agent_stats + (size_t)env * A * b.S;
-    for (int i = lane; i < A * (MG_HOT_STATS / 4); i += 32) {
-      const int ai = i / (MG_HOT_STATS / 4), q = i % (MG_HOT_STATS / 4);
-      reinterpret_cast<uint4*>(sm.hot)[i] = *reinterpret_cast<const uint4*>(gst + (size_t)ai * b.S + q * 4);
+    if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
+      __syncwarp();
+      accumulate_episode_warp(b, env, lane);
+      __syncwarp();
+      if (b.num_maps > 0) er.map_idx = (er.map_idx + b.map_stride) % b.num_maps;
+      er.episodes += 1;
+      reset_env_warp(b, env, lane, er);
+      __syncwarp();
+      // set_buffers of the new Simulation: the initial observation nobody sees is still counted
+      count_observation_pass_warp(b, env, lane, 0u);
+      fresh = true;
+      continue;  // load the new episode's state
     }
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      const int i = lane + 32 * k;
+      if (i < A * 4) {
+        reinterpret_cast<uint4*>(sm.ag)[i] = ag_v[k];
+        reinterpret_cast<uint4*>(sm.hot)[i] = hot_v[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NA; k++) {
+      const int ai = lane + 32 * k;
+      if (ai < A) {
+        sm.action[ai] = act_v[k];
+        sm.executed[ai] = 0;
+        sm.success[ai] = 0;
+      }
+    }
+    break;
   }
   __syncwarp();
+  // the stat slots the rewards will read at the end of the step: start pulling them into L1 now
+  for (int ai = lane; ai < A; ai += 32) {
+    const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
+    const float* st = b.agent_stats + (abase + ai) * b.S;
+    for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
+      const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
+      if (slot >= MG_HOT_STATS) MG_PREFETCH_L1(st + slot);
+    }
+  }
+  if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L1(b.game_stats + (size_t)env * b.GS + lane * 32);
   er.current_step += 1;
   EnvCtx e = make_ctx(b, env, sm.ag, er);
   e.hot = sm.hot;
+  e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
   {
     // which resources each action kind requires / consumes: most configs name none or one, so the
     // per-action checks iterate set bits instead of all resources
@@ -365,25 +483,36 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   uint32_t* mt = b.rng + (size_t)env * MT_N;
   const int nact = cfg[MGC_NUM_ACTIONS];
-  // Pull what the ordered pass will touch into L1 now, all agents at once: the cell each agent
-  // moves into and, when that is an assembler or a chest, its record. The pass itself re-reads the
-  // cells (it must see earlier agents' moves) but then hits L1 instead of waiting on HBM per agent.
-  for (int ai = lane; ai < A; ai += 32) {
-    const int a = sm.action[ai];
-    if (a < 0 || a >= nact) continue;
-    const int32_t* act = cfg + cfg[MGC_OFF_ACTIONS] + a * MG_ACT_WORDS;
-    if (act[MG_ACT_KIND] != MG_ACTION_MOVE) continue;
-    const int arg = act[MG_ACT_ARG];
-    const int tr = (int)sm.ag[ai].r + (int)((0xA058u >> (2 * arg)) & 3u) - 1;
-    const int tc = (int)sm.ag[ai].c + (int)((0x8885u >> (2 * arg)) & 3u) - 1;
-    if (tr < 0 || tc < 0 || tr >= b.H || tc >= b.W) continue;
-    const uint16_t g = e.grid[tr * b.W + tc];
-    if (MG_GRID_KIND(g) == MG_GK_ASM) MG_PREFETCH_L1(&e.asms[MG_GRID_INDEX(g)]);
-    else if (MG_GRID_KIND(g) == MG_GK_CHEST) MG_PREFETCH_L1(&e.chests[MG_GRID_INDEX(g)]);
+  const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+  // ---- what does every agent want to do? One agent per lane: decode the action, find the target
+  // cell of a move and what stands there. These loads (and the prefetch of the assembler or chest
+  // record behind the cell) are issued for all agents at once; the passes below hit L1.
+  int my_kind = 0, my_arg = 0, my_tr = -1, my_tc = -1;
+  bool my_valid = false;
+  uint32_t my_target = 0;  // grid value of the cell a move goes to (0: empty, or no in-bounds move)
+  if (A <= 32 && lane < A) {
+    const int a = sm.action[lane];
+    my_valid = a >= 0 && a < nact;
+    if (my_valid) {
+      my_kind = acts[a * MG_ACT_WORDS + MG_ACT_KIND];
+      my_arg = acts[a * MG_ACT_WORDS + MG_ACT_ARG];
+      if (my_kind == MG_ACTION_MOVE && sm.ag[lane].frozen == 0) {
+        const int tr = (int)sm.ag[lane].r + (int)((0xA058u >> (2 * my_arg)) & 3u) - 1;
+        const int tc2 = (int)sm.ag[lane].c + (int)((0x8885u >> (2 * my_arg)) & 3u) - 1;
+        if (tr >= 0 && tc2 >= 0 && tr < b.H && tc2 < b.W) {
+          my_tr = tr; my_tc = tc2;
+          my_target = e.grid[tr * b.W + tc2];
+          if (MG_GRID_KIND(my_target) == MG_GK_ASM) MG_PREFETCH_L1(&e.asms[MG_GRID_INDEX(my_target)]);
+          else if (MG_GRID_KIND(my_target) == MG_GK_CHEST) MG_PREFETCH_L1(&e.chests[MG_GRID_INDEX(my_target)]);
+        }
+      }
+    }
   }
-
-  // random processing order (mettagrid_c.cpp:591-593)
-  std_shuffle_warp(mt, er.rng_idx, lane, sm.order, A);
+  MG_TICK(0);
+  // random processing order (mettagrid_c.cpp:591-593); the words it needs are fetched in one go
+  MtStream rs = mt_stream(mt, er.rng_idx);
+  mt_prefetch_warp(rs, sm.rngbuf, lane);
+  std_shuffle_fast_warp(rs, lane, sm.order, A, reinterpret_cast<uint32_t*>(sm.scratch));
 
   // out-of-range actions: counted once per priority pass, two passes (mettagrid_c.cpp:599-608)
   for (int ai = lane; ai < A; ai += 32) {
@@ -395,59 +524,62 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   __syncwarp();
 
+  MG_TICK(1);
   // ---- which agents can act independently of the processing order?
-  // An action reads and writes a small set of cells (and the agents standing on them): the mover's
-  // cell and the cell it moves into; for an assembler the 3x3 block around it (whose agents pay the
-  // inputs). If the bounding box of that footprint overlaps no other agent's box, nothing another
-  // agent does this step can change this action's outcome or see its effects, so the reference's
-  // shuffled order is irrelevant for it and one lane per agent can run them all at once. Agents
-  // whose boxes overlap (and everything touching chests or the clipper, whose stats are
-  // last-writer-wins) go through the ordered pass below, in the shuffled order.
-  const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+  // An action touches the mover's cell and the cell it moves into; using an assembler touches the
+  // agents standing in the 3x3 block around it (they pay the inputs). Agents stand on distinct
+  // cells, so the reference's shuffled order can only matter for an agent when
+  //   (1) another agent moves into the same cell,
+  //   (2) the cell it moves into holds an agent (swap, attack, transfer, or that agent leaves first),
+  //   (3) it uses an assembler and another agent stands in, or moves into, that assembler's block,
+  //   (4) it touches a chest or a chest-searching assembler (chest.<res>.amount is last-writer-wins)
+  //       or anything under a clipper (shared infection weights).
+  // Everybody else is handled one agent per lane, all at once; the rest goes through the ordered
+  // pass below in the shuffled order. Both sides of a conflict are ordered.
   uint32_t ordered_mask;
   if (A <= 32) {
-    int r0 = 0, r1 = -1, c0 = 0, c1 = -1;  // empty box for lanes without an agent
-    bool ordered = false, valid = false;
-    int kind = 0, arg = 0;
-    if (lane < A) {
-      const AgentRec& me = sm.ag[lane];
-      r0 = r1 = me.r;
-      c0 = c1 = me.c;
-      const int a = sm.action[lane];
-      valid = a >= 0 && a < nact;
-      if (valid) {
-        kind = acts[a * MG_ACT_WORDS + MG_ACT_KIND];
-        arg = acts[a * MG_ACT_WORDS + MG_ACT_ARG];
-      }
-      if (valid && kind == MG_ACTION_MOVE && me.frozen == 0) {
-        const int tr = (int)me.r + (int)((0xA058u >> (2 * arg)) & 3u) - 1;
-        const int tc = (int)me.c + (int)((0x8885u >> (2 * arg)) & 3u) - 1;
-        if (tr >= 0 && tc >= 0 && tr < b.H && tc < b.W) {
-          r0 = tr < r0 ? tr : r0; r1 = tr > r1 ? tr : r1;
-          c0 = tc < c0 ? tc : c0; c1 = tc > c1 ? tc : c1;
-          const uint16_t g = e.grid[tr * b.W + tc];
-          const uint32_t gk = MG_GRID_KIND(g);
-          if (gk == MG_GK_CHEST) ordered = true;  // chest.<res>.amount is set, not added: order matters
-          if (gk == MG_GK_ASM) {
-            const AsmRec* ar = &e.asms[MG_GRID_INDEX(g)];
-            const int dist = asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE];
-            if (dist > 0 || b.has_clipper) ordered = true;
-            r0 = tr - 1 < r0 ? tr - 1 : r0; r1 = tr + 1 > r1 ? tr + 1 : r1;
-            c0 = tc - 1 < c0 ? tc - 1 : c0; c1 = tc + 1 > c1 ? tc + 1 : c1;
+    if (lane == 0) sm.scratch[0] = 0;  // bits of agents that someone else's action can affect
+    __syncwarp();
+    bool ordered = false;
+    const uint32_t tkind = MG_GRID_KIND(my_target);
+    const bool moving = my_tr >= 0;
+    const uint32_t same_target = __match_any_sync(MG_FULL_MASK, moving ? my_tr * b.W + my_tc : -1 - lane);
+    if (moving && (same_target & (same_target - 1u)) != 0u) ordered = true;                 // (1)
+    if (moving && my_target != 0u && tkind == MG_GK_AGENT) {                                // (2)
+      ordered = true;
+      atomicOr(reinterpret_cast<unsigned int*>(&sm.scratch[0]), 1u << MG_GRID_INDEX(my_target));
+    }
+    bool uses_asm = moving && tkind == MG_GK_ASM;
+    if (moving && tkind == MG_GK_CHEST) ordered = true;                                     // (4)
+    if (uses_asm) {
+      const AsmRec* ar = &e.asms[MG_GRID_INDEX(my_target)];
+      if (b.has_clipper || asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE] > 0) ordered = true;  // (4)
+      for (int i = -1; i <= 1; i++)                                                         // (3) standing in the block
+        for (int j = -1; j <= 1; j++) {
+          const int rr = my_tr + i, cc = my_tc + j;
+          if ((i == 0 && j == 0) || rr < 0 || cc < 0 || rr >= b.H || cc >= b.W) continue;
+          const uint16_t g = e.grid[rr * b.W + cc];
+          if (MG_GRID_KIND(g) == MG_GK_AGENT && (int)MG_GRID_INDEX(g) != lane) {
+            ordered = true;
+            atomicOr(reinterpret_cast<unsigned int*>(&sm.scratch[0]), 1u << MG_GRID_INDEX(g));
           }
         }
-      }
     }
-    const uint32_t rr = (uint32_t)(r0 + 1) | ((uint32_t)(r1 + 1) << 16), cc = (uint32_t)(c0 + 1) | ((uint32_t)(c1 + 1) << 16);
-    for (int k = 0; k < A; k++) {
-      const uint32_t orr = __shfl_sync(MG_FULL_MASK, rr, k), occ = __shfl_sync(MG_FULL_MASK, cc, k);
-      const int kr0 = (int)(orr & 0xFFFFu) - 1, kr1 = (int)(orr >> 16) - 1, kc0 = (int)(occ & 0xFFFFu) - 1, kc1 = (int)(occ >> 16) - 1;
-      if (k != lane && !(r1 < kr0 || kr1 < r0 || c1 < kc0 || kc1 < c0)) ordered = true;
+    uint32_t users = __ballot_sync(MG_FULL_MASK, uses_asm);
+    while (users != 0u) {                                                                   // (3) moving into the block
+      const int u = __ffs((int)users) - 1;
+      users &= users - 1u;
+      const int br = __shfl_sync(MG_FULL_MASK, my_tr, u), bc = __shfl_sync(MG_FULL_MASK, my_tc, u);
+      const bool hit = moving && lane != u && my_tr >= br - 1 && my_tr <= br + 1 && my_tc >= bc - 1 && my_tc <= bc + 1;
+      if (hit) ordered = true;
+      if (__ballot_sync(MG_FULL_MASK, hit) != 0u && lane == u) ordered = true;
     }
+    __syncwarp();
+    if ((((uint32_t)sm.scratch[0]) >> lane) & 1u) ordered = true;
     ordered_mask = __ballot_sync(MG_FULL_MASK, ordered && lane < A);
-    if (lane < A && valid && !ordered) {
+    if (lane < A && my_valid && !ordered) {
       e.concurrent = true;
-      const bool ok = handle_action(e, lane, kind, arg);
+      const bool ok = handle_action(e, lane, my_kind, my_arg);
       e.concurrent = false;
       sm.success[lane] = ok ? 1 : 0;
       if (ok) sm.executed[lane] = sm.action[lane];
@@ -457,6 +589,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   __syncwarp();
 
+  MG_TICK(2);
   // the ordered action pass: later agents see what earlier agents did
   if (lane == 0 && ordered_mask != 0u) {
     for (int k = 0; k < A; k++) {
@@ -471,6 +604,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   __syncwarp();
 
+  MG_TICK(3);
   // inventory regeneration (mettagrid_c.cpp:625-640): independent per agent
   const uint32_t regen = (uint32_t)cfg[MGC_REGEN_INTERVAL];
   if (regen > 0u && er.current_step % regen == 0u) {
@@ -516,7 +650,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
       if (n > 0) {
         int weights[MG_RES_STRIDE];
         for (int i = 0; i < n; i++) weights[i] = sm.scratch[1 + MG_RES_STRIDE + i];
-        const int sel = discrete_pick_warp(mt, er.rng_idx, lane, weights, n);
+        const int sel = discrete_pick_warp(rs, lane, weights, n);
         if (lane == 0) {
           InvView iv = agent_inv(e, who);
           const int item = sm.scratch[1 + sel];
@@ -535,14 +669,15 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
     const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
     uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
     const uint32_t period = (uint32_t)cc[MG_CLIP_PERIOD];
+    MtStream cs = mt_stream(cmt, er.clip_rng_idx);
     bool fire;
     if (period == 0u) {
       // uniform_int_distribution<uint32_t>(1, 0): the 64-bit range wraps, libstdc++ composes two draws
       // (uniform_int_dist.h:331-356) and truncates: the result is 1 only when the second word is 0.
-      (void)mt_next_warp(cmt, er.clip_rng_idx, lane);
-      fire = mt_next_warp(cmt, er.clip_rng_idx, lane) == 0u;
+      (void)mt_next_warp(cs, lane);
+      fire = mt_next_warp(cs, lane) == 0u;
     } else {
-      fire = uniform_below_warp(cmt, er.clip_rng_idx, lane, period) == 0u;
+      fire = uniform_below_warp(cs, lane, period) == 0u;
     }
     if (fire) {
       if (lane == 0) {
@@ -562,27 +697,30 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
       if (nun > 0) {
         int pick = -1;
         if (total == 0u) {
-          uint32_t k = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)nun);
+          uint32_t k = uniform_below_warp(cs, lane, (uint32_t)nun);
           for (int i = 0; i < e.n_asm && pick < 0; i++)
             if (e.asms[i].flags & MG_ASMF_UNCLIPPED) { if (k == 0u) pick = i; else k--; }
         } else {
-          uint32_t rw = uniform_below_warp(cmt, er.clip_rng_idx, lane, total) + 1u;
+          uint32_t rw = uniform_below_warp(cs, lane, total) + 1u;
           for (int i = 0; i < e.n_asm && pick < 0; i++) {
             if (!(e.asms[i].flags & MG_ASMF_BORDER)) continue;
             if (rw <= e.asms[i].infection_weight) pick = i; else rw -= e.asms[i].infection_weight;
           }
         }
         if (pick >= 0) {
-          const uint32_t sel = uniform_below_warp(cmt, er.clip_rng_idx, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+          const uint32_t sel = uniform_below_warp(cs, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
           if (lane == 0) clip_assembler(e, &e.asms[pick], sel);
           __syncwarp();
         }
       }
     }
+    er.clip_rng_idx = cs.idx;
   }
 
   update_protocol_cache_warp(b, e, lane);
-  write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);
+  // where the visible protocol can change without the assembler being used (vibes of neighbours, the
+  // clipper), all assembler records are refreshed; otherwise assembler_on_use already did it
+  if (cfg[MGC_HAS_VIBE_ASM]) write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);
 
   // rewards, episode totals, truncation (mettagrid_c.cpp:655-677) and the write-back
   const uint32_t max_steps = (uint32_t)cfg[MGC_MAX_STEPS];
@@ -605,10 +743,13 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
     b.truncations[g] = (uint8_t)((er.done >> 1) & 1);
     b.last_action[g] = sm.executed[ai];
     b.action_success[g] = sm.success[ai];
-    write_agent_tokens(b, sm.ag[ai], b.agent_tok + g * b.atok_stride);  // what observers will see of this agent
+    if (sm.ag[ai].pad0 != 0) {  // vibe, frozen or inventory changed: refresh what observers see of this agent
+      write_agent_tokens(b, sm.ag[ai], token_record(b, env, MG_GK_AGENT, (uint32_t)ai));
+      sm.ag[ai].pad0 = 0;
+    }
+    write_global_tokens(b, sm.ag[ai], er.current_step, sm.executed[ai], b.gtok + g * MG_GTOK_STRIDE);
   }
-  for (int i = lane; i < er.n_chest; i += 32)
-    write_chest_tokens(b, e.chests[i], b.chest_tok + ((size_t)env * b.max_chest + i) * b.ctok_stride);
+  for (int i = lane; i < er.n_chest; i += 32) write_chest_tokens(b, e.chests[i], token_record(b, env, MG_GK_CHEST, (uint32_t)i));
   __syncwarp();
   {
     uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
@@ -620,6 +761,11 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
       *reinterpret_cast<uint4*>(gst + (size_t)ai * b.S + q * 4) = reinterpret_cast<const uint4*>(sm.hot)[i];
     }
   }
+  er.rng_idx = rs.idx;
+  MG_TICK(4);
+#ifdef MG_TIMING
+  for (int i = 0; i < 5; i++) er.spare[i] = tick_acc[i];
+#endif
   if (lane == 0) b.env[env] = er;
 }
 
@@ -629,10 +775,10 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const long long g = (long long)blockIdx.x * MG_OBS_WARPS + warp;  // global agent index
-  if (g >= (long long)b.num_envs * b.A) return;
-  const int env = (int)(g / b.A), ai = (int)(g % b.A);
+  const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
+  if (ai >= b.A) return;
   if (mask != nullptr && !mask[env]) return;
+  const size_t g = (size_t)env * b.A + ai;  // global agent index
   const int row_bytes = b.T * 3;
   const int slot = (row_bytes + 16 + 15) & ~15;  // room to mirror the row's misalignment
   uint8_t* out = b.obs + (size_t)g * row_bytes;
@@ -647,7 +793,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   }
   __syncwarp();
   const uint32_t current_step = b.env[env].current_step;
-  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, current_step, b.last_action[g]);
+  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, current_step);
   __syncwarp();
   // store: bytes up to the first 16-byte boundary, 16-byte body, byte tail
   const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
@@ -689,7 +835,7 @@ MG_GLOBAL void mg_set_inventory_kernel(MgBatch b, int env, int ai, const int32_t
     e.astats[(size_t)ai * e.S + MG_AS_AMOUNT + existing[i]] = 0.0f;
   }
   for (int i = 0; i < n; i++) inv_update(e, iv, items[i], amounts[i] - (int)agents[ai].amt[items[i]], false, 0);
-  write_agent_tokens(b, agents[ai], b.agent_tok + ((size_t)env * b.A + ai) * b.atok_stride);
+  write_agent_tokens(b, agents[ai], token_record(b, env, MG_GK_AGENT, (uint32_t)ai));
 }
 
 #endif  // MG_KERNELS_CUH_

@@ -43,13 +43,44 @@ MG_DEVICE inline void mt_twist_warp(uint32_t* mt, int lane) {
   }
 }
 
-// operator() (bits/random.tcc:435-455). Called by all lanes; every lane gets the same word.
-MG_DEVICE inline uint32_t mt_next_warp(uint32_t* mt, uint32_t& idx, int lane) {
-  if (idx >= MT_N) {
-    mt_twist_warp(mt, lane);
-    idx = 0;
+// A warp's view of one env's generator. `buf` optionally holds the next untempered words
+// (state[buf_base .. buf_base + buf_n)), fetched by all lanes in one go so that a run of draws
+// does not pay one HBM round trip each.
+struct MtStream {
+  uint32_t* mt;
+  uint32_t idx;  // std::mt19937::_M_p
+  const uint32_t* buf;
+  uint32_t buf_base, buf_n;
+};
+
+MG_DEVICE inline MtStream mt_stream(uint32_t* mt, uint32_t idx) {
+  MtStream s;
+  s.mt = mt; s.idx = idx; s.buf = nullptr; s.buf_base = 0; s.buf_n = 0;
+  return s;
+}
+
+// Regenerate if the state is exhausted, then stage the next (up to 32) words in `buf` (shared memory).
+MG_DEVICE inline void mt_prefetch_warp(MtStream& s, uint32_t* buf, int lane) {
+  if (s.idx >= MT_N) {
+    mt_twist_warp(s.mt, lane);
+    s.idx = 0;
   }
-  uint32_t z = mt[idx++];
+  const uint32_t n = MT_N - s.idx < 32u ? MT_N - s.idx : 32u;
+  if ((uint32_t)lane < n) buf[lane] = s.mt[s.idx + lane];
+  __syncwarp();
+  s.buf = buf; s.buf_base = s.idx; s.buf_n = n;
+}
+
+// operator() (bits/random.tcc:435-455). Called by all lanes; every lane gets the same word.
+MG_DEVICE inline uint32_t mt_next_warp(MtStream& s, int lane) {
+  if (s.idx >= MT_N) {
+    mt_twist_warp(s.mt, lane);
+    s.idx = 0;
+    s.buf_n = 0;
+  }
+  const uint32_t k = s.idx - s.buf_base;
+  uint32_t z = (s.buf_n != 0u && k < s.buf_n) ? s.buf[k] : s.mt[s.idx];
+  s.idx++;
   z ^= (z >> 11);
   z ^= (z << 7) & 0x9d2c5680u;
   z ^= (z << 15) & 0xefc60000u;
@@ -59,13 +90,13 @@ MG_DEVICE inline uint32_t mt_next_warp(uint32_t* mt, uint32_t& idx, int lane) {
 
 // uniform_int_distribution<T>(0, range-1), range < 2^32, on a 32-bit engine: Lemire's method
 // (bits/uniform_int_dist.h:257-330).
-MG_DEVICE inline uint32_t uniform_below_warp(uint32_t* mt, uint32_t& idx, int lane, uint32_t range) {
-  uint64_t product = (uint64_t)mt_next_warp(mt, idx, lane) * (uint64_t)range;
+MG_DEVICE inline uint32_t uniform_below_warp(MtStream& s, int lane, uint32_t range) {
+  uint64_t product = (uint64_t)mt_next_warp(s, lane) * (uint64_t)range;
   uint32_t low = (uint32_t)product;
   if (low < range) {
     uint32_t threshold = (0u - range) % range;
     while (low < threshold) {
-      product = (uint64_t)mt_next_warp(mt, idx, lane) * (uint64_t)range;
+      product = (uint64_t)mt_next_warp(s, lane) * (uint64_t)range;
       low = (uint32_t)product;
     }
   }
@@ -74,20 +105,20 @@ MG_DEVICE inline uint32_t uniform_below_warp(uint32_t* mt, uint32_t& idx, int la
 
 // std::shuffle over n indices (bits/stl_algo.h:3742-3800, two swap positions per draw).
 // Every lane runs the same loop so the draws stay warp-uniform; lane 0 owns `order`.
-MG_DEVICE inline void std_shuffle_warp(uint32_t* mt, uint32_t& idx, int lane, uint8_t* order, int n) {
+MG_DEVICE inline void std_shuffle_warp(MtStream& s, int lane, uint8_t* order, int n) {
   if (lane == 0)
     for (int i = 0; i < n; i++) order[i] = (uint8_t)i;
   if (n <= 1) return;
   int i = 1;
   if ((n & 1) == 0) {
-    uint32_t j = uniform_below_warp(mt, idx, lane, 2u);
+    uint32_t j = uniform_below_warp(s, lane, 2u);
     if (lane == 0) { uint8_t t = order[1]; order[1] = order[j]; order[j] = t; }
     i = 2;
   }
   while (i < n) {
-    uint32_t s = (uint32_t)i + 1u;
-    uint32_t x = uniform_below_warp(mt, idx, lane, s * (s + 1u));
-    uint32_t p0 = x / (s + 1u), p1 = x % (s + 1u);
+    uint32_t sr = (uint32_t)i + 1u;
+    uint32_t x = uniform_below_warp(s, lane, sr * (sr + 1u));
+    uint32_t p0 = x / (sr + 1u), p1 = x % (sr + 1u);
     if (lane == 0) {
       uint8_t t = order[i]; order[i] = order[p0]; order[p0] = t;
       t = order[i + 1]; order[i + 1] = order[p1]; order[p1] = t;
@@ -96,14 +127,65 @@ MG_DEVICE inline void std_shuffle_warp(uint32_t* mt, uint32_t& idx, int lane, ui
   }
 }
 
+// The same shuffle with the draws computed side by side: draw d only depends on word d of the
+// stream (unless Lemire's method rejects a word, about once in 10^7 draws: then everything is redone
+// by the loop above), so lane d tempers word d and derives its pair of swap positions, and one lane
+// applies the swaps in order. `scratch` is shared memory for 32 words.
+MG_DEVICE inline void std_shuffle_fast_warp(MtStream& s, int lane, uint8_t* order, int n, uint32_t* scratch) {
+  const int nd = n >> 1;  // draws: n even: 1 + (n - 2) / 2, n odd: (n - 1) / 2
+  const uint32_t first = s.idx - s.buf_base;
+  if (n <= 1 || nd > 32 || s.buf_n == 0u || s.idx < s.buf_base || first + (uint32_t)nd > s.buf_n) {
+    std_shuffle_warp(s, lane, order, n);
+    return;
+  }
+  bool reject = false;
+  if (lane < nd) {
+    const bool even = (n & 1) == 0;
+    const uint32_t i = even ? 2u * (uint32_t)lane : 2u * (uint32_t)lane + 1u;  // index of the first element this draw places
+    const uint32_t sr = i + 1u;
+    const uint32_t range = (even && lane == 0) ? 2u : sr * (sr + 1u);
+    uint32_t z = s.buf[first + lane];
+    z ^= (z >> 11);
+    z ^= (z << 7) & 0x9d2c5680u;
+    z ^= (z << 15) & 0xefc60000u;
+    z ^= (z >> 18);
+    const uint64_t product = (uint64_t)z * (uint64_t)range;
+    const uint32_t low = (uint32_t)product;
+    if (low < range && low < (0u - range) % range) reject = true;
+    const uint32_t x = (uint32_t)(product >> 32);
+    scratch[lane] = (even && lane == 0) ? x : ((x / (sr + 1u)) | ((x % (sr + 1u)) << 16));
+  }
+  if (__ballot_sync(MG_FULL_MASK, reject) != 0u) {
+    std_shuffle_warp(s, lane, order, n);
+    return;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    for (int k = 0; k < n; k++) order[k] = (uint8_t)k;
+    int i = 1, d = 0;
+    if ((n & 1) == 0) {
+      const uint32_t j = scratch[0];
+      uint8_t t = order[1]; order[1] = order[j]; order[j] = t;
+      i = 2; d = 1;
+    }
+    for (; i < n; i += 2, d++) {
+      const uint32_t p0 = scratch[d] & 0xFFFFu, p1 = scratch[d] >> 16;
+      uint8_t t = order[i]; order[i] = order[p0]; order[p0] = t;
+      t = order[i + 1]; order[i + 1] = order[p1]; order[p1] = t;
+    }
+  }
+  s.idx += (uint32_t)nd;
+  __syncwarp();
+}
+
 // std::discrete_distribution<size_t>(weights)(g) (bits/random.tcc:2657-2730); generate_canonical
 // draws two words (:3349-3382). A single weight returns 0 without drawing. Doubles, as the reference.
-MG_DEVICE inline int discrete_pick_warp(uint32_t* mt, uint32_t& idx, int lane, const int* weights, int n) {
+MG_DEVICE inline int discrete_pick_warp(MtStream& st, int lane, const int* weights, int n) {
   if (n < 2) return 0;
   double sum = 0.0;
   for (int i = 0; i < n; i++) sum += (double)weights[i];
-  double s = (double)mt_next_warp(mt, idx, lane);
-  s += (double)mt_next_warp(mt, idx, lane) * 4294967296.0;
+  double s = (double)mt_next_warp(st, lane);
+  s += (double)mt_next_warp(st, lane) * 4294967296.0;
   double u = s / 18446744073709551616.0;
   if (u >= 1.0) u = 0.99999999999999988897769753748;  // nextafter(1.0, 0.0)
   double acc = 0.0;

@@ -28,6 +28,9 @@
 #define MG_GK_ASM 2
 #define MG_GK_CHEST 3
 
+#define MG_GTOK_STRIDE 64
+#define MG_REC_TOKENS 8 /* byte offset of the tokens inside a token record */
+
 #define MG_ORDER_EMPTY 0xFFFFFFFFFFFFFFFFull /* inventory order list: 4-bit item ids, 0xF ends the list */
 
 struct alignas(16) AgentRec {
@@ -38,7 +41,7 @@ struct alignas(16) AgentRec {
   uint32_t steps_without_motion;
   uint64_t order;  // iteration order of the reference's unordered_map<item, amount>
   uint16_t amt[MG_MAX_RESOURCES];
-  uint16_t pad0;
+  uint16_t pad0;  // step kernel scratch: token record needs a refresh
   float current_stat_reward;
   float episode_reward;
   uint32_t pad1;
@@ -94,6 +97,7 @@ struct MgBatch {
   int32_t obs_cells;           // obs_h * obs_w
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
+  int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
   // static token templates, built once per config on the host (mg_abi.cu build_templates):
@@ -101,8 +105,13 @@ struct MgBatch {
   const uint16_t* tmpl_tok;
   const uint32_t* tmpl_ix;     // [cells: full list for walls, tags+vibe tail for assemblers, tags for chests][protocols][groups: tags]
   int32_t ix_proto, ix_group;  // section starts inside tmpl_ix
-  int32_t atok_stride, ctok_stride, mtok_stride, stok_stride;  // bytes per agent / chest / assembler / static token record
-  const uint8_t* static_tok;   // [cell codes][stok_stride]: token records of static objects (walls), same format as the entity records
+  // Token records: what an observer copies for one object. Uniform format for every kind of object:
+  // byte 0 = token count n, bytes 4..7 = cooldown_end (assemblers; 0 otherwise: a cooldown_remaining
+  // token is prepended while cooldown_end > current_step), n u16 tokens from byte 8.
+  // One array per env, slots [static cell codes | agents | assemblers | chests], stride 1 << rec_shift.
+  int32_t rec_shift, rec_slots;       // bytes per record = 1 << rec_shift; records per env
+  uint32_t rec_kind_base_lo, rec_kind_base_hi;  // first slot of grid kinds 0..3, 16 bits each
+  const uint8_t* static_rec;   // [cell codes][1 << rec_shift]: records of static objects, copied into every env at reset
   // map pool
   const uint16_t* pool_grid;   // [M][H*W]
   const int32_t* pool_agents;  // [M][A][3]
@@ -120,9 +129,8 @@ struct MgBatch {
   float* game_stats;           // [N][GS]
   uint32_t* rng;               // [N][624]
   uint32_t* clip_rng;          // [N][624] (only with a clipper)
-  uint8_t* agent_tok;          // [N][A][atok_stride]: byte 0 = token count, u16 tokens from byte 2: what observers see of an agent
-  uint8_t* chest_tok;          // [N][max_chest][ctok_stride]
-  uint8_t* asm_tok;            // [N][max_asm][mtok_stride]: rewritten every step (cooldown_remaining changes with time)
+  uint8_t* etok;               // [N][rec_slots][1 << rec_shift] token records (see above)
+  uint8_t* gtok;               // [N][A][MG_GTOK_STRIDE]: byte 0 = n, then n (location, feature, value) triples: the global tokens of an agent
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]

@@ -56,7 +56,8 @@ void block_barrier() {
   while (s.block_gen == gen) yield();
 }
 
-void launch(int grid, int block, size_t smem, std::function<void()> body) {
+void launch(dim3 grid3, int block, size_t smem, std::function<void()> body) {
+  const int grid = (int)(grid3.x * grid3.y);
   State& s = st();
   s.body = body;
   if ((int)s.fibers.size() < block) {
@@ -65,12 +66,13 @@ void launch(int grid, int block, size_t smem, std::function<void()> body) {
     for (size_t i = old; i < (size_t)block; i++) s.fibers[i].stack = (char*)malloc(kStack);
   }
   s.dyn = (unsigned char*)aligned_alloc(256, ((smem + 255) & ~(size_t)255) + 256);
-  gridDim.x = (unsigned)grid; gridDim.y = gridDim.z = 1;
+  gridDim.x = grid3.x; gridDim.y = grid3.y; gridDim.z = 1;
   blockDim.x = (unsigned)block; blockDim.y = blockDim.z = 1;
-  threadIdx.y = threadIdx.z = blockIdx.y = blockIdx.z = 0;
+  threadIdx.y = threadIdx.z = blockIdx.z = 0;
   const int nwarps = (block + 31) / 32;
   for (int bid = 0; bid < grid; bid++) {
-    blockIdx.x = (unsigned)bid;
+    blockIdx.x = (unsigned)bid % grid3.x;
+    blockIdx.y = (unsigned)bid / grid3.x;
     s.warps.assign(nwarps, WarpState());
     for (int wi = 0; wi < nwarps; wi++) {
       int nl = block - wi * 32;

@@ -37,7 +37,12 @@
 static inline float MG_INT_AS_FLOAT(int32_t x) { float f; memcpy(&f, &x, 4); return f; }
 
 struct uint4 { uint32_t x, y, z, w; } __attribute__((aligned(16)));
+struct uint2 { uint32_t x, y; } __attribute__((aligned(8)));
 struct emu_dim3 { unsigned x, y, z; };
+struct dim3 {
+  unsigned x, y, z;
+  dim3(unsigned x_ = 1, unsigned y_ = 1, unsigned z_ = 1) : x(x_), y(y_), z(z_) {}
+};
 
 namespace simt_emu {
 struct Fiber {
@@ -62,7 +67,7 @@ struct State {
   bool progressed;
 };
 State& st();
-void launch(int grid, int block, size_t smem, std::function<void()> body);
+void launch(dim3 grid, int block, size_t smem, std::function<void()> body);
 void yield();
 unsigned char* dyn_smem();
 void warp_barrier();
@@ -115,7 +120,22 @@ static inline unsigned __ballot_sync(unsigned, int pred) {
   simt_emu::warp_barrier();
   return m;
 }
+static inline unsigned __match_any_sync(unsigned, int v) {
+  simt_emu::State& s = simt_emu::st();
+  simt_emu::WarpState& w = s.warps[s.cur / 32];
+  w.xchg[s.cur % 32] = (uint64_t)(uint32_t)v;
+  simt_emu::warp_barrier();
+  unsigned m = 0;
+  int nl = (int)blockDim.x - (s.cur / 32) * 32;
+  if (nl > 32) nl = 32;
+  for (int i = 0; i < nl; i++)
+    if (w.xchg[i] == (uint64_t)(uint32_t)v) m |= 1u << i;
+  simt_emu::warp_barrier();
+  return m;
+}
+static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
 static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
+static inline long long clock64() { return 0; }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline double atomicAdd(double* p, double v) { double o = *p; *p += v; return o; }
@@ -154,6 +174,13 @@ static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
 static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.0f; return 0; }
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return 0; }
 enum { cudaLimitStackSize = 0 };
+enum { cudaEventDisableTiming = 2 };
+typedef void* cudaGraph_t;
+typedef void* cudaGraphExec_t;
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, int) { *e = nullptr; return 0; }
+static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, int) { return 0; }
+static inline cudaError_t cudaGraphExecDestroy(cudaGraphExec_t) { return 0; }
+static inline cudaError_t cudaGraphDestroy(cudaGraph_t) { return 0; }
 static inline cudaError_t cudaDeviceSetLimit(int, size_t) { return 0; }
 
 #endif  // SIMT_EMU_H_

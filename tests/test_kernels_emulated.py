@@ -36,3 +36,15 @@ def test_emulated_arena(emu_lib):
         ls.step(rng.randint(0, 5, size=ls.N * ls.A))
     ls.compare_state()
     ls.close()
+
+
+def test_emulated_chunked_launch(emu_lib, monkeypatch):
+    """The step is launched in slices of envs (MG_CHUNKS); slices must tile the batch exactly."""
+    monkeypatch.setenv("MG_CHUNKS", "3")
+    cfg, grid = SCENARIOS["tiny_truncating"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=7, seeds=np.arange(7) + 30, clib=emu_lib)
+    rng = np.random.RandomState(4)
+    for s in range(14):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+    ls.close()

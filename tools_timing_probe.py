@@ -1,0 +1,30 @@
+import os, sys, numpy as np, torch
+sys.path.insert(0, os.getcwd())
+from metta_b200.batch import Batch
+from metta_b200.builders import make_arena
+from metta_b200.lowering import lower_game_config
+from metta_b200.maps import arena_maps, build_pool
+N=int(sys.argv[1]) if len(sys.argv)>1 else 4096
+FLUSH=(sys.argv[2]=='flush') if len(sys.argv)>2 else True
+A,T=24,200
+cfg=make_arena(A); low=lower_game_config(cfg.game,62,62)
+pool=build_pool(low, arena_maps(low,256,seed=1234))
+b=Batch(low,pool,N)
+dev='cuda'
+obs=torch.zeros((N*A,T,3),dtype=torch.uint8,device=dev); term=torch.zeros(N*A,dtype=torch.uint8,device=dev); trunc=torch.zeros_like(term); rew=torch.zeros(N*A,dtype=torch.float32,device=dev)
+act=torch.randint(0,5,(N*A,),dtype=torch.int32).to(dev)
+b.set_buffers(obs.data_ptr(),term.data_ptr(),trunc.data_ptr(),rew.data_ptr(),act.data_ptr())
+b.reset((np.arange(N)+42).astype(np.uint32),(np.arange(N)%256).astype(np.int32))
+flush=torch.empty(256*1024*1024,dtype=torch.uint8,device=dev)
+for s in range(20):
+    act.copy_(torch.randint(0,5,(N*A,),dtype=torch.int32))
+    if FLUSH: flush.fill_(s)
+    torch.cuda.synchronize()
+    b.step(); torch.cuda.synchronize()
+env=b.read_env()
+sp=env['spare'].astype(np.float64)
+names=['stage(fold,load,prefetch)','shuffle','boxes+parallel','ordered','rest(regen,dmg,asm,rewards,wb)']
+tot=sp.sum(1)
+print('N',N,'flush',FLUSH); print('per-env total cycles: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f'%(tot.mean(),np.percentile(tot,50),np.percentile(tot,90),np.percentile(tot,99),tot.max()))
+for i,n in enumerate(names):
+    c=sp[:,i]; print('%-34s mean %8.0f p50 %8.0f p99 %8.0f max %8.0f'%(n,c.mean(),np.percentile(c,50),np.percentile(c,99),c.max()))
