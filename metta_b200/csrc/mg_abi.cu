@@ -18,6 +18,8 @@
 static thread_local std::string g_err;
 
 #define MG_MAX_CHUNKS 16
+// Dynamic shared memory of the step kernel: room for the config copy when it fits beside the static part.
+#define MG_CFG_SMEM_LIMIT (96 * 1024)
 #define MG_OK 0
 #define MG_ERR_ARG 1
 #define MG_ERR_CUDA 2
@@ -147,9 +149,10 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   uint8_t* d_pat = nullptr;
   int rc;
 #define TRY(x) if ((rc = (x)) != MG_OK) { return rc; }
-  TRY(dev_alloc(e, &d_cfg, (size_t)n_words));
+  TRY(dev_alloc(e, &d_cfg, (size_t)n_words + 4));
   CUDA_TRY(cudaMemcpy(d_cfg, cfg, sizeof(int32_t) * (size_t)n_words, cudaMemcpyHostToDevice));
   b.cfg = d_cfg;
+  b.cfg_words = (int32_t)n_words;
   std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
   TRY(dev_alloc(e, &d_pat, pat.size() + 64));
   CUDA_TRY(cudaMemcpy(d_pat, pat.data(), pat.size(), cudaMemcpyHostToDevice));
@@ -248,6 +251,12 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &e->d_mask, N));
   TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+#ifndef MG_SIMT_EMU
+  CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(sizeof(StepSmem<32>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
+  CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<MG_MAX_AGENTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(sizeof(StepSmem<MG_MAX_AGENTS>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
+#endif
   // slices of about 512 envs (128 CTAs of the step kernel, a little under one per SM)
   e->chunks = (num_envs + 511) / 512;
   if (e->chunks > 8) e->chunks = 8;
@@ -368,8 +377,13 @@ static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) { return l
 
 static int launch_step_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
   const int grid = (b.env_end - b.env_begin + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
-  if (b.A <= 32) { MG_LAUNCH(mg_step_kernel<32>, grid, MG_STEP_WARPS * 32, 0, s, b); }
-  else { MG_LAUNCH(mg_step_kernel<MG_MAX_AGENTS>, grid, MG_STEP_WARPS * 32, 0, s, b); }
+  int cfg_bytes = ((b.cfg_words + 3) / 4) * 16;
+  if (cfg_bytes > MG_CFG_SMEM_LIMIT) cfg_bytes = 0;
+  if (b.A <= 32) {
+    MG_LAUNCH(mg_step_kernel<32>, grid, MG_STEP_WARPS * 32, sizeof(StepSmem<32>) * MG_STEP_WARPS + (size_t)cfg_bytes, s, b, cfg_bytes);
+  } else {
+    MG_LAUNCH(mg_step_kernel<MG_MAX_AGENTS>, grid, MG_STEP_WARPS * 32, sizeof(StepSmem<MG_MAX_AGENTS>) * MG_STEP_WARPS + (size_t)cfg_bytes, s, b, cfg_bytes);
+  }
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   return MG_OK;
@@ -494,8 +508,22 @@ int mg_compute_observations(void* h, void* stream) {
   return launch_obs(e, (cudaStream_t)stream, nullptr);
 }
 
+// Is this host pointer page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory)? Then the DMA
+// engines can reach it directly and no staging copy is needed.
+static bool is_pinned_host(const void* p) {
+#ifdef MG_SIMT_EMU
+  (void)p;
+  return false;
+#else
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return attr.type == cudaMemoryTypeHost;
+#endif
+}
+
 // Host-buffer step: the call a numpy caller makes. actions i32 [N*A] in; obs, rewards, terminals,
-// truncations out. Copies go through pinned staging on the library's stream; returns when done.
+// truncations out. Page-locked caller buffers are used directly by the copy engines; pageable ones
+// go through the library's pinned staging buffer. Runs on the library's stream; returns when done.
 int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, uint8_t* terminals, uint8_t* truncations) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e || !actions || !obs || !rewards || !terminals || !truncations) return fail(MG_ERR_ARG, "mg_step_host: null pointer");
@@ -504,27 +532,33 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   MgBatch& b = e->b;
   const size_t NA = (size_t)b.num_envs * b.A;
   const size_t obs_bytes = NA * b.T * 3;
+  const bool direct = is_pinned_host(actions) && is_pinned_host(obs) && is_pinned_host(rewards) && is_pinned_host(terminals) &&
+                      is_pinned_host(truncations);
   const size_t off_act = 0, off_rew = off_act + NA * 4, off_term = off_rew + NA * 4, off_trunc = off_term + NA;
   const size_t off_obs = (off_trunc + NA + 255) & ~(size_t)255, total = off_obs + obs_bytes;
-  if (e->h_pinned_bytes < total) {
+  if (!direct && e->h_pinned_bytes < total) {
     if (e->h_pinned) cudaFreeHost(e->h_pinned);
     CUDA_TRY(cudaMallocHost((void**)&e->h_pinned, total));
     e->h_pinned_bytes = total;
   }
   cudaStream_t s = e->stream;
-  memcpy(e->h_pinned + off_act, actions, NA * 4);
-  CUDA_TRY(cudaMemcpyAsync((void*)b.actions, e->h_pinned + off_act, NA * 4, cudaMemcpyHostToDevice, s));
+  uint8_t* st = e->h_pinned;
+  const void* src_act = actions;
+  if (!direct) { memcpy(st + off_act, actions, NA * 4); src_act = st + off_act; }
+  CUDA_TRY(cudaMemcpyAsync((void*)b.actions, src_act, NA * 4, cudaMemcpyHostToDevice, s));
   int rc;
   TRY(mg_step(h, (void*)s));
-  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_obs, b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
-  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_rew, b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
-  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_term, b.terminals, NA, cudaMemcpyDeviceToHost, s));
-  CUDA_TRY(cudaMemcpyAsync(e->h_pinned + off_trunc, b.truncations, NA, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)rewards : (void*)(st + off_rew), b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)terminals : (void*)(st + off_term), b.terminals, NA, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)truncations : (void*)(st + off_trunc), b.truncations, NA, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaStreamSynchronize(s));
-  memcpy(obs, e->h_pinned + off_obs, obs_bytes);
-  memcpy(rewards, e->h_pinned + off_rew, NA * 4);
-  memcpy(terminals, e->h_pinned + off_term, NA);
-  memcpy(truncations, e->h_pinned + off_trunc, NA);
+  if (!direct) {
+    memcpy(obs, st + off_obs, obs_bytes);
+    memcpy(rewards, st + off_rew, NA * 4);
+    memcpy(terminals, st + off_term, NA);
+    memcpy(truncations, st + off_trunc, NA);
+  }
   return MG_OK;
 }
 

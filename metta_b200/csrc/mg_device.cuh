@@ -203,9 +203,24 @@ MG_DEVICE MG_NOINLINE int inv_update(EnvCtx& e, InvView& v, int item, int attemp
   return clamped_delta;
 }
 
+// The inventories that take part in an assembler use, without an array of views (arrays indexed at
+// run time live in per-thread local memory, whose lane-interleaved layout makes a single lane's
+// accesses miss L1 on every word): up to 8 agents as 8-bit indices packed in a u64, then chests.
+struct InvList {
+  uint64_t agents;
+  int n_agents, n_chests;
+  const uint16_t* chests;  // only with chest_search_distance > 0
+};
+MG_DEVICE inline int inv_list_size(const InvList& l) { return l.n_agents + l.n_chests; }
+MG_DEVICE inline InvView inv_list_view(const EnvCtx& e, const InvList& l, int i) {
+  if (i < l.n_agents) return agent_inv(e, (int)((l.agents >> (8 * i)) & 0xFFull));
+  return chest_inv(e, (int)l.chests[i - l.n_agents]);
+}
+
 // HasInventory::shared_update, has_inventory.cpp:7-74
 #define MG_MAX_SHARED 40
-MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, InvView* invs, int n, int item, int delta) {
+MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, const InvList& l, int item, int delta) {
+  const int n = inv_list_size(l);
   if (n == 0) return 0;
   int delta_remaining = delta;
   uint64_t active = n >= 64 ? ~0ull : ((1ull << n) - 1ull);  // inventories still to consider, in order
@@ -217,11 +232,12 @@ MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, InvView* invs, int n, int ite
     for (int i = 0; i < n; i++) {
       if (!((active >> i) & 1ull)) continue;
       ncur++;
+      InvView v = inv_list_view(e, l, i);
       bool now;
-      if (delta_remaining > 0) now = inv_free_space(invs[i], item) <= per;
-      else now = (int)invs[i].amt[item] <= -per;
+      if (delta_remaining > 0) now = inv_free_space(v, item) <= per;
+      else now = (int)v.amt[item] <= -per;
       if (now) {
-        delta_remaining -= inv_update(e, invs[i], item, per, false, 0);
+        delta_remaining -= inv_update(e, v, item, per, false, 0);
         num_remaining--;
         if (num_remaining > 0) per = delta_remaining / num_remaining;
       } else {
@@ -238,7 +254,8 @@ MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, InvView* invs, int n, int ite
   for (int i = n - 1; i >= 0; i--) {  // reverse order: earlier inventories get the remainder
     if (!((active >> i) & 1ull)) continue;
     int d = delta_remaining / cnt;
-    delta_remaining -= inv_update(e, invs[i], item, d, false, 0);
+    InvView v = inv_list_view(e, l, i);
+    delta_remaining -= inv_update(e, v, item, d, false, 0);
     cnt--;
   }
   return delta - delta_remaining;
@@ -395,97 +412,97 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   if (pi < 0) return false;
   const int32_t* p = proto_cfg(e.cfg, pi);
   bool clipped = (a->flags & MG_ASMF_CLIPPED) != 0;
-  ItemList in, out;
-  if (remaining > 0 && partial) {  // scale_protocol_for_partial_usage :427-453
-    uint32_t duration = a->cooldown_duration, elapsed = duration - remaining;
-    list_load(in, p + MG_PROTO_SCALED_INPUTS);
-    list_load(out, p + MG_PROTO_SCALED_OUTPUTS);
-    bool original_has_output = list_has_positive(out);
-    for (int i = 0; i < in.n; i++) in.val[i] = (int)(uint16_t)(((uint32_t)(uint16_t)in.val[i] * elapsed + duration - 1) / duration);
-    for (int i = 0; i < out.n; i++) out.val[i] = (int)(uint16_t)(((uint32_t)(uint16_t)out.val[i] * elapsed) / duration);
-    if (!list_has_positive(out) && original_has_output && !clipped) return false;
-  } else {
-    list_load(in, p + MG_PROTO_INPUTS);
-    list_load(out, p + MG_PROTO_OUTPUTS);
-  }
-  // get_surrounding_agents(&actor) :48-92: NW,N,NE,W,E,SW,S,SE restricted to valid cells, rotated to the actor
-  int pr[8], pc[8], npos = 0;
-  for (int i = -1; i <= 1; i++)
-    for (int j = -1; j <= 1; j++) {
-      if (i == 0 && j == 0) continue;
-      int rr = (int)a->r + i, cc = (int)a->c + j;
-      if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
-      pr[npos] = rr;
-      pc[npos] = cc;
-      npos++;
-    }
+  // scale_protocol_for_partial_usage :427-453. The scaled protocol is a rebuilt map: its lists are
+  // stored in that map's iteration order; amounts are scaled on the fly (inputs up, outputs down).
+  const bool scaled = remaining > 0 && partial;
+  const uint32_t duration = a->cooldown_duration, elapsed = duration - remaining;
+  const int32_t* lin = p + (scaled ? MG_PROTO_SCALED_INPUTS : MG_PROTO_INPUTS);
+  const int32_t* lout = p + (scaled ? MG_PROTO_SCALED_OUTPUTS : MG_PROTO_OUTPUTS);
+  const int n_in = lin[MG_LIST_N], n_out = lout[MG_LIST_N];
+#define MG_IN_AMOUNT(i) (scaled ? (int)(uint16_t)(((uint32_t)(uint16_t)lin[MG_LIST_VAL(i)] * elapsed + duration - 1) / duration) : (int)(uint16_t)lin[MG_LIST_VAL(i)])
+#define MG_OUT_AMOUNT(i) (scaled ? (int)(uint16_t)(((uint32_t)(uint16_t)lout[MG_LIST_VAL(i)] * elapsed) / duration) : (int)(uint16_t)lout[MG_LIST_VAL(i)])
+  bool has_output = false;
+  for (int i = 0; i < n_out; i++) has_output = has_output || MG_OUT_AMOUNT(i) > 0;
+  if (scaled && !has_output && p[MG_PROTO_HAS_OUTPUT] && !clipped) return false;
+  // get_surrounding_agents(&actor) :48-92: NW,N,NE,W,E,SW,S,SE restricted to valid cells, starting at the actor
+  const int ar = (int)a->r, ac = (int)a->c;
   int start = 0;
-  for (int i = 0; i < npos; i++)
-    if (pr[i] == e.ag[actor].r && pc[i] == e.ag[actor].c) { start = i; break; }
-  int sur[8], nsur = 0;
-  for (int k = 0; k < npos; k++) {
-    int i = start + k;
-    if (i >= npos) i -= npos;
-    uint16_t g = grid_at(e, pr[i], pc[i]);
-    if (MG_GRID_KIND(g) == MG_GK_AGENT) sur[nsur++] = MG_GRID_INDEX(g);
+  for (int k = 0; k < 8; k++) {
+    const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
+    if (rr == (int)e.ag[actor].r && cc == (int)e.ag[actor].c) start = k;
   }
-  InvView inputs[MG_MAX_SHARED];
-  int nin = 0;
-  for (int i = 0; i < nsur; i++) inputs[nin++] = agent_inv(e, sur[i]);
-  int dist = t[MG_ASM_CHEST_DISTANCE];
+  InvList inputs;
+  inputs.agents = 0; inputs.n_agents = 0; inputs.n_chests = 0; inputs.chests = nullptr;
+  for (int j = 0; j < 8; j++) {
+    const int k = (start + j) & 7;
+    const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
+    if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+    const uint16_t g = grid_at(e, rr, cc);
+    if (MG_GRID_KIND(g) == MG_GK_AGENT) inputs.agents |= (uint64_t)MG_GRID_INDEX(g) << (8 * inputs.n_agents++);
+  }
+  uint16_t chest_idx[MG_MAX_SHARED - 8];
+  const int dist = t[MG_ASM_CHEST_DISTANCE];
   if (dist > 0) {  // get_surrounding_chests :96-121
+    inputs.chests = chest_idx;
     for (int dr = -dist; dr <= dist; dr++)
       for (int dc = -dist; dc <= dist; dc++) {
         if (dr == 0 && dc == 0) continue;
-        int rr = (int)a->r + dr, cc = (int)a->c + dc;
+        const int rr = ar + dr, cc = ac + dc;
         if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
-        uint16_t g = grid_at(e, rr, cc);
-        if (MG_GRID_KIND(g) == MG_GK_CHEST && nin < MG_MAX_SHARED) inputs[nin++] = chest_inv(e, MG_GRID_INDEX(g));
+        const uint16_t g = grid_at(e, rr, cc);
+        if (MG_GRID_KIND(g) == MG_GK_CHEST && inputs.n_chests < MG_MAX_SHARED - 8) chest_idx[inputs.n_chests++] = (uint16_t)MG_GRID_INDEX(g);
       }
   }
-  for (int i = 0; i < in.n; i++) {  // can_afford_protocol :124-137 (u16 accumulation)
+  const int nin = inv_list_size(inputs);
+  for (int i = 0; i < n_in; i++) {  // can_afford_protocol :124-137 (u16 accumulation)
+    const int item = lin[MG_LIST_ITEM(i)];
     uint32_t total = 0;
-    for (int k = 0; k < nin; k++) total = (total + inputs[k].amt[in.item[i]]) & 0xFFFFu;
-    if (total < (uint32_t)(uint16_t)in.val[i]) return false;
+    for (int k = 0; k < nin; k++) total = (total + inv_list_view(e, inputs, k).amt[item]) & 0xFFFFu;
+    if (total < (uint32_t)MG_IN_AMOUNT(i)) return false;
   }
-  InvView outputs[8];  // get_output_inventories :198-223
-  int nout = 0;
-  int nvibes = p[MG_PROTO_NUM_VIBES];
+  InvList outputs;  // get_output_inventories :198-223
+  outputs.agents = 0; outputs.n_agents = 0; outputs.n_chests = 0; outputs.chests = nullptr;
+  const int nvibes = p[MG_PROTO_NUM_VIBES];
   if (nvibes > 1) {
     uint32_t used = 0;  // which of the protocol's vibe slots are taken
-    for (int i = 0; i < nsur && nout < nvibes; i++) {
-      int v = e.ag[sur[i]].vibe;
+    for (int i = 0; i < inputs.n_agents && outputs.n_agents < nvibes; i++) {
+      const int ai = (int)((inputs.agents >> (8 * i)) & 0xFFull);
+      const int v = e.ag[ai].vibe;
       if (v == 0) continue;
-      for (int s = 0; s < nvibes; s++) {
-        if (!((used >> s) & 1u) && p[MG_PROTO_VIBES + s] == v) {
-          used |= 1u << s;
-          outputs[nout++] = agent_inv(e, sur[i]);
+      for (int sidx = 0; sidx < nvibes; sidx++) {
+        if (!((used >> sidx) & 1u) && p[MG_PROTO_VIBES + sidx] == v) {
+          used |= 1u << sidx;
+          outputs.agents |= (uint64_t)ai << (8 * outputs.n_agents++);
           break;
         }
       }
     }
   }
-  if (nout == 0) outputs[nout++] = agent_inv(e, actor);
+  if (outputs.n_agents == 0) { outputs.agents = (uint64_t)actor; outputs.n_agents = 1; }
   bool can_receive = true;  // can_receive_output :143-171
-  if (list_has_positive(out)) {
+  if (has_output) {
     can_receive = false;
-    for (int i = 0; i < out.n && !can_receive; i++) {
-      if (out.val[i] <= 0) continue;
+    for (int i = 0; i < n_out && !can_receive; i++) {
+      if (MG_OUT_AMOUNT(i) <= 0) continue;
       uint32_t free_total = 0;
-      for (int k = 0; k < nout; k++) free_total = (free_total + (uint32_t)inv_free_space(outputs[k], out.item[i])) & 0xFFFFu;
+      for (int k = 0; k < outputs.n_agents; k++)
+        free_total = (free_total + (uint32_t)inv_free_space(inv_list_view(e, outputs, k), lout[MG_LIST_ITEM(i)])) & 0xFFFFu;
       if (free_total >= 1) can_receive = true;
     }
   }
   if (!can_receive && !clipped) return false;
-  for (int i = 0; i < in.n; i++) shared_update(e, inputs, nin, in.item[i], -(int)(uint16_t)in.val[i]);
-  for (int i = 0; i < out.n; i++) {  // give_output_for_protocol :174-184
-    int distributed = shared_update(e, outputs, nout, out.item[i], (int)(uint16_t)out.val[i]);
+  for (int i = 0; i < n_in; i++) shared_update(e, inputs, lin[MG_LIST_ITEM(i)], -MG_IN_AMOUNT(i));
+  for (int i = 0; i < n_out; i++) {  // give_output_for_protocol :174-184
+    const int item = lout[MG_LIST_ITEM(i)];
+    const int distributed = shared_update(e, outputs, item, MG_OUT_AMOUNT(i));
     if (distributed > 0) {
       // integer-valued float counter: the sum does not depend on the order of the additions
-      if (e.concurrent) atomicAdd(&e.gstats[MG_GS_ASM_CREATED + out.item[i]], (float)distributed);
-      else e.gstats[MG_GS_ASM_CREATED + out.item[i]] += (float)distributed;
+      if (e.concurrent) atomicAdd(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
+      else e.gstats[MG_GS_ASM_CREATED + item] += (float)distributed;
     }
   }
+#undef MG_IN_AMOUNT
+#undef MG_OUT_AMOUNT
   a->cooldown_duration = (uint32_t)(uint16_t)p[MG_PROTO_COOLDOWN];
   a->cooldown_end = e.current_step + a->cooldown_duration;
   if (clipped) {  // become_unclipped :581-590

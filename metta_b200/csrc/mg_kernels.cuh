@@ -18,18 +18,22 @@
 // -DMG_TIMING: per-env cycle counts of the step kernel's phases in EnvRec::spare (tuning builds only)
 #ifdef MG_TIMING
 #define MG_TICK(i) do { const long long now__ = clock64(); tick_acc[i] += (uint32_t)(now__ - tick_last); tick_last = now__; } while (0)
+#define MG_SM_TICK(sm, i) do { if (lane == 0) { const long long now__ = clock64(); (sm).er.spare[i] += (uint32_t)(now__ - (sm).tick_last); (sm).tick_last = now__; } } while (0)
 #else
 #define MG_TICK(i) do { } while (0)
+#define MG_SM_TICK(sm, i) do { } while (0)
 #endif
 
-#define MG_STEP_WARPS 4    /* envs per CTA in the reset/step kernels */
+#ifndef MG_STEP_WARPS
+#define MG_STEP_WARPS 8    /* envs per CTA in the reset/step kernels: they share one shared-memory copy of the config */
+#endif
 #define MG_OBS_WARPS 8     /* agents per CTA in the observation kernel */
 #define MG_MAX_AGENTS 64   /* agents per env that fit the shared-memory staging */
 #ifndef MG_OBS_MIN_CTAS
 #define MG_OBS_MIN_CTAS 8 /* CTAs of the observation kernel resident per SM (measured: 4 -> 135 us, 6 -> 111 us, 8 -> 103 us) */
 #endif
 #ifndef MG_STEP_MIN_CTAS
-#define MG_STEP_MIN_CTAS 8 /* CTAs of the step kernel resident per SM: all 1024 CTAs of 4096 envs in one wave */
+#define MG_STEP_MIN_CTAS 3 /* CTAs of the step kernel resident per SM: all 1024 CTAs of 4096 envs in one wave */
 #endif
 
 template <int MAXA>
@@ -42,6 +46,11 @@ struct StepSmem {
   uint8_t order[MAXA];
   int32_t scratch[2 * MG_RES_STRIDE + 8];
   uint32_t rngbuf[32];
+  uint32_t intent[MAXA];  // per agent: bit 0 = act in the parallel pass, bits 8..15 action kind, 16..31 argument
+  uint32_t ordered_mask;
+  long long tick_last;
+  EnvRec er;
+  EnvCtx ctx;  // warp-uniform; lives here so that passing it to out-of-line functions costs no stack traffic
 };
 
 MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
@@ -70,7 +79,7 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
 // tokens_written / tokens_dropped / tokens_free_space (mettagrid_c.cpp:552-554) are produced by the
 // observation kernel as integer counts per agent and folded into the float game stats here, agent
 // by agent, so that the float additions happen in the reference's order.
-MG_DEVICE inline void fold_token_stats_warp(const MgBatch& b, int env, int lane) {
+MG_DEVICE MG_NOINLINE void fold_token_stats_warp(const MgBatch& b, int env, int lane) {
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
   float* gs = b.game_stats + (size_t)env * b.GS;
   // All counts are small integers. While a total stays below 2^24 every float addition is exact, so
@@ -111,7 +120,7 @@ MG_DEVICE inline void fold_token_stats_warp(const MgBatch& b, int env, int lane)
 
 // Cache, on every assembler that has an agent next to it, the protocol observers will see this
 // step (see sink_object). One agent per lane; duplicates write identical values.
-MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
+MG_DEVICE MG_NOINLINE void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
   if (!b.cfg[MGC_HAS_VIBE_ASM] || !b.cfg[MGC_PROTOCOL_DETAILS_OBS]) return;
   for (int ai = lane; ai < e.A; ai += 32) {
     const int r = e.ag[ai].r, c = e.ag[ai].c;
@@ -132,7 +141,7 @@ MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, in
 }
 
 // What observers will see of every assembler this step (see write_asm_tokens).
-MG_DEVICE inline void write_all_asm_tokens_warp(const MgBatch& b, int env, int lane, int n_asm, uint32_t current_step) {
+MG_DEVICE MG_NOINLINE void write_all_asm_tokens_warp(const MgBatch& b, int env, int lane, int n_asm, uint32_t current_step) {
   const AsmRec* asms = b.asms + (size_t)env * b.max_asm;
   for (int i = lane; i < n_asm; i += 32) write_asm_tokens(b, &asms[i], current_step, token_record(b, env, MG_GK_ASM, (uint32_t)i));
   __syncwarp();
@@ -140,7 +149,7 @@ MG_DEVICE inline void write_all_asm_tokens_warp(const MgBatch& b, int env, int l
 
 // One observation pass that only counts tokens (nothing is written): the reference runs such
 // passes on buffers nobody reads (see reset_env_warp), but their token counts stay in the stats.
-MG_DEVICE inline void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step) {
+MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step) {
   __syncwarp();
   for (int ai = 0; ai < b.A; ai++) {
     const int attempted = obs_count_agent_warp(b, env, ai, lane, current_step);
@@ -157,7 +166,7 @@ MG_DEVICE inline void count_observation_pass_warp(const MgBatch& b, int env, int
 // ---------------------------------------------------------------- reset
 // MettaGrid::MettaGrid + _init_grid + Clipper ctor (mettagrid_c.cpp:46-245, clipper.hpp:35-91),
 // from a map that the host already split into per-kind object tables (metta_b200/maps.py).
-MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er) {
+MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er) {
   const int32_t* cfg = b.cfg;
   const int map = er.map_idx;
   // grid: 16-byte copies (grid_stride is a multiple of 8 cells)
@@ -310,7 +319,7 @@ MG_DEVICE inline void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec
 }
 
 // Sum a finished episode into the batch accumulators before its state is overwritten.
-MG_DEVICE inline void accumulate_episode_warp(const MgBatch& b, int env, int lane) {
+MG_DEVICE MG_NOINLINE void accumulate_episode_warp(const MgBatch& b, int env, int lane) {
   const AgentRec* agents = b.agents + (size_t)env * b.A;
   const float* astats = b.agent_stats + (size_t)env * b.A * b.S;
   const float* gstats = b.game_stats + (size_t)env * b.GS;
@@ -329,7 +338,7 @@ MG_DEVICE inline void accumulate_episode_warp(const MgBatch& b, int env, int lan
     if (gstats[s] != 0.0f) atomicAdd(&b.episode_accum[2 + b.S + s], (double)gstats[s]);
 }
 
-MG_GLOBAL void mg_reset_kernel(MgBatch b, const uint8_t* mask) {
+MG_GLOBAL void mg_reset_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * MG_STEP_WARPS + (threadIdx.x >> 5);
   if (env >= b.num_envs) return;
@@ -345,24 +354,132 @@ MG_GLOBAL void mg_reset_kernel(MgBatch b, const uint8_t* mask) {
   if (lane == 0) b.env[env] = er;
 }
 
+// Agent::check_and_apply_damage for every agent of the env (agent.cpp:134-177), in agent order,
+// drawing from the env's generator.
+MG_DEVICE MG_NOINLINE void damage_pass_warp(const MgBatch& b, EnvCtx& e, int32_t* scratch, MtStream& rs, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  for (int base = 0; base < A; base += 32) {
+    const int ai = base + lane;
+    bool met = false;
+    if (ai < A) {
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + e.ag[ai].group * MG_GRP_WORDS;
+      if (grp[MG_GRP_DAMAGE_ENABLED]) {
+        met = true;
+        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
+        for (int i = 0; i < th[MG_LIST_N]; i++)
+          if ((int)e.ag[ai].amt[th[MG_LIST_ITEM(i)]] < (th[MG_LIST_VAL(i)] & 0xFFFF)) { met = false; break; }
+      }
+    }
+    uint32_t todo = __ballot_sync(MG_FULL_MASK, met);
+    while (todo) {
+      const int who = base + (__ffs((int)todo) - 1);
+      todo &= todo - 1u;
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + e.ag[who].group * MG_GRP_WORDS;
+      if (lane == 0) {
+        InvView iv = agent_inv(e, who);
+        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
+        for (int i = 0; i < th[MG_LIST_N]; i++) inv_update(e, iv, th[MG_LIST_ITEM(i)], -th[MG_LIST_VAL(i)], false, 0);
+        const int32_t* rs = grp + MG_GRP_DAMAGE_RESOURCES;
+        int n = 0;
+        for (int i = 0; i < rs[MG_LIST_N]; i++) {
+          const int removable = (int)e.ag[who].amt[rs[MG_LIST_ITEM(i)]] - rs[MG_LIST_VAL(i)];
+          if (removable > 0) { scratch[1 + n] = rs[MG_LIST_ITEM(i)]; scratch[1 + MG_RES_STRIDE + n] = removable; n++; }
+        }
+        scratch[0] = n;
+      }
+      __syncwarp();
+      const int n = scratch[0];
+      if (n > 0) {
+        int weights[MG_RES_STRIDE];
+        for (int i = 0; i < n; i++) weights[i] = scratch[1 + MG_RES_STRIDE + i];
+        const int sel = discrete_pick_warp(rs, lane, weights, n);
+        if (lane == 0) {
+          InvView iv = agent_inv(e, who);
+          const int item = scratch[1 + sel];
+          inv_update(e, iv, item, -1, false, 0);
+          *agent_stat(e, who, MG_AS_DAMAGE_ITEMS_LOST) += 1.0f;
+          *agent_stat(e, who, MG_AS_DAMAGED + item) += 1.0f;
+        }
+      }
+      if (lane == 0) *agent_stat(e, who, MG_AS_DAMAGE_TRIGGERED) += 1.0f;
+      __syncwarp();
+    }
+  }
+
+}
+
+// Clipper::maybe_clip_new_assembler (clipper.hpp:203-238) with the clipper's private generator.
+MG_DEVICE MG_NOINLINE void clipper_step_warp(const MgBatch& b, EnvCtx& e, int32_t* scratch, uint32_t& clip_rng_idx, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int env = e.env;
+  {
+    const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
+    uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
+    const uint32_t period = (uint32_t)cc[MG_CLIP_PERIOD];
+    MtStream cs = mt_stream(cmt, clip_rng_idx);
+    bool fire;
+    if (period == 0u) {
+      // uniform_int_distribution<uint32_t>(1, 0): the 64-bit range wraps, libstdc++ composes two draws
+      // (uniform_int_dist.h:331-356) and truncates: the result is 1 only when the second word is 0.
+      (void)mt_next_warp(cs, lane);
+      fire = mt_next_warp(cs, lane) == 0u;
+    } else {
+      fire = uniform_below_warp(cs, lane, period) == 0u;
+    }
+    if (fire) {
+      if (lane == 0) {
+        int nun = 0;
+        uint32_t total = 0;
+        for (int i = 0; i < e.n_asm; i++) {
+          nun += (e.asms[i].flags & MG_ASMF_UNCLIPPED) ? 1 : 0;
+          if (e.asms[i].flags & MG_ASMF_BORDER) total += e.asms[i].infection_weight;
+        }
+        scratch[0] = nun;
+        scratch[1] = (int32_t)total;
+      }
+      __syncwarp();
+      const int nun = scratch[0];
+      const uint32_t total = (uint32_t)scratch[1];
+      __syncwarp();
+      if (nun > 0) {
+        int pick = -1;
+        if (total == 0u) {
+          uint32_t k = uniform_below_warp(cs, lane, (uint32_t)nun);
+          for (int i = 0; i < e.n_asm && pick < 0; i++)
+            if (e.asms[i].flags & MG_ASMF_UNCLIPPED) { if (k == 0u) pick = i; else k--; }
+        } else {
+          uint32_t rw = uniform_below_warp(cs, lane, total) + 1u;
+          for (int i = 0; i < e.n_asm && pick < 0; i++) {
+            if (!(e.asms[i].flags & MG_ASMF_BORDER)) continue;
+            if (rw <= e.asms[i].infection_weight) pick = i; else rw -= e.asms[i].infection_weight;
+          }
+        }
+        if (pick >= 0) {
+          const uint32_t sel = uniform_below_warp(cs, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+          if (lane == 0) clip_assembler(e, &e.asms[pick], sel);
+          __syncwarp();
+        }
+      }
+    }
+    clip_rng_idx = cs.idx;
+  }
+
+}
+
 // ---------------------------------------------------------------- step
-// MAXA: agents per env the shared-memory staging is sized for (32 or MG_MAX_AGENTS)
+// The step kernel is written as a short sequence of out-of-line phases that communicate through
+// the warp's shared-memory block (StepSmem): each phase gets its own register allocation, so the
+// kernel needs no spills (as one function it wanted 210 registers per thread; spill traffic to local
+// memory was three times the real data traffic, see profiles/r01e). All phases are called by the
+// full warp.
+
+// Phase 1: bring the env in (and start a new episode first if the last one ended).
 template <int MAXA>
-MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_kernel(MgBatch b) {
-  MG_SHARED StepSmem<MAXA> smem[MG_STEP_WARPS];
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
-  if (env >= b.env_end) return;
-  StepSmem<MAXA>& sm = smem[warp];
+MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
   const int32_t* cfg = b.cfg;
   const int A = b.A;
   EnvRec er = b.env[env];
-#ifdef MG_TIMING
-  long long tick_last = clock64();
-  uint32_t tick_acc[5] = {0, 0, 0, 0, 0};
-#endif
-
   // ---- bring the env in. Every load that does not depend on another is issued before the first
   // use, so the whole stage costs about one HBM round trip instead of one per array: agent records
   // and their 16 per-step stat slots (16-byte loads), actions, the pending token counts of the last
@@ -467,20 +584,36 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L1(b.game_stats + (size_t)env * b.GS + lane * 32);
   er.current_step += 1;
-  EnvCtx e = make_ctx(b, env, sm.ag, er);
-  e.hot = sm.hot;
-  e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
+  if (lane == 0) sm.er = er;
+  EnvCtx& e = sm.ctx;
   {
     // which resources each action kind requires / consumes: most configs name none or one, so the
     // per-action checks iterate set bits instead of all resources
     const int32_t* res = cfg + cfg[MGC_OFF_ACTION_RES];
+    uint32_t rqm[3], cnm[3];
     for (int k = 0; k < 3; k++) {
       const bool rq = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_REQUIRED + lane] & 0xFFFF) != 0;
       const bool cn = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_CONSUMED + lane] & 0xFFFF) != 0;
-      e.req_mask[k] = __ballot_sync(MG_FULL_MASK, rq);
-      e.con_mask[k] = __ballot_sync(MG_FULL_MASK, cn);
+      rqm[k] = __ballot_sync(MG_FULL_MASK, rq);
+      cnm[k] = __ballot_sync(MG_FULL_MASK, cn);
     }
+    if (lane == 0) {
+      e = make_ctx(b, env, sm.ag, er);
+      e.hot = sm.hot;
+      e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
+      for (int k = 0; k < 3; k++) { e.req_mask[k] = rqm[k]; e.con_mask[k] = cnm[k]; }
+    }
+    __syncwarp();
   }
+}
+
+// Phase 2: processing order, every agent's intent, and who may act independently of the order.
+// Leaves order[], intent[] and ordered_mask in shared memory.
+template <int MAXA>
+MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  EnvCtx& e = sm.ctx;
   uint32_t* mt = b.rng + (size_t)env * MT_N;
   const int nact = cfg[MGC_NUM_ACTIONS];
   const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
@@ -508,12 +641,12 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
       }
     }
   }
-  MG_TICK(0);
   // random processing order (mettagrid_c.cpp:591-593); the words it needs are fetched in one go
-  MtStream rs = mt_stream(mt, er.rng_idx);
+  MtStream rs = mt_stream(mt, sm.er.rng_idx);
   mt_prefetch_warp(rs, sm.rngbuf, lane);
   std_shuffle_fast_warp(rs, lane, sm.order, A, reinterpret_cast<uint32_t*>(sm.scratch));
 
+  if (lane == 0) sm.er.rng_idx = rs.idx;
   // out-of-range actions: counted once per priority pass, two passes (mettagrid_c.cpp:599-608)
   for (int ai = lane; ai < A; ai += 32) {
     const int a = sm.action[ai];
@@ -524,7 +657,6 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   }
   __syncwarp();
 
-  MG_TICK(1);
   // ---- which agents can act independently of the processing order?
   // An action touches the mover's cell and the cell it moves into; using an assembler touches the
   // agents standing in the 3x3 block around it (they pay the inputs). Agents stand on distinct
@@ -577,19 +709,38 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
     __syncwarp();
     if ((((uint32_t)sm.scratch[0]) >> lane) & 1u) ordered = true;
     ordered_mask = __ballot_sync(MG_FULL_MASK, ordered && lane < A);
-    if (lane < A && my_valid && !ordered) {
-      e.concurrent = true;
-      const bool ok = handle_action(e, lane, my_kind, my_arg);
-      e.concurrent = false;
-      sm.success[lane] = ok ? 1 : 0;
-      if (ok) sm.executed[lane] = sm.action[lane];
-    }
+    if (lane < A) sm.intent[lane] = (my_valid && !ordered) ? (1u | ((uint32_t)my_kind << 8) | ((uint32_t)(my_arg & 0xFFFF) << 16)) : 0u;
   } else {
     ordered_mask = 0xFFFFFFFFu;
   }
+  if (lane == 0) sm.ordered_mask = ordered_mask;
   __syncwarp();
 
-  MG_TICK(2);
+}
+
+// Phase 3: the actions. Order-independent agents one per lane, then the ordered pass on one lane.
+template <int MAXA>
+MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  EnvCtx& e = sm.ctx;
+  const int nact = cfg[MGC_NUM_ACTIONS];
+  const int32_t* acts = cfg + cfg[MGC_OFF_ACTIONS];
+  const uint32_t ordered_mask = sm.ordered_mask;
+  if (A <= 32) {
+    if (lane == 0) e.concurrent = true;
+    __syncwarp();
+    const uint32_t intent = lane < A ? sm.intent[lane] : 0u;
+    if (intent & 1u) {
+      const bool ok = handle_action(e, lane, (int)((intent >> 8) & 0xFFu), (int)(intent >> 16));
+      sm.success[lane] = ok ? 1 : 0;
+      if (ok) sm.executed[lane] = sm.action[lane];
+    }
+    __syncwarp();
+    if (lane == 0) e.concurrent = false;
+    __syncwarp();
+  }
+  MG_SM_TICK(sm, 2);
   // the ordered action pass: later agents see what earlier agents did
   if (lane == 0 && ordered_mask != 0u) {
     for (int k = 0; k < A; k++) {
@@ -603,8 +754,18 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
     }
   }
   __syncwarp();
+  MG_SM_TICK(sm, 3);
+}
 
-  MG_TICK(3);
+// Phase 4: what happens after the actions: regeneration, damage, clipper, assembler views.
+template <int MAXA>
+MG_DEVICE MG_NOINLINE void step_phase_post(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  EnvCtx& e = sm.ctx;
+  EnvRec& er = sm.er;
+  uint32_t* mt = b.rng + (size_t)env * MT_N;
+  MtStream rs = mt_stream(mt, er.rng_idx);
   // inventory regeneration (mettagrid_c.cpp:625-640): independent per agent
   const uint32_t regen = (uint32_t)cfg[MGC_REGEN_INTERVAL];
   if (regen > 0u && er.current_step % regen == 0u) {
@@ -616,105 +777,12 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   bool any_damage = false;
   for (int gidx = 0; gidx < cfg[MGC_NUM_GROUPS]; gidx++)
     any_damage = any_damage || cfg[cfg[MGC_OFF_GROUPS] + gidx * MG_GRP_WORDS + MG_GRP_DAMAGE_ENABLED] != 0;
-  for (int base = 0; any_damage && base < A; base += 32) {
-    const int ai = base + lane;
-    bool met = false;
-    if (ai < A) {
-      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
-      if (grp[MG_GRP_DAMAGE_ENABLED]) {
-        met = true;
-        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
-        for (int i = 0; i < th[MG_LIST_N]; i++)
-          if ((int)sm.ag[ai].amt[th[MG_LIST_ITEM(i)]] < (th[MG_LIST_VAL(i)] & 0xFFFF)) { met = false; break; }
-      }
-    }
-    uint32_t todo = __ballot_sync(MG_FULL_MASK, met);
-    while (todo) {
-      const int who = base + (__ffs((int)todo) - 1);
-      todo &= todo - 1u;
-      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[who].group * MG_GRP_WORDS;
-      if (lane == 0) {
-        InvView iv = agent_inv(e, who);
-        const int32_t* th = grp + MG_GRP_DAMAGE_THRESHOLD;
-        for (int i = 0; i < th[MG_LIST_N]; i++) inv_update(e, iv, th[MG_LIST_ITEM(i)], -th[MG_LIST_VAL(i)], false, 0);
-        const int32_t* rs = grp + MG_GRP_DAMAGE_RESOURCES;
-        int n = 0;
-        for (int i = 0; i < rs[MG_LIST_N]; i++) {
-          const int removable = (int)sm.ag[who].amt[rs[MG_LIST_ITEM(i)]] - rs[MG_LIST_VAL(i)];
-          if (removable > 0) { sm.scratch[1 + n] = rs[MG_LIST_ITEM(i)]; sm.scratch[1 + MG_RES_STRIDE + n] = removable; n++; }
-        }
-        sm.scratch[0] = n;
-      }
-      __syncwarp();
-      const int n = sm.scratch[0];
-      if (n > 0) {
-        int weights[MG_RES_STRIDE];
-        for (int i = 0; i < n; i++) weights[i] = sm.scratch[1 + MG_RES_STRIDE + i];
-        const int sel = discrete_pick_warp(rs, lane, weights, n);
-        if (lane == 0) {
-          InvView iv = agent_inv(e, who);
-          const int item = sm.scratch[1 + sel];
-          inv_update(e, iv, item, -1, false, 0);
-          *agent_stat(e, who, MG_AS_DAMAGE_ITEMS_LOST) += 1.0f;
-          *agent_stat(e, who, MG_AS_DAMAGED + item) += 1.0f;
-        }
-      }
-      if (lane == 0) *agent_stat(e, who, MG_AS_DAMAGE_TRIGGERED) += 1.0f;
-      __syncwarp();
-    }
-  }
-
+  if (any_damage) damage_pass_warp(b, e, sm.scratch, rs, lane);
   // clipper (clipper.hpp:203-238): draws from its private rng copy
   if (b.has_clipper) {
-    const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
-    uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
-    const uint32_t period = (uint32_t)cc[MG_CLIP_PERIOD];
-    MtStream cs = mt_stream(cmt, er.clip_rng_idx);
-    bool fire;
-    if (period == 0u) {
-      // uniform_int_distribution<uint32_t>(1, 0): the 64-bit range wraps, libstdc++ composes two draws
-      // (uniform_int_dist.h:331-356) and truncates: the result is 1 only when the second word is 0.
-      (void)mt_next_warp(cs, lane);
-      fire = mt_next_warp(cs, lane) == 0u;
-    } else {
-      fire = uniform_below_warp(cs, lane, period) == 0u;
-    }
-    if (fire) {
-      if (lane == 0) {
-        int nun = 0;
-        uint32_t total = 0;
-        for (int i = 0; i < e.n_asm; i++) {
-          nun += (e.asms[i].flags & MG_ASMF_UNCLIPPED) ? 1 : 0;
-          if (e.asms[i].flags & MG_ASMF_BORDER) total += e.asms[i].infection_weight;
-        }
-        sm.scratch[0] = nun;
-        sm.scratch[1] = (int32_t)total;
-      }
-      __syncwarp();
-      const int nun = sm.scratch[0];
-      const uint32_t total = (uint32_t)sm.scratch[1];
-      __syncwarp();
-      if (nun > 0) {
-        int pick = -1;
-        if (total == 0u) {
-          uint32_t k = uniform_below_warp(cs, lane, (uint32_t)nun);
-          for (int i = 0; i < e.n_asm && pick < 0; i++)
-            if (e.asms[i].flags & MG_ASMF_UNCLIPPED) { if (k == 0u) pick = i; else k--; }
-        } else {
-          uint32_t rw = uniform_below_warp(cs, lane, total) + 1u;
-          for (int i = 0; i < e.n_asm && pick < 0; i++) {
-            if (!(e.asms[i].flags & MG_ASMF_BORDER)) continue;
-            if (rw <= e.asms[i].infection_weight) pick = i; else rw -= e.asms[i].infection_weight;
-          }
-        }
-        if (pick >= 0) {
-          const uint32_t sel = uniform_below_warp(cs, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
-          if (lane == 0) clip_assembler(e, &e.asms[pick], sel);
-          __syncwarp();
-        }
-      }
-    }
-    er.clip_rng_idx = cs.idx;
+    uint32_t cidx = er.clip_rng_idx;
+    clipper_step_warp(b, e, sm.scratch, cidx, lane);
+    if (lane == 0) er.clip_rng_idx = cidx;
   }
 
   update_protocol_cache_warp(b, e, lane);
@@ -722,6 +790,17 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   // clipper), all assembler records are refreshed; otherwise assembler_on_use already did it
   if (cfg[MGC_HAS_VIBE_ASM]) write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);
 
+  if (lane == 0) er.rng_idx = rs.idx;
+  __syncwarp();
+}
+
+// Phase 5: rewards, flags, what observers will see, write-back.
+template <int MAXA>
+MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
+  const int32_t* cfg = b.cfg;
+  const int A = b.A;
+  EnvCtx& e = sm.ctx;
+  EnvRec er = sm.er;
   // rewards, episode totals, truncation (mettagrid_c.cpp:655-677) and the write-back
   const uint32_t max_steps = (uint32_t)cfg[MGC_MAX_STEPS];
   bool term = false, trunc = false;
@@ -761,17 +840,57 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
       *reinterpret_cast<uint4*>(gst + (size_t)ai * b.S + q * 4) = reinterpret_cast<const uint4*>(sm.hot)[i];
     }
   }
-  er.rng_idx = rs.idx;
-  MG_TICK(4);
-#ifdef MG_TIMING
-  for (int i = 0; i < 5; i++) er.spare[i] = tick_acc[i];
-#endif
   if (lane == 0) b.env[env] = er;
+}
+
+// MAXA: agents per env the shared-memory staging is sized for (32 or MG_MAX_AGENTS)
+template <int MAXA>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_kernel(const MG_GRID_CONSTANT MgBatch b_param, int cfg_bytes_in_smem) {
+  // dynamic shared memory: [StepSmem per warp][config copy]
+  MG_SHARED MgBatch batch_s;  // the launch parameters with cfg redirected to the shared-memory copy
+  MG_DYN_SMEM(dyn_smem);
+  StepSmem<MAXA>* smem = reinterpret_cast<StepSmem<MAXA>*>(dyn_smem);
+  unsigned char* cfg_smem = dyn_smem + sizeof(StepSmem<MAXA>) * MG_STEP_WARPS;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  // The rules consult the lowered config constantly (dependent lookups: section offset -> record ->
+  // field). From global memory those loads miss L1 most of the time here (the per-env state streams
+  // through it), so each CTA first copies the config next to its envs; every lookup is then a
+  // shared-memory access. Configs too large for the launch's dynamic shared memory stay in HBM/L2.
+  const bool cfg_fits = cfg_bytes_in_smem >= b_param.cfg_words * 4;
+  if (cfg_fits) {
+    const uint4* src = reinterpret_cast<const uint4*>(b_param.cfg);
+    uint4* dst = reinterpret_cast<uint4*>(cfg_smem);
+    for (int i = threadIdx.x; i < (b_param.cfg_words + 3) / 4; i += blockDim.x) dst[i] = src[i];
+  }
+  if (threadIdx.x == 0) {
+    batch_s = b_param;
+    if (cfg_fits) batch_s.cfg = reinterpret_cast<const int32_t*>(cfg_smem);
+  }
+  __syncthreads();
+  const MgBatch& b = batch_s;
+  const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
+  if (env >= b.env_end) return;
+  StepSmem<MAXA>& sm = smem[warp];
+#ifdef MG_TIMING
+  if (lane == 0) sm.tick_last = clock64();
+#endif
+  step_phase_load<MAXA>(b, sm, env, lane);
+#ifdef MG_TIMING
+  if (lane == 0) for (int i = 0; i < 5; i++) sm.er.spare[i] = 0;
+#endif
+  MG_SM_TICK(sm, 0);
+  step_phase_decide<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 1);
+  step_phase_act<MAXA>(b, sm, lane);
+  step_phase_post<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 4);
+  step_phase_finish<MAXA>(b, sm, env, lane);
 }
 
 // ---------------------------------------------------------------- observations
 template <int CPL>
-MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(MgBatch b, const uint8_t* mask) {
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -813,7 +932,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
 }
 
 // Folds pending token counts so that game stats can be read out (mg_read).
-MG_GLOBAL void mg_fold_kernel(MgBatch b) {
+MG_GLOBAL void mg_fold_kernel(const MG_GRID_CONSTANT MgBatch b) {
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * MG_STEP_WARPS + (threadIdx.x >> 5);
   if (env >= b.num_envs) return;
@@ -821,7 +940,7 @@ MG_GLOBAL void mg_fold_kernel(MgBatch b) {
 }
 
 // Agent::set_inventory (agent.cpp:54-72) for one agent; a test/tooling entry point of the reference API.
-MG_GLOBAL void mg_set_inventory_kernel(MgBatch b, int env, int ai, const int32_t* items, const int32_t* amounts, int n) {
+MG_GLOBAL void mg_set_inventory_kernel(const MG_GRID_CONSTANT MgBatch b, int env, int ai, const int32_t* items, const int32_t* amounts, int n) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   EnvRec er = b.env[env];
   AgentRec* agents = b.agents + (size_t)env * b.A;

@@ -23,6 +23,7 @@
 #define MG_LAUNCH_BOUNDS(t, b) __launch_bounds__(t, b)
 #define MG_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
 #define MG_LDG(p) __ldg(p)
+#define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif
 
 #define MG_FULL_MASK 0xFFFFFFFFu

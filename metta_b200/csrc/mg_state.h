@@ -98,6 +98,7 @@ struct MgBatch {
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
+  int32_t cfg_words;           // length of cfg in int32 words
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
   // static token templates, built once per config on the host (mg_abi.cu build_templates):

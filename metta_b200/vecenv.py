@@ -188,7 +188,7 @@ class GpuMettaGridVecEnv:
         """All-reduce (SUM) the episode accumulators over the process group: the only collective of
         the env path. Returns a float64 tensor on this rank's GPU."""
         torch = self._torch
+        from .sharding import reduce_episode_accumulators
+
         acc = torch.from_numpy(self.batch.read_episode_accum()).to(self.device)
-        if torch.distributed.is_available() and torch.distributed.is_initialized():
-            torch.distributed.all_reduce(acc, op=torch.distributed.ReduceOp.SUM)
-        return acc
+        return reduce_episode_accumulators(acc)

@@ -29,6 +29,7 @@
 #define MG_LAUNCH_BOUNDS(t, b)
 #define MG_PREFETCH_L1(p) ((void)(p))
 #define MG_LDG(p) (*(p))
+#define MG_GRID_CONSTANT
 #define MG_FADD(a, b) ((float)(a) + (float)(b))
 #define MG_FMUL(a, b) ((float)(a) * (float)(b))
 #define MG_LAUNCH(kernel, grid, block, smem, stream, ...) \

@@ -163,3 +163,34 @@ def test_full_size_properties(lib):
     written = (~empty).sum(axis=1).reshape(n, A).sum(axis=1)
     assert np.all(gs[:, L.MG_GS_TOKENS_WRITTEN] > 0) and written.min() > 0
     b.close()
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_buffer_step_matches_oracle(pinned, lib):
+    """mg_step_host (numpy in, numpy out) with pageable and with page-locked buffers."""
+    import torch
+
+    from oracle.oracle import OracleEnv
+
+    cfg, grid = SCENARIOS["kitchen_sink"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    n, A, T = 5, cfg.game.num_agents, cfg.game.obs.num_tokens
+    b = Batch(low, build_pool(low, codes[None]), n)
+    b.use_internal_buffers()
+    seeds = np.arange(n, dtype=np.uint32) + 9
+    b.reset(seeds, np.zeros(n, np.int32))
+    mk = (lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()) if pinned else (
+        lambda shape, dt: np.empty(shape, dtype=torch.empty(0, dtype=dt).numpy().dtype))
+    act, obs = mk((n * A,), torch.int32), mk((n * A, T, 3), torch.uint8)
+    rew, term, trunc = mk((n * A,), torch.float32), mk((n * A,), torch.uint8), mk((n * A,), torch.uint8)
+    orcs = [OracleEnv(low.words, codes, int(s)) for s in seeds]
+    rng = np.random.RandomState(12)
+    for s in range(40):
+        act[:] = random_actions(rng, cfg, low, n * A)
+        b.step_host(act, obs, rew, term, trunc)
+        for i, o in enumerate(orcs):
+            o.step(act[i * A : (i + 1) * A])
+            assert np.array_equal(obs[i * A : (i + 1) * A], o.observations), f"step {s} env {i}"
+            assert np.array_equal(rew[i * A : (i + 1) * A], o.rewards)
+    b.close()

@@ -23,8 +23,9 @@ for s in range(20):
     b.step(); torch.cuda.synchronize()
 env=b.read_env()
 sp=env['spare'].astype(np.float64)
-names=['stage(fold,load,prefetch)','shuffle','boxes+parallel','ordered','rest(regen,dmg,asm,rewards,wb)']
+names=['load','decide(shuffle,intent,conflicts)','act parallel','act ordered','post(regen,dmg,clip,asm)']
 tot=sp.sum(1)
 print('N',N,'flush',FLUSH); print('per-env total cycles: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f'%(tot.mean(),np.percentile(tot,50),np.percentile(tot,90),np.percentile(tot,99),tot.max()))
+print('envs with ordered work: %.1f%%' % (100.0*(sp[:,3] > 2000).mean()))
 for i,n in enumerate(names):
     c=sp[:,i]; print('%-34s mean %8.0f p50 %8.0f p99 %8.0f max %8.0f'%(n,c.mean(),np.percentile(c,50),np.percentile(c,99),c.max()))
