@@ -154,7 +154,8 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   b.cfg = d_cfg;
   b.cfg_words = (int32_t)n_words;
   std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
-  TRY(dev_alloc(e, &d_pat, pat.size() + 64));
+  pat.resize(((pat.size() + 255) / 256 + 1) * 256, 0xFF);  // padded: lanes read whole runs of cells
+  TRY(dev_alloc(e, &d_pat, pat.size()));
   CUDA_TRY(cudaMemcpy(d_pat, pat.data(), pat.size(), cudaMemcpyHostToDevice));
   b.pattern = d_pat;
   TRY(dev_alloc(e, &b.env, N));
@@ -362,11 +363,12 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
 static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask) {
   const dim3 grid((unsigned)(b.env_end - b.env_begin), (unsigned)((b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
   const int slot = (b.T * 3 + 16 + 15) & ~15;
-  const size_t smem = (size_t)slot * MG_OBS_WARPS;
   const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
-  if (cpl <= 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
-  else if (cpl <= 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
-  else if (cpl <= 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  const int cpl_t = cpl <= 1 ? 1 : cpl <= 2 ? 2 : cpl <= 4 ? 4 : 8;
+  const size_t smem = (size_t)(slot + MG_OBS_DESC_BYTES(cpl_t)) * MG_OBS_WARPS;
+  if (cpl_t == 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  else if (cpl_t == 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+  else if (cpl_t == 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   e->launches++;
   CUDA_TRY(cudaGetLastError());
@@ -742,15 +744,7 @@ extern "C" int mg_peek_observations_noalloc(void* h, void* obs_out_dev, void* st
   view.obs = reinterpret_cast<uint8_t*>(obs_out_dev);
   view.tok_counts = scratch;
   cudaStream_t s = (cudaStream_t)stream;
-  const dim3 grid((unsigned)view.num_envs, (unsigned)((view.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
-  const int slot = (view.T * 3 + 16 + 15) & ~15;
-  const size_t smem = (size_t)slot * MG_OBS_WARPS;
-  const int cpl = (view.obs_cells + 31) / 32;
-  if (cpl <= 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
-  else if (cpl <= 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
-  else if (cpl <= 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
-  else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, view, (const uint8_t*)nullptr); }
-  e->launches++;
-  CUDA_TRY(cudaGetLastError());
+  const int rc_launch = launch_obs_slice(e, view, s, nullptr);
+  if (rc_launch != MG_OK) return rc_launch;
   return MG_OK;
 }

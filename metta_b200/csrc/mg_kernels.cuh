@@ -902,28 +902,33 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   const int slot = (row_bytes + 16 + 15) & ~15;  // room to mirror the row's misalignment
   uint8_t* out = b.obs + (size_t)g * row_bytes;
   const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
-  uint8_t* base = dyn + (size_t)warp * slot;     // 16-byte aligned
+  uint8_t* base = dyn + (size_t)warp * (slot + MG_OBS_DESC_BYTES(CPL));  // 16-byte aligned: [row image | cell descriptors]
   uint8_t* row = base + mis;                     // row and out are congruent mod 16
+  uint2* desc = reinterpret_cast<uint2*>(base + slot);
   {
     uint4 ff;
     ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
     uint4* p = reinterpret_cast<uint4*>(base);
-    for (int i = lane; i < slot / 16; i += 32) p[i] = ff;
+    const int n16 = slot >> 4;
+#pragma unroll 1
+    for (int i = lane; i < n16; i += 32) p[i] = ff;
   }
   __syncwarp();
   const uint32_t current_step = b.env[env].current_step;
-  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, current_step);
+  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, desc, current_step);
   __syncwarp();
-  // store: bytes up to the first 16-byte boundary, 16-byte body, byte tail
+  // store: bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
   const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
-  const int body = (row_bytes - head) & ~15;
-  for (int i = lane; i < head; i += 32) out[i] = row[i];
+  const int n16 = (row_bytes - head) >> 4;
+  const int tail = head + (n16 << 4);
+  if (lane < head) out[lane] = row[lane];
   {
     const uint4* s = reinterpret_cast<const uint4*>(row + head);
     uint4* d = reinterpret_cast<uint4*>(out + head);
-    for (int i = lane; i < body / 16; i += 32) d[i] = s[i];
+#pragma unroll 1
+    for (int i = lane; i < n16; i += 32) d[i] = s[i];
   }
-  for (int i = head + body + lane; i < row_bytes; i += 32) out[i] = row[i];
+  if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
   if (lane == 0) {
     uint16_t* tc = b.tok_counts + (size_t)g * 2;
     tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
