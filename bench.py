@@ -263,23 +263,35 @@ def run_ours(args):
     h_obs = pin((N * A, T, 3), torch.uint8); h_rew = pin((N * A,), torch.float32)
     h_term = pin((N * A,), torch.uint8); h_trunc = pin((N * A,), torch.uint8)
     e2e_steps = max(3, min(args.steps, 30))
-    for i in range(3):
-        hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
+
+    def e2e_run(changed_rows_only):
+        hb.set_host_export(changed_rows_only)
+        for i in range(3):
+            hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        b0 = hb.transfer_bytes()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
+        torch.cuda.synchronize()
+        secs = time.perf_counter() - t0
+        b1 = hb.transfer_bytes()
+        return secs, (b1[0] - b0[0]) / e2e_steps, (b1[1] - b0[1]) / e2e_steps
+
+    e2e_full_s, _, full_d2h = e2e_run(False)   # every observation byte crosses the host link
+    e2e_s, e2e_h2d, e2e_d2h = e2e_run(True)    # only the part of each row that changed (mg_set_host_export 1)
+    # the export must leave the host buffer identical to the device observations
+    if not np.array_equal(h_obs, hb.read_obs().reshape(h_obs.shape)):
+        raise SystemExit("bench: host observation buffer differs from the device buffer after the changed-rows export")
     # ---- the only collective of the env path: episode stats (a few KB) over NCCL
     acc = torch.from_numpy(batch.read_episode_accum()).to(dev)
-    t = torch.tensor([total_ms, free_ms, e2e_s], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, free_ms, e2e_s, e2e_full_s], dtype=torch.float64, device=dev)
     reduce_episode_accumulators(acc)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, free_ms, e2e_s = (float(x) for x in t.cpu())
+    total_ms, free_ms, e2e_s, e2e_full_s = (float(x) for x in t.cpu())
     if rank == 0:
         units = world * N * A * args.steps
         value = units / (total_ms / 1000.0)
@@ -300,7 +312,11 @@ def run_ours(args):
                        "parallelism": f"env shards x{world}, no data-path collective"},
             "clocks": clocks,
             "e2e": {"value": world * N * A * e2e_steps / e2e_s, "unit": "agent-steps/s",
-                    "h2d_bytes_per_step": N * A * 4, "d2h_bytes_per_step": N * A * (T * 3 + 4 + 1 + 1)},
+                    "h2d_bytes_per_step": int(e2e_h2d), "d2h_bytes_per_step": int(e2e_d2h),
+                    "host_export": "page-locked caller buffers; observations: changed row prefixes written by a kernel (mg_set_host_export 1), "
+                                   "host buffer checked equal to the device buffer after the run",
+                    "full_rows": {"value": world * N * A * e2e_steps / e2e_full_s, "d2h_bytes_per_step": int(full_d2h),
+                                  "note": "same call with every observation byte copied (mg_set_host_export 0)"}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "mg_obs_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,

@@ -155,6 +155,18 @@ class Batch:
             )
         )
 
+    def set_host_export(self, changed_rows_only: bool) -> None:
+        """step_host with page-locked buffers: False = copy the whole observation buffer every call,
+        True = after one full copy only write the part of each row that changed (the caller must not
+        write to that buffer between calls)."""
+        self._check(self._c.mg_set_host_export(self._h, 1 if changed_rows_only else 0))
+
+    def transfer_bytes(self) -> tuple[int, int]:
+        """(host->device, device->host) bytes step_host has moved so far."""
+        v = np.zeros(2, dtype=np.uint64)
+        self._check(self._c.mg_transfer_bytes(self._h, v.ctypes.data, v.ctypes.data + 8))
+        return int(v[0]), int(v[1])
+
     def profile_step(self, stream: int = 0) -> tuple[float, float]:
         ms = np.zeros(2, dtype=np.float32)
         self._check(self._c.mg_profile_step(self._h, stream, ms.ctypes.data))
@@ -237,6 +249,10 @@ class Batch:
 
     def read_rng(self) -> np.ndarray:
         return self._read(ST_RNG, np.uint32, (self.num_envs, 624))
+
+    def read_obs(self) -> np.ndarray:
+        """The bound observation buffer, copied to the host: u8 [N*A, T, 3]."""
+        return self._read(ST_OBS, np.uint8, (self.num_envs * self.num_agents, -1, 3))
 
     def read_buffer(self, what: int, dtype, shape) -> np.ndarray:
         return self._read(what, dtype, shape)

@@ -59,6 +59,13 @@ struct MgEnvs {
   cudaGraphExec_t graph_exec;
   uint8_t* d_mask;
   int32_t* d_tmp;  // small scratch for set_inventory
+  // mg_step_host with page-locked buffers, export mode 1: only the part of each row that changed
+  int host_export_mode;
+  const void* host_obs_last;      // the host buffer whose contents d_prev_counts describes (nullptr = none)
+  uint16_t* d_prev_counts;        // [N*A] tokens the host row holds
+  unsigned long long* d_export_bytes;
+  unsigned long long* h_export_bytes;  // pinned mirror of the counter
+  unsigned long long h2d_total, d2h_total;
 };
 
 template <typename T>
@@ -252,6 +259,10 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &e->d_mask, N));
   TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  TRY(dev_alloc(e, &e->d_prev_counts, N * A));
+  TRY(dev_alloc(e, &e->d_export_bytes, 1));
+  CUDA_TRY(cudaMallocHost((void**)&e->h_export_bytes, sizeof(unsigned long long)));
+  *e->h_export_bytes = 0;
 #ifndef MG_SIMT_EMU
   CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(sizeof(StepSmem<32>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
@@ -281,6 +292,7 @@ void mg_destroy(void* h) {
   cudaDeviceSynchronize();
   for (void* p : e->allocs) cudaFree(p);
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
+  if (e->h_export_bytes) cudaFreeHost(e->h_export_bytes);
   if (e->stream) cudaStreamDestroy(e->stream);
   if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
   if (e->graph) cudaGraphDestroy(e->graph);
@@ -550,7 +562,40 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   CUDA_TRY(cudaMemcpyAsync((void*)b.actions, src_act, NA * 4, cudaMemcpyHostToDevice, s));
   int rc;
   TRY(mg_step(h, (void*)s));
-  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
+  // observations: the whole buffer, or (export mode 1, same page-locked buffer as last time) only the
+  // prefix of each row that can differ from what the host holds, written by a kernel over PCIe
+  const int row_bytes = b.T * 3;
+  const int export_grid = (int)((NA + MG_EXPORT_ROWS * 8 - 1) / (MG_EXPORT_ROWS * 8));
+  uint8_t* obs_mapped = nullptr;
+  bool sparse = false;
+#ifndef MG_SIMT_EMU
+  if (direct && e->host_export_mode == 1 && e->host_obs_last == obs && row_bytes % 8 == 0 &&
+      (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0 && (reinterpret_cast<uintptr_t>(obs) & 7) == 0) {
+    void* dp = nullptr;
+    if (cudaHostGetDevicePointer(&dp, obs, 0) == cudaSuccess && dp != nullptr) { obs_mapped = reinterpret_cast<uint8_t*>(dp); sparse = true; }
+    else cudaGetLastError();
+  }
+#endif
+  if (sparse) {
+    MG_LAUNCH(mg_export_rows_kernel, export_grid, 256, 0, s, (const uint8_t*)b.obs, obs_mapped, (const uint16_t*)b.tok_counts,
+              e->d_prev_counts, (int)NA, row_bytes, e->d_export_bytes);
+    e->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(e->h_export_bytes, e->d_export_bytes, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  } else {
+    CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
+    e->d2h_total += obs_bytes;
+    e->host_obs_last = nullptr;
+    if (direct && e->host_export_mode == 1) {  // from now on the host buffer is known row by row
+      MG_LAUNCH(mg_export_rows_kernel, export_grid, 256, 0, s, (const uint8_t*)b.obs, (uint8_t*)nullptr, (const uint16_t*)b.tok_counts,
+                e->d_prev_counts, (int)NA, row_bytes, e->d_export_bytes);
+      e->launches++;
+      CUDA_TRY(cudaGetLastError());
+      e->host_obs_last = obs;
+    }
+  }
+  e->h2d_total += NA * 4;
+  e->d2h_total += NA * 6;
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)rewards : (void*)(st + off_rew), b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)terminals : (void*)(st + off_term), b.terminals, NA, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)truncations : (void*)(st + off_trunc), b.truncations, NA, cudaMemcpyDeviceToHost, s));
@@ -561,6 +606,28 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
     memcpy(terminals, st + off_term, NA);
     memcpy(truncations, st + off_trunc, NA);
   }
+  return MG_OK;
+}
+
+// How mg_step_host delivers observations into a page-locked caller buffer. 0 (default): the whole
+// buffer every call. 1: after one full copy, only the leading part of each row that can differ from
+// what the buffer holds (rows end in 0xFF padding, and the padding does not move unless the token count
+// does). Mode 1 relies on the library being the only writer of that buffer between calls; passing
+// another buffer, or calling this again, starts over with a full copy.
+int mg_set_host_export(void* h, int32_t mode) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || (mode != 0 && mode != 1)) return fail(MG_ERR_ARG, "mg_set_host_export: mode must be 0 or 1");
+  e->host_export_mode = mode;
+  e->host_obs_last = nullptr;
+  return MG_OK;
+}
+
+// Bytes mg_step_host moved over the host link since mg_create (what the copies and the export kernel wrote).
+int mg_transfer_bytes(void* h, uint64_t* h2d, uint64_t* d2h) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !h2d || !d2h) return fail(MG_ERR_ARG, "mg_transfer_bytes: bad arguments");
+  *h2d = e->h2d_total;
+  *d2h = e->d2h_total + (e->h_export_bytes ? *e->h_export_bytes : 0ull);
   return MG_OK;
 }
 

@@ -936,6 +936,41 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   }
 }
 
+// Host export of observations for mg_step_host (page-locked caller buffer, written over PCIe by the
+// SMs): a row only differs from what the host already holds in its first max(previous, current)
+// tokens, because everything behind the tokens written is 0xFF in both. One warp copies that prefix
+// (rounded up to 8 bytes: the device row is right for every byte, so copying too much is harmless)
+// of MG_EXPORT_ROWS rows. host == nullptr only records the counts (after a full copy).
+#define MG_EXPORT_ROWS 4
+MG_GLOBAL void mg_export_rows_kernel(const uint8_t* obs, uint8_t* host, const uint16_t* tok_counts, uint16_t* prev, int rows,
+                                     int row_bytes, unsigned long long* bytes_out) {
+  const int lane = threadIdx.x & 31;
+  const int first = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * MG_EXPORT_ROWS;
+  int cur = 0, pv = 0;
+  if (lane < MG_EXPORT_ROWS && first + lane < rows) {
+    cur = tok_counts[(size_t)(first + lane) * 2];
+    pv = prev[first + lane];
+    prev[first + lane] = (uint16_t)cur;
+  }
+  if (host == nullptr) return;
+  unsigned long long total = 0;
+#pragma unroll 1
+  for (int k = 0; k < MG_EXPORT_ROWS; k++) {
+    const int c = __shfl_sync(MG_FULL_MASK, cur, k), p = __shfl_sync(MG_FULL_MASK, pv, k);
+    if (first + k >= rows) break;
+    const int n = c > p ? c : p;
+    int nb = (n * 3 + 7) & ~7;
+    nb = nb < row_bytes ? nb : row_bytes;
+    const size_t off = (size_t)(first + k) * row_bytes;
+    const uint2* src = reinterpret_cast<const uint2*>(obs + off);
+    uint2* dst = reinterpret_cast<uint2*>(host + off);
+#pragma unroll 1
+    for (int i = lane; i < (nb >> 3); i += 32) dst[i] = src[i];
+    total += (unsigned long long)nb;
+  }
+  if (lane == 0 && total != 0) atomicAdd(bytes_out, total);
+}
+
 // Folds pending token counts so that game stats can be read out (mg_read).
 MG_GLOBAL void mg_fold_kernel(const MG_GRID_CONSTANT MgBatch b) {
   const int lane = threadIdx.x & 31;

@@ -142,6 +142,7 @@ static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline double atomicAdd(double* p, double v) { double o = *p; *p += v; return o; }
 static inline float atomicAdd(float* p, float v) { float o = *p; *p += v; return o; }
 static inline int atomicAdd(int* p, int v) { int o = *p; *p += v; return o; }
+static inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { unsigned long long o = *p; *p += v; return o; }
 
 // ---- the few CUDA runtime entry points used by mg_abi.cu
 typedef int cudaError_t;

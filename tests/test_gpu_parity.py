@@ -165,9 +165,10 @@ def test_full_size_properties(lib):
     b.close()
 
 
-@pytest.mark.parametrize("pinned", [False, True])
-def test_host_buffer_step_matches_oracle(pinned, lib):
-    """mg_step_host (numpy in, numpy out) with pageable and with page-locked buffers."""
+@pytest.mark.parametrize("pinned,changed_only", [(False, False), (True, False), (True, True)])
+def test_host_buffer_step_matches_oracle(pinned, changed_only, lib):
+    """mg_step_host (numpy in, numpy out) with pageable and with page-locked buffers, and with the
+    observation export that only writes the part of each row that changed."""
     import torch
 
     from oracle.oracle import OracleEnv
@@ -178,6 +179,7 @@ def test_host_buffer_step_matches_oracle(pinned, lib):
     n, A, T = 5, cfg.game.num_agents, cfg.game.obs.num_tokens
     b = Batch(low, build_pool(low, codes[None]), n)
     b.use_internal_buffers()
+    b.set_host_export(changed_only)
     seeds = np.arange(n, dtype=np.uint32) + 9
     b.reset(seeds, np.zeros(n, np.int32))
     mk = (lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()) if pinned else (
@@ -193,4 +195,44 @@ def test_host_buffer_step_matches_oracle(pinned, lib):
             o.step(act[i * A : (i + 1) * A])
             assert np.array_equal(obs[i * A : (i + 1) * A], o.observations), f"step {s} env {i}"
             assert np.array_equal(rew[i * A : (i + 1) * A], o.rewards)
+    h2d, d2h = b.transfer_bytes()
+    full = 40 * n * A * (T * 3 + 6)
+    assert h2d == 40 * n * A * 4
+    assert (d2h < full) if changed_only else (d2h == full), (d2h, full)
+    b.close()
+
+
+def test_changed_rows_export_follows_resets(lib):
+    """Export mode 1 across episode ends (token counts drop back at a reset), a second buffer and a
+    mode switch: the page-locked host buffer always equals the device observations."""
+    import torch
+
+    cfg, grid = SCENARIOS["tiny_truncating"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    n, A, T = 67, cfg.game.num_agents, cfg.game.obs.num_tokens
+    b = Batch(low, build_pool(low, codes[None]), n)
+    b.use_internal_buffers()
+    b.set_host_export(True)
+    b.reset(np.arange(n, dtype=np.uint32) + 3, np.zeros(n, np.int32))
+    pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()  # noqa: E731
+    act = pin((n * A,), torch.int32)
+    obs_a, obs_b = pin((n * A, T, 3), torch.uint8), pin((n * A, T, 3), torch.uint8)
+    obs_a[...] = 7  # garbage: the first call on a buffer must not rely on its contents
+    obs_b[...] = 9
+    rew, term, trunc = pin((n * A,), torch.float32), pin((n * A,), torch.uint8), pin((n * A,), torch.uint8)
+    rng = np.random.RandomState(5)
+    episodes_seen = 0
+    for s in range(3 * cfg.game.max_steps + 5):
+        act[:] = random_actions(rng, cfg, low, n * A)
+        buf = obs_b if 20 <= s < 30 else obs_a
+        if s == 40:
+            b.set_host_export(False)
+        if s == 45:
+            b.set_host_export(True)
+        b.step_host(act, buf, rew, term, trunc)
+        dev = b.read_obs()
+        assert np.array_equal(buf, dev.reshape(buf.shape)), f"step {s}"
+        episodes_seen += int(trunc.any() or term.any())
+    assert episodes_seen >= 2
     b.close()

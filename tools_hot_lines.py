@@ -1,5 +1,5 @@
 """Per-source-line instruction and stall-sample totals from an ncu report (cuda,sass source view).
-usage: python tools_hot_lines.py report.ncu-rep [warps_per_launch]"""
+usage: python tools_hot_lines.py report.ncu-rep [warps_per_launch] [samples]"""
 import csv, subprocess, sys
 rep = sys.argv[1]
 div = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
@@ -24,5 +24,7 @@ for r in rows:
         a[0] += n; a[1] += s
         tot += n
 print("kernel", kernel, "total inst", tot, "per warp %.1f" % (tot / div))
-for (f, l), (n, s, src) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:60]:
+by = 1 if len(sys.argv) > 3 and sys.argv[3] == "samples" else 0
+print("total samples", sum(v[1] for v in agg.values()))
+for (f, l), (n, s, src) in sorted(agg.items(), key=lambda kv: -kv[1][by])[:70]:
     print("%-16s:%4d inst/warp=%7.1f (%4.1f%%) samples=%5d  %s" % (f, l, n / div, 100.0 * n / tot, s, src))
