@@ -66,7 +66,14 @@ struct MgEnvs {
   unsigned long long* d_export_bytes;
   unsigned long long* h_export_bytes;  // pinned mirror of the counter
   unsigned long long h2d_total, d2h_total;
+  // the step graph with the export kernels of every slice in it, for one set of host buffers
+  cudaGraph_t hgraph;
+  cudaGraphExec_t hgraph_exec;
+  bool hgraph_dirty;
+  MgHostTargets hgraph_targets;
 };
+
+static void mark_graphs_dirty(MgEnvs* e) { e->graph_dirty = true; e->hgraph_dirty = true; }
 
 template <typename T>
 static int dev_alloc(MgEnvs* e, T** out, size_t count, bool zero = true) {
@@ -126,7 +133,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   e->h_pinned_bytes = 0;
   e->stream = nullptr;
   e->chunks = 1;
-  e->graph_dirty = true;
+  mark_graphs_dirty(e);
   e->graph = nullptr;
   e->graph_exec = nullptr;
   e->ev_fork = nullptr;
@@ -296,6 +303,8 @@ void mg_destroy(void* h) {
   if (e->stream) cudaStreamDestroy(e->stream);
   if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
   if (e->graph) cudaGraphDestroy(e->graph);
+  if (e->hgraph_exec) cudaGraphExecDestroy(e->hgraph_exec);
+  if (e->hgraph) cudaGraphDestroy(e->hgraph);
   if (e->capture_stream) cudaStreamDestroy(e->capture_stream);
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   for (int i = 0; i < MG_MAX_CHUNKS; i++) {
@@ -337,7 +346,7 @@ int mg_load_maps(void* h, int32_t num_maps, const uint16_t* grids, const int32_t
   b.pool_grid = d_grid; b.pool_agents = d_ag; b.pool_n_asm = d_na; b.pool_asm = d_as; b.pool_n_chest = d_nc; b.pool_chest = d_ch;
   b.num_maps = num_maps;
   e->maps_loaded = true;
-  e->graph_dirty = true;
+  mark_graphs_dirty(e);
   return MG_OK;
 }
 
@@ -368,7 +377,7 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
     b.rewards = (float*)rewards; b.actions = (const int32_t*)actions;
   }
   e->buffers_bound = true;
-  e->graph_dirty = true;
+  mark_graphs_dirty(e);
   return MG_OK;
 }
 
@@ -403,8 +412,20 @@ static int launch_step_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
   return MG_OK;
 }
 
-// Fork from `s` to the chunk streams, run step + observation kernel of each env slice, join back.
-static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s) {
+static int launch_export(MgEnvs* e, const MgBatch& b, cudaStream_t s, const MgHostTargets& ht, int row_begin, int row_end) {
+  const int per_cta = MG_EXPORT_WARPS * MG_EXPORT_ROWS;
+  const int grid = (row_end - row_begin + per_cta - 1) / per_cta;
+  if (grid <= 0) return MG_OK;
+  MG_LAUNCH(mg_export_rows_kernel, grid, MG_EXPORT_WARPS * 32, 0, s, (const uint8_t*)b.obs, (const float*)b.rewards, (const uint8_t*)b.terminals,
+            (const uint8_t*)b.truncations, ht, (const uint16_t*)b.tok_counts, e->d_prev_counts, row_begin, row_end, b.T * 3, e->d_export_bytes);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+// Fork from `s` to the chunk streams, run step + observation kernel (+ host export, if `ht`) of each
+// env slice, join back.
+static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* ht = nullptr) {
   const int n = e->b.num_envs, per = (n + e->chunks - 1) / e->chunks;
   int rc;
   CUDA_TRY(cudaEventRecord(e->ev_fork, s));
@@ -417,6 +438,7 @@ static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s) {
     CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_fork, 0));
     if ((rc = launch_step_slice(e, slice, cs)) != MG_OK) return rc;
     if ((rc = launch_obs_slice(e, slice, cs, nullptr)) != MG_OK) return rc;
+    if (ht != nullptr && (rc = launch_export(e, slice, cs, *ht, slice.env_begin * slice.A, slice.env_end * slice.A)) != MG_OK) return rc;
     CUDA_TRY(cudaEventRecord(e->ev_join[c], cs));
     CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[c], 0));
   }
@@ -461,6 +483,22 @@ int mg_reset(void* h, const uint32_t* seeds, const int32_t* map_idx, const uint8
 
 // One step of every env on `stream` (a cudaStream_t, may be null): reads the bound actions,
 // overwrites observations/rewards/terminals/truncations. Asynchronous.
+#ifndef MG_SIMT_EMU
+static int capture_step_graph(MgEnvs* e, const MgHostTargets* ht, cudaGraph_t* graph, cudaGraphExec_t* exec) {
+  if (*exec) { cudaGraphExecDestroy(*exec); *exec = nullptr; }
+  if (*graph) { cudaGraphDestroy(*graph); *graph = nullptr; }
+  const long long before = e->launches;
+  CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
+  int rc = enqueue_chunked_step(e, e->capture_stream, ht);
+  cudaError_t end = cudaStreamEndCapture(e->capture_stream, graph);
+  e->launches = before;
+  if (rc != MG_OK) return rc;
+  if (end != cudaSuccess) return fail(MG_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(end));
+  CUDA_TRY(cudaGraphInstantiate(exec, *graph, 0));
+  return MG_OK;
+}
+#endif
+
 int mg_step(void* h, void* stream) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e) return fail(MG_ERR_ARG, "mg_step: null handle");
@@ -474,16 +512,8 @@ int mg_step(void* h, void* stream) {
   return enqueue_chunked_step(e, s);
 #else
   if (e->graph_dirty) {  // (re)capture: buffers, options or maps changed since the last capture
-    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
-    if (e->graph) { cudaGraphDestroy(e->graph); e->graph = nullptr; }
-    const long long before = e->launches;
-    CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue_chunked_step(e, e->capture_stream);
-    cudaError_t end = cudaStreamEndCapture(e->capture_stream, &e->graph);
-    e->launches = before;
+    int rc = capture_step_graph(e, nullptr, &e->graph, &e->graph_exec);
     if (rc != MG_OK) return rc;
-    if (end != cudaSuccess) return fail(MG_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(end));
-    CUDA_TRY(cudaGraphInstantiate(&e->graph_exec, e->graph, 0));
     e->graph_dirty = false;
   }
   CUDA_TRY(cudaGraphLaunch(e->graph_exec, s));
@@ -560,42 +590,56 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   const void* src_act = actions;
   if (!direct) { memcpy(st + off_act, actions, NA * 4); src_act = st + off_act; }
   CUDA_TRY(cudaMemcpyAsync((void*)b.actions, src_act, NA * 4, cudaMemcpyHostToDevice, s));
+  e->h2d_total += NA * 4;
+  e->d2h_total += NA * 6;
   int rc;
-  TRY(mg_step(h, (void*)s));
-  // observations: the whole buffer, or (export mode 1, same page-locked buffer as last time) only the
-  // prefix of each row that can differ from what the host holds, written by a kernel over PCIe
+  // observations: the whole buffer, or (export mode 1, same page-locked buffers as last time) only the
+  // prefix of each row that can differ from what the host holds, written over PCIe by a kernel that
+  // follows each slice's observation kernel inside the step graph (rewards and flags ride along)
   const int row_bytes = b.T * 3;
-  const int export_grid = (int)((NA + MG_EXPORT_ROWS * 8 - 1) / (MG_EXPORT_ROWS * 8));
-  uint8_t* obs_mapped = nullptr;
+  MgHostTargets ht;
+  ht.obs = nullptr; ht.rewards = nullptr; ht.terminals = nullptr; ht.truncations = nullptr;
   bool sparse = false;
 #ifndef MG_SIMT_EMU
   if (direct && e->host_export_mode == 1 && e->host_obs_last == obs && row_bytes % 8 == 0 &&
       (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0 && (reinterpret_cast<uintptr_t>(obs) & 7) == 0) {
-    void* dp = nullptr;
-    if (cudaHostGetDevicePointer(&dp, obs, 0) == cudaSuccess && dp != nullptr) { obs_mapped = reinterpret_cast<uint8_t*>(dp); sparse = true; }
-    else cudaGetLastError();
-  }
-#endif
-  if (sparse) {
-    MG_LAUNCH(mg_export_rows_kernel, export_grid, 256, 0, s, (const uint8_t*)b.obs, obs_mapped, (const uint16_t*)b.tok_counts,
-              e->d_prev_counts, (int)NA, row_bytes, e->d_export_bytes);
-    e->launches++;
-    CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaMemcpyAsync(e->h_export_bytes, e->d_export_bytes, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-  } else {
-    CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
-    e->d2h_total += obs_bytes;
-    e->host_obs_last = nullptr;
-    if (direct && e->host_export_mode == 1) {  // from now on the host buffer is known row by row
-      MG_LAUNCH(mg_export_rows_kernel, export_grid, 256, 0, s, (const uint8_t*)b.obs, (uint8_t*)nullptr, (const uint16_t*)b.tok_counts,
-                e->d_prev_counts, (int)NA, row_bytes, e->d_export_bytes);
-      e->launches++;
-      CUDA_TRY(cudaGetLastError());
-      e->host_obs_last = obs;
+    void *p0 = nullptr, *p1 = nullptr, *p2 = nullptr, *p3 = nullptr;
+    if (cudaHostGetDevicePointer(&p0, obs, 0) == cudaSuccess && cudaHostGetDevicePointer(&p1, rewards, 0) == cudaSuccess &&
+        cudaHostGetDevicePointer(&p2, terminals, 0) == cudaSuccess && cudaHostGetDevicePointer(&p3, truncations, 0) == cudaSuccess) {
+      ht.obs = reinterpret_cast<uint8_t*>(p0); ht.rewards = reinterpret_cast<float*>(p1);
+      ht.terminals = reinterpret_cast<uint8_t*>(p2); ht.truncations = reinterpret_cast<uint8_t*>(p3);
+      sparse = true;
+    } else {
+      cudaGetLastError();
     }
   }
-  e->h2d_total += NA * 4;
-  e->d2h_total += NA * 6;
+  if (sparse) {
+    if (e->chunks <= 1) {
+      TRY(launch_step_slice(e, b, s));
+      TRY(launch_obs(e, s, nullptr));
+      TRY(launch_export(e, b, s, ht, 0, (int)NA));
+    } else {
+      if (e->hgraph_dirty || memcmp(&ht, &e->hgraph_targets, sizeof(ht)) != 0) {
+        TRY(capture_step_graph(e, &ht, &e->hgraph, &e->hgraph_exec));
+        e->hgraph_targets = ht;
+        e->hgraph_dirty = false;
+      }
+      CUDA_TRY(cudaGraphLaunch(e->hgraph_exec, s));
+      e->launches += 3LL * e->chunks;
+    }
+    CUDA_TRY(cudaMemcpyAsync(e->h_export_bytes, e->d_export_bytes, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return MG_OK;
+  }
+#endif
+  TRY(mg_step(h, (void*)s));
+  CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
+  e->d2h_total += obs_bytes;
+  e->host_obs_last = nullptr;
+  if (direct && e->host_export_mode == 1) {  // from now on the host buffer is known row by row
+    TRY(launch_export(e, b, s, ht, 0, (int)NA));
+    e->host_obs_last = obs;
+  }
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)rewards : (void*)(st + off_rew), b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)terminals : (void*)(st + off_term), b.terminals, NA, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)truncations : (void*)(st + off_trunc), b.truncations, NA, cudaMemcpyDeviceToHost, s));
@@ -638,7 +682,7 @@ int mg_set_options(void* h, int32_t auto_reset, int32_t map_stride) {
   if (!e) return fail(MG_ERR_ARG, "mg_set_options: null handle");
   e->b.auto_reset = auto_reset ? 1 : 0;
   e->b.map_stride = map_stride < 0 ? 0 : map_stride;
-  e->graph_dirty = true;
+  mark_graphs_dirty(e);
   return MG_OK;
 }
 

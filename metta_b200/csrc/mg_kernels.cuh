@@ -940,33 +940,72 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
 // SMs): a row only differs from what the host already holds in its first max(previous, current)
 // tokens, because everything behind the tokens written is 0xFF in both. One warp copies that prefix
 // (rounded up to 8 bytes: the device row is right for every byte, so copying too much is harmless)
-// of MG_EXPORT_ROWS rows. host == nullptr only records the counts (after a full copy).
+// of MG_EXPORT_ROWS rows; the CTA's first warp also writes the rows' rewards and flags.
+// host.obs == nullptr only records the counts (after a full copy).
 #define MG_EXPORT_ROWS 4
-MG_GLOBAL void mg_export_rows_kernel(const uint8_t* obs, uint8_t* host, const uint16_t* tok_counts, uint16_t* prev, int rows,
-                                     int row_bytes, unsigned long long* bytes_out) {
+#ifndef MG_EXPORT_ALIGN
+#define MG_EXPORT_ALIGN 32
+#endif
+#define MG_EXPORT_WARPS 8
+struct MgHostTargets {  // device-visible addresses of the caller's page-locked buffers (all rows; nullptr = not exported here)
+  uint8_t* obs;
+  float* rewards;
+  uint8_t* terminals;
+  uint8_t* truncations;
+};
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_EXPORT_WARPS * 32, 4)
+    mg_export_rows_kernel(const uint8_t* obs, const float* rewards, const uint8_t* terminals, const uint8_t* truncations, MgHostTargets host,
+                          const uint16_t* tok_counts, uint16_t* prev, int row_begin, int row_end, int row_bytes, unsigned long long* bytes_out) {
   const int lane = threadIdx.x & 31;
-  const int first = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * MG_EXPORT_ROWS;
+  const int cta_first = row_begin + (int)blockIdx.x * (MG_EXPORT_WARPS * MG_EXPORT_ROWS);
+  const int first = cta_first + (int)(threadIdx.x >> 5) * MG_EXPORT_ROWS;
   int cur = 0, pv = 0;
-  if (lane < MG_EXPORT_ROWS && first + lane < rows) {
+  if (lane < MG_EXPORT_ROWS && first + lane < row_end) {
     cur = tok_counts[(size_t)(first + lane) * 2];
     pv = prev[first + lane];
     prev[first + lane] = (uint16_t)cur;
   }
-  if (host == nullptr) return;
+  if (host.rewards != nullptr && threadIdx.x < MG_EXPORT_WARPS * MG_EXPORT_ROWS && cta_first + (int)threadIdx.x < row_end) {
+    const int r = cta_first + (int)threadIdx.x;  // the CTA's rows: one thread each for the per-agent scalars
+    host.rewards[r] = rewards[r];
+    host.terminals[r] = terminals[r];
+    host.truncations[r] = truncations[r];
+  }
+  if (host.obs == nullptr) return;
+  const bool sector_aligned = MG_EXPORT_ALIGN > 8 && ((reinterpret_cast<uintptr_t>(obs) | reinterpret_cast<uintptr_t>(host.obs)) & (MG_EXPORT_ALIGN - 1)) == 0;
   unsigned long long total = 0;
 #pragma unroll 1
   for (int k = 0; k < MG_EXPORT_ROWS; k++) {
     const int c = __shfl_sync(MG_FULL_MASK, cur, k), p = __shfl_sync(MG_FULL_MASK, pv, k);
-    if (first + k >= rows) break;
+    if (first + k >= row_end) break;
     const int n = c > p ? c : p;
+    if (n == 0) continue;
     int nb = (n * 3 + 7) & ~7;
     nb = nb < row_bytes ? nb : row_bytes;
-    const size_t off = (size_t)(first + k) * row_bytes;
-    const uint2* src = reinterpret_cast<const uint2*>(obs + off);
-    uint2* dst = reinterpret_cast<uint2*>(host + off);
+    // widen to whole 32-byte sectors (neighbouring rows of this launch are final too, so their bytes
+    // are the right ones): PCIe writes of whole sectors need no byte enables
+    size_t lo = (size_t)(first + k) * row_bytes, hi = lo + nb;
+    if (sector_aligned) {
+      const size_t lim_lo = (size_t)row_begin * row_bytes, lim_hi = (size_t)row_end * row_bytes;
+      lo &= ~(size_t)(MG_EXPORT_ALIGN - 1);
+      hi = (hi + MG_EXPORT_ALIGN - 1) & ~(size_t)(MG_EXPORT_ALIGN - 1);
+      lo = lo < lim_lo ? lim_lo : lo;
+      hi = hi > lim_hi ? lim_hi : hi;
+    }
+    if (((lo | hi) & 15) == 0) {
+      const uint4* src = reinterpret_cast<const uint4*>(obs + lo);
+      uint4* dst = reinterpret_cast<uint4*>(host.obs + lo);
+      const int nv = (int)((hi - lo) >> 4);
 #pragma unroll 1
-    for (int i = lane; i < (nb >> 3); i += 32) dst[i] = src[i];
-    total += (unsigned long long)nb;
+      for (int i = lane; i < nv; i += 32) dst[i] = src[i];
+    } else {
+      const uint2* src = reinterpret_cast<const uint2*>(obs + lo);
+      uint2* dst = reinterpret_cast<uint2*>(host.obs + lo);
+      const int nv = (int)((hi - lo) >> 3);
+#pragma unroll 1
+      for (int i = lane; i < nv; i += 32) dst[i] = src[i];
+    }
+    total += (unsigned long long)(hi - lo);
   }
   if (lane == 0 && total != 0) atomicAdd(bytes_out, total);
 }

@@ -7,7 +7,7 @@ import json,sys
 v=sys.argv[1]
 try:
     d=json.loads(open(f'gpurun_out/bench_{v}.log').read().strip().splitlines()[-1])
-    print(v, 'M/s %.1f ms/step %.4f obs_ms %.4f step_ms %.4f free %.1f e2e %.1f' % (d['value']/1e6, d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['step_kernel_ms'], d['free_running']['value']/1e6, d['e2e']['value']/1e6))
+    print(v, 'M/s %.1f ms/step %.4f obs_ms %.4f step_ms %.4f free %.1f e2e %.1f (d2h %.2f MB) full %.1f' % (d['value']/1e6, d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['step_kernel_ms'], d['free_running']['value']/1e6, d['e2e']['value']/1e6, d['e2e']['d2h_bytes_per_step']/1e6, d['e2e']['full_rows']['value']/1e6))
 except Exception as ex:
     print(v, 'FAILED', ex); print(open(f'gpurun_out/bench_{v}.log').read()[-600:])
 PY
