@@ -163,10 +163,25 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   uint8_t* d_pat = nullptr;
   int rc;
 #define TRY(x) if ((rc = (x)) != MG_OK) { return rc; }
-  TRY(dev_alloc(e, &d_cfg, (size_t)n_words + 4));
-  CUDA_TRY(cudaMemcpy(d_cfg, cfg, sizeof(int32_t) * (size_t)n_words, cudaMemcpyHostToDevice));
+  // behind the blob: for every INVCFG record and limit, which items share the limit and which items
+  // modify it, one bit per item, so that the inventory code walks set bits instead of all resources
+  std::vector<int32_t> cfg_ext(cfg, cfg + n_words);
+  for (int ic = 0; ic < cfg[MGC_NUM_INVCFG]; ic++) {
+    const int32_t* rec = cfg + cfg[MGC_OFF_INVCFG] + (size_t)ic * MG_INVCFG_WORDS;
+    int32_t members[MG_MAX_LIMITS] = {0}, mods[MG_MAX_LIMITS] = {0};
+    for (int l = 0; l < MG_MAX_LIMITS; l++)
+      for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+        if (rec[MG_INVCFG_ITEM_LIMIT + i] == l) members[l] |= 1 << i;
+        if (rec[MG_INVCFG_LIMIT_MOD + l * MG_RES_STRIDE + i] != 0) mods[l] |= 1 << i;
+      }
+    cfg_ext.insert(cfg_ext.end(), members, members + MG_MAX_LIMITS);
+    cfg_ext.insert(cfg_ext.end(), mods, mods + MG_MAX_LIMITS);
+  }
+  TRY(dev_alloc(e, &d_cfg, cfg_ext.size() + 4));
+  CUDA_TRY(cudaMemcpy(d_cfg, cfg_ext.data(), sizeof(int32_t) * cfg_ext.size(), cudaMemcpyHostToDevice));
   b.cfg = d_cfg;
-  b.cfg_words = (int32_t)n_words;
+  b.cfg_words = (int32_t)cfg_ext.size();
+  b.inv_masks_off = (int32_t)n_words;
   std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
   pat.resize(((pat.size() + 255) / 256 + 1) * 256, 0xFF);  // padded: lanes read whole runs of cells
   TRY(dev_alloc(e, &d_pat, pat.size()));
@@ -267,6 +282,9 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   TRY(dev_alloc(e, &e->d_prev_counts, N * A));
+#ifdef MG_TIMING
+  TRY(dev_alloc(e, &b.dbg, N * 16));
+#endif
   TRY(dev_alloc(e, &e->d_export_bytes, 1));
   CUDA_TRY(cudaMallocHost((void**)&e->h_export_bytes, sizeof(unsigned long long)));
   *e->h_export_bytes = 0;
@@ -704,7 +722,7 @@ int mg_set_early_reset(void* h, const uint32_t* steps) {
 enum { MG_ST_ENV = 0, MG_ST_GRID = 1, MG_ST_AGENTS = 2, MG_ST_ASMS = 3, MG_ST_CHESTS = 4, MG_ST_AGENT_STATS = 5,
        MG_ST_GAME_STATS = 6, MG_ST_LAST_ACTION = 7, MG_ST_ACTION_SUCCESS = 8, MG_ST_EPISODE_ACCUM = 9, MG_ST_RNG = 10,
        MG_ST_OBS = 11, MG_ST_REWARDS = 12, MG_ST_TERMINALS = 13, MG_ST_TRUNCATIONS = 14, MG_ST_ACTIONS = 15,
-       MG_ST_COUNT = 16 };
+       MG_ST_DEBUG = 16, MG_ST_COUNT = 17 };
 
 static void* state_ptr(MgEnvs* e, int what, size_t* bytes) {
   MgBatch& b = e->b;
@@ -726,6 +744,7 @@ static void* state_ptr(MgEnvs* e, int what, size_t* bytes) {
     case MG_ST_TERMINALS: *bytes = N * A; return b.terminals;
     case MG_ST_TRUNCATIONS: *bytes = N * A; return b.truncations;
     case MG_ST_ACTIONS: *bytes = N * A * sizeof(int32_t); return (void*)b.actions;
+    case MG_ST_DEBUG: *bytes = b.dbg ? N * 16 * sizeof(uint32_t) : 0; return b.dbg;
     default: *bytes = 0; return nullptr;
   }
 }

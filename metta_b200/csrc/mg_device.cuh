@@ -30,6 +30,7 @@ struct EnvCtx {
   bool concurrent;    // several lanes of the warp are running handle_action for different agents
   const MgBatch* batch;
   bool asm_records_on_use;  // assembler token records are rewritten where an assembler changes (else: all, every step)
+  int inv_masks_off;  // word offset of the limit member/modifier masks behind the config (mg_create)
 };
 
 // The per-step counters of an agent (action success/failure, frozen ticks, motion) live in the first
@@ -49,6 +50,7 @@ struct InvView {
   uint16_t* amt;
   uint64_t* order;
   const int32_t* invcfg;  // INVCFG record
+  const int32_t* masks;   // per limit of that record: [MG_MAX_LIMITS] items sharing it, [MG_MAX_LIMITS] items that modify it (bit per item)
   int owner_kind;         // 0 agent, 1 chest
   int owner_idx;
 };
@@ -60,6 +62,7 @@ MG_DEVICE inline InvView agent_inv(const EnvCtx& e, int ai) {
   v.order = &a->order;
   const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
   v.invcfg = e.cfg + e.cfg[MGC_OFF_INVCFG] + grp[MG_GRP_INVCFG] * MG_INVCFG_WORDS;
+  v.masks = e.cfg + e.inv_masks_off + grp[MG_GRP_INVCFG] * (2 * MG_MAX_LIMITS);
   v.owner_kind = 0;
   v.owner_idx = ai;
   return v;
@@ -73,6 +76,7 @@ MG_DEVICE inline InvView chest_inv(const EnvCtx& e, int ci) {
   const int32_t* cell = e.cfg + e.cfg[MGC_OFF_CELLTYPES] + c->cell * MG_CELL_WORDS;
   const int32_t* ct = e.cfg + e.cfg[MGC_OFF_CHEST_TYPES] + cell[MG_CELL_PARAM] * MG_CHEST_WORDS;
   v.invcfg = e.cfg + e.cfg[MGC_OFF_INVCFG] + ct[MG_CHEST_INVCFG] * MG_INVCFG_WORDS;
+  v.masks = e.cfg + e.inv_masks_off + ct[MG_CHEST_INVCFG] * (2 * MG_MAX_LIMITS);
   v.owner_kind = 1;
   v.owner_idx = ci;
   return v;
@@ -81,8 +85,7 @@ MG_DEVICE inline InvView chest_inv(const EnvCtx& e, int ci) {
 // SharedInventoryLimit::amount: kept by the reference as a running u16 sum (inventory.cpp:66-69).
 MG_DEVICE inline uint32_t inv_limit_amount(const InvView& v, int limit) {
   uint32_t sum = 0;
-  for (int i = 0; i < MG_MAX_RESOURCES; i++)
-    if (v.invcfg[MG_INVCFG_ITEM_LIMIT + i] == limit) sum += v.amt[i];
+  for (uint32_t m = (uint32_t)v.masks[limit]; m != 0u; m &= m - 1u) sum += v.amt[__ffs((int)m) - 1];
   return sum & 0xFFFFu;
 }
 
@@ -90,9 +93,9 @@ MG_DEVICE inline uint32_t inv_limit_amount(const InvView& v, int limit) {
 MG_DEVICE inline int inv_effective_limit(const InvView& v, int limit) {
   int effective = v.invcfg[MG_INVCFG_LIMIT_BASE + limit];
   const int32_t* mod = v.invcfg + MG_INVCFG_LIMIT_MOD + limit * RS;
-  for (int i = 0; i < MG_MAX_RESOURCES; i++) {
-    int bonus = mod[i];
-    if (bonus != 0) effective += (int)v.amt[i] * bonus;
+  for (uint32_t m = (uint32_t)v.masks[MG_MAX_LIMITS + limit]; m != 0u; m &= m - 1u) {
+    const int i = __ffs((int)m) - 1;
+    effective += (int)v.amt[i] * mod[i];
   }
   effective = effective < 0 ? 0 : effective;
   return effective > 65535 ? 65535 : effective;
@@ -131,8 +134,8 @@ MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item,
     AgentRec* a = &e.ag[v.owner_idx];
     a->pad0 = 1;  // token record is stale
     int amount = a->amt[item];
-    if (delta > 0) st[MG_AS_GAINED + item] += (float)delta;
-    else st[MG_AS_LOST + item] += (float)(-delta);
+    if (delta > 0) MG_RED_ADD(&st[MG_AS_GAINED + item], (float)delta);
+    else MG_RED_ADD(&st[MG_AS_LOST + item], (float)(-delta));
     st[MG_AS_AMOUNT + item] = (float)amount;
     const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
     if (grp[MG_GRP_DIVERSITY + item]) {
@@ -145,8 +148,8 @@ MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item,
       }
     }
   } else {
-    if (delta > 0) e.gstats[MG_GS_CHEST_DEPOSITED + item] += (float)delta;
-    else e.gstats[MG_GS_CHEST_WITHDRAWN + item] += (float)(-delta);
+    if (delta > 0) MG_RED_ADD(&e.gstats[MG_GS_CHEST_DEPOSITED + item], (float)delta);
+    else MG_RED_ADD(&e.gstats[MG_GS_CHEST_WITHDRAWN + item], (float)(-delta));
     e.gstats[MG_GS_CHEST_AMOUNT + item] = (float)v.amt[item];
   }
 }
@@ -497,8 +500,7 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
     const int distributed = shared_update(e, outputs, item, MG_OUT_AMOUNT(i));
     if (distributed > 0) {
       // integer-valued float counter: the sum does not depend on the order of the additions
-      if (e.concurrent) atomicAdd(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
-      else e.gstats[MG_GS_ASM_CREATED + item] += (float)distributed;
+      MG_RED_ADD(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
     }
   }
 #undef MG_IN_AMOUNT
@@ -535,10 +537,10 @@ MG_DEVICE MG_NOINLINE bool chest_on_use(EnvCtx& e, int chest_idx, int actor) {
     int item = deltas.item[i], d = deltas.val[i];
     if (d > 0) {
       int moved = transfer_resources(e, ai, ci, item, d, true);
-      if (moved > 0) { any = true; st[MG_AS_CHEST_DEPOSITED + item] += (float)moved; }
+      if (moved > 0) { any = true; MG_RED_ADD(&st[MG_AS_CHEST_DEPOSITED + item], (float)moved); }
     } else if (d < 0) {
       int moved = transfer_resources(e, ci, ai, item, -d, true);
-      if (moved > 0) { any = true; st[MG_AS_CHEST_WITHDRAWN + item] += (float)moved; }
+      if (moved > 0) { any = true; MG_RED_ADD(&st[MG_AS_CHEST_WITHDRAWN + item], (float)moved); }
     }
   }
   return any;
@@ -759,8 +761,12 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
   float total = 0.0f;
   for (int i = 0; i < n; i++) {
     const int32_t* rw = grp + MG_GRP_REWARDS + i * MG_RWD_WORDS;
-    float v = rw[MG_RWD_AGENT_STAT] >= 0 ? *agent_stat(e, ai, rw[MG_RWD_AGENT_STAT]) : 0.0f;
-    v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? e.gstats[rw[MG_RWD_GAME_STAT]] : 0.0f);
+    float v = 0.0f;
+    if (rw[MG_RWD_AGENT_STAT] >= 0) {
+      const float* sp = agent_stat(e, ai, rw[MG_RWD_AGENT_STAT]);
+      v = rw[MG_RWD_AGENT_STAT] < MG_HOT_STATS && e.hot != nullptr ? *sp : MG_LDCG(sp);
+    }
+    v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LDCG(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));
     if (rw[MG_RWD_HAS_MAX]) {
       float cap = MG_INT_AS_FLOAT(rw[MG_RWD_MAX]);

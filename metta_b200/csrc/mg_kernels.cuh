@@ -18,7 +18,7 @@
 // -DMG_TIMING: per-env cycle counts of the step kernel's phases in EnvRec::spare (tuning builds only)
 #ifdef MG_TIMING
 #define MG_TICK(i) do { const long long now__ = clock64(); tick_acc[i] += (uint32_t)(now__ - tick_last); tick_last = now__; } while (0)
-#define MG_SM_TICK(sm, i) do { if (lane == 0) { const long long now__ = clock64(); (sm).er.spare[i] += (uint32_t)(now__ - (sm).tick_last); (sm).tick_last = now__; } } while (0)
+#define MG_SM_TICK(sm, i) do { __syncwarp(); if (lane == 0) { const long long now__ = clock64(); (sm).ticks[i] += (uint32_t)(now__ - (sm).tick_last); (sm).tick_last = now__; } } while (0)
 #else
 #define MG_TICK(i) do { } while (0)
 #define MG_SM_TICK(sm, i) do { } while (0)
@@ -49,6 +49,9 @@ struct StepSmem {
   uint32_t intent[MAXA];  // per agent: bit 0 = act in the parallel pass, bits 8..15 action kind, 16..31 argument
   uint32_t ordered_mask;
   long long tick_last;
+#ifdef MG_TIMING
+  uint32_t ticks[16];
+#endif
   EnvRec er;
   EnvCtx ctx;  // warp-uniform; lives here so that passing it to out-of-line functions costs no stack traffic
 };
@@ -68,6 +71,7 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
   e.concurrent = false;
   e.batch = &b;
   e.asm_records_on_use = false;
+  e.inv_masks_off = b.inv_masks_off;
   for (int k = 0; k < 3; k++) e.req_mask[k] = e.con_mask[k] = 0x1FFFu;
   e.gstats = b.game_stats + (size_t)env * b.GS;
   e.n_asm = er.n_asm;
@@ -540,6 +544,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
         }
       }
     }
+    MG_SM_TICK(sm, 0);
     if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
       __syncwarp();
       accumulate_episode_warp(b, env, lane);
@@ -573,16 +578,17 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     break;
   }
   __syncwarp();
-  // the stat slots the rewards will read at the end of the step: start pulling them into L1 now
+  MG_SM_TICK(sm, 1);
+  // the stat slots the rewards will read at the end of the step (at L2, see MG_LDCG): start pulling them in now
   for (int ai = lane; ai < A; ai += 32) {
     const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
     const float* st = b.agent_stats + (abase + ai) * b.S;
     for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
       const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
-      if (slot >= MG_HOT_STATS) MG_PREFETCH_L1(st + slot);
+      if (slot >= MG_HOT_STATS) MG_PREFETCH_L2(st + slot);
     }
   }
-  if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L1(b.game_stats + (size_t)env * b.GS + lane * 32);
+  if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L2(b.game_stats + (size_t)env * b.GS + lane * 32);
   er.current_step += 1;
   if (lane == 0) sm.er = er;
   EnvCtx& e = sm.ctx;
@@ -641,10 +647,14 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
       }
     }
   }
+  MG_SM_TICK(sm, 3);
   // random processing order (mettagrid_c.cpp:591-593); the words it needs are fetched in one go
   MtStream rs = mt_stream(mt, sm.er.rng_idx);
   mt_prefetch_warp(rs, sm.rngbuf, lane);
-  std_shuffle_fast_warp(rs, lane, sm.order, A, reinterpret_cast<uint32_t*>(sm.scratch));
+  // the draws are always taken; the swaps are only applied if somebody needs the order (below)
+  uint32_t* draws = reinterpret_cast<uint32_t*>(sm.scratch);
+  const bool fast_shuffle = std_shuffle_draws_warp(rs, lane, A, draws);
+  if (!fast_shuffle) std_shuffle_warp(rs, lane, sm.order, A);
 
   if (lane == 0) sm.er.rng_idx = rs.idx;
   // out-of-range actions: counted once per priority pass, two passes (mettagrid_c.cpp:599-608)
@@ -657,6 +667,7 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
   }
   __syncwarp();
 
+  MG_SM_TICK(sm, 4);
   // ---- which agents can act independently of the processing order?
   // An action touches the mover's cell and the cell it moves into; using an assembler touches the
   // agents standing in the 3x3 block around it (they pay the inputs). Agents stand on distinct
@@ -670,7 +681,7 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
   // pass below in the shuffled order. Both sides of a conflict are ordered.
   uint32_t ordered_mask;
   if (A <= 32) {
-    if (lane == 0) sm.scratch[0] = 0;  // bits of agents that someone else's action can affect
+    if (lane == 0) sm.ordered_mask = 0u;  // bits of agents that someone else's action can affect
     __syncwarp();
     bool ordered = false;
     const uint32_t tkind = MG_GRID_KIND(my_target);
@@ -679,7 +690,7 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
     if (moving && (same_target & (same_target - 1u)) != 0u) ordered = true;                 // (1)
     if (moving && my_target != 0u && tkind == MG_GK_AGENT) {                                // (2)
       ordered = true;
-      atomicOr(reinterpret_cast<unsigned int*>(&sm.scratch[0]), 1u << MG_GRID_INDEX(my_target));
+      atomicOr(&sm.ordered_mask, 1u << MG_GRID_INDEX(my_target));
     }
     bool uses_asm = moving && tkind == MG_GK_ASM;
     if (moving && tkind == MG_GK_CHEST) ordered = true;                                     // (4)
@@ -693,7 +704,7 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
           const uint16_t g = e.grid[rr * b.W + cc];
           if (MG_GRID_KIND(g) == MG_GK_AGENT && (int)MG_GRID_INDEX(g) != lane) {
             ordered = true;
-            atomicOr(reinterpret_cast<unsigned int*>(&sm.scratch[0]), 1u << MG_GRID_INDEX(g));
+            atomicOr(&sm.ordered_mask, 1u << MG_GRID_INDEX(g));
           }
         }
     }
@@ -707,13 +718,17 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
       if (__ballot_sync(MG_FULL_MASK, hit) != 0u && lane == u) ordered = true;
     }
     __syncwarp();
-    if ((((uint32_t)sm.scratch[0]) >> lane) & 1u) ordered = true;
+    if ((sm.ordered_mask >> lane) & 1u) ordered = true;
+    __syncwarp();
     ordered_mask = __ballot_sync(MG_FULL_MASK, ordered && lane < A);
     if (lane < A) sm.intent[lane] = (my_valid && !ordered) ? (1u | ((uint32_t)my_kind << 8) | ((uint32_t)(my_arg & 0xFFFF) << 16)) : 0u;
   } else {
     ordered_mask = 0xFFFFFFFFu;
   }
-  if (lane == 0) sm.ordered_mask = ordered_mask;
+  if (lane == 0) {
+    sm.ordered_mask = ordered_mask;
+    if (fast_shuffle && ordered_mask != 0u) std_shuffle_apply(sm.order, A, draws);
+  }
   __syncwarp();
 
 }
@@ -740,7 +755,7 @@ MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, 
     if (lane == 0) e.concurrent = false;
     __syncwarp();
   }
-  MG_SM_TICK(sm, 2);
+  MG_SM_TICK(sm, 6);
   // the ordered action pass: later agents see what earlier agents did
   if (lane == 0 && ordered_mask != 0u) {
     for (int k = 0; k < A; k++) {
@@ -754,7 +769,7 @@ MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, 
     }
   }
   __syncwarp();
-  MG_SM_TICK(sm, 3);
+  MG_SM_TICK(sm, 7);
 }
 
 // Phase 4: what happens after the actions: regeneration, damage, clipper, assembler views.
@@ -830,6 +845,7 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
   }
   for (int i = lane; i < er.n_chest; i += 32) write_chest_tokens(b, e.chests[i], token_record(b, env, MG_GK_CHEST, (uint32_t)i));
   __syncwarp();
+  MG_SM_TICK(sm, 9);
   {
     uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
     const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
@@ -873,19 +889,20 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   if (env >= b.env_end) return;
   StepSmem<MAXA>& sm = smem[warp];
 #ifdef MG_TIMING
-  if (lane == 0) sm.tick_last = clock64();
+  if (lane == 0) { sm.tick_last = clock64(); for (int i = 0; i < 16; i++) sm.ticks[i] = 0; }
 #endif
   step_phase_load<MAXA>(b, sm, env, lane);
-#ifdef MG_TIMING
-  if (lane == 0) for (int i = 0; i < 5; i++) sm.er.spare[i] = 0;
-#endif
-  MG_SM_TICK(sm, 0);
+  MG_SM_TICK(sm, 2);
   step_phase_decide<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 1);
+  MG_SM_TICK(sm, 5);
   step_phase_act<MAXA>(b, sm, lane);
   step_phase_post<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 4);
+  MG_SM_TICK(sm, 8);
   step_phase_finish<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 11);
+#ifdef MG_TIMING
+  if (lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = sm.ticks[lane];
+#endif
 }
 
 // ---------------------------------------------------------------- observations

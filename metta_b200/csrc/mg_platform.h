@@ -22,7 +22,12 @@
 #define MG_INT_AS_FLOAT(x) __int_as_float(x)
 #define MG_LAUNCH_BOUNDS(t, b) __launch_bounds__(t, b)
 #define MG_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
+#define MG_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #define MG_LDG(p) __ldg(p)
+// Counters in HBM that nobody needs back within the step are bumped with a reduction (no load, no
+// stall); code that reads such a slot later in the same kernel reads it at L2, past any stale L1 line.
+#define MG_RED_ADD(p, v) ((void)atomicAdd((p), (v)))
+#define MG_LDCG(p) __ldcg(p)
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif
 

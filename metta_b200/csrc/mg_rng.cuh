@@ -127,17 +127,17 @@ MG_DEVICE inline void std_shuffle_warp(MtStream& s, int lane, uint8_t* order, in
   }
 }
 
-// The same shuffle with the draws computed side by side: draw d only depends on word d of the
-// stream (unless Lemire's method rejects a word, about once in 10^7 draws: then everything is redone
-// by the loop above), so lane d tempers word d and derives its pair of swap positions, and one lane
-// applies the swaps in order. `scratch` is shared memory for 32 words.
-MG_DEVICE inline void std_shuffle_fast_warp(MtStream& s, int lane, uint8_t* order, int n, uint32_t* scratch) {
+// The same shuffle in two halves, because the order only matters to the agents that go through the
+// ordered pass, while the draws always have to be taken. Draw d only depends on word d of the stream
+// (unless Lemire's method rejects a word, about once in 10^7 draws), so lane d tempers word d and
+// derives its pair of swap positions into `scratch` (shared memory, 32 words). Returns false when the
+// staged words do not cover the draws or a word was rejected: then nothing has been consumed and the
+// caller runs std_shuffle_warp.
+MG_DEVICE inline bool std_shuffle_draws_warp(MtStream& s, int lane, int n, uint32_t* scratch) {
   const int nd = n >> 1;  // draws: n even: 1 + (n - 2) / 2, n odd: (n - 1) / 2
+  if (n <= 1) return true;
   const uint32_t first = s.idx - s.buf_base;
-  if (n <= 1 || nd > 32 || s.buf_n == 0u || s.idx < s.buf_base || first + (uint32_t)nd > s.buf_n) {
-    std_shuffle_warp(s, lane, order, n);
-    return;
-  }
+  if (nd > 32 || s.buf_n == 0u || s.idx < s.buf_base || first + (uint32_t)nd > s.buf_n) return false;
   bool reject = false;
   if (lane < nd) {
     const bool even = (n & 1) == 0;
@@ -155,27 +155,27 @@ MG_DEVICE inline void std_shuffle_fast_warp(MtStream& s, int lane, uint8_t* orde
     const uint32_t x = (uint32_t)(product >> 32);
     scratch[lane] = (even && lane == 0) ? x : ((x / (sr + 1u)) | ((x % (sr + 1u)) << 16));
   }
-  if (__ballot_sync(MG_FULL_MASK, reject) != 0u) {
-    std_shuffle_warp(s, lane, order, n);
-    return;
-  }
-  __syncwarp();
-  if (lane == 0) {
-    for (int k = 0; k < n; k++) order[k] = (uint8_t)k;
-    int i = 1, d = 0;
-    if ((n & 1) == 0) {
-      const uint32_t j = scratch[0];
-      uint8_t t = order[1]; order[1] = order[j]; order[j] = t;
-      i = 2; d = 1;
-    }
-    for (; i < n; i += 2, d++) {
-      const uint32_t p0 = scratch[d] & 0xFFFFu, p1 = scratch[d] >> 16;
-      uint8_t t = order[i]; order[i] = order[p0]; order[p0] = t;
-      t = order[i + 1]; order[i + 1] = order[p1]; order[p1] = t;
-    }
-  }
+  if (__ballot_sync(MG_FULL_MASK, reject) != 0u) return false;
   s.idx += (uint32_t)nd;
   __syncwarp();
+  return true;
+}
+
+// Second half, one lane: apply the swaps std_shuffle_draws_warp left in `scratch`.
+MG_DEVICE inline void std_shuffle_apply(uint8_t* order, int n, const uint32_t* scratch) {
+  for (int k = 0; k < n; k++) order[k] = (uint8_t)k;
+  if (n <= 1) return;
+  int i = 1, d = 0;
+  if ((n & 1) == 0) {
+    const uint32_t j = scratch[0];
+    uint8_t t = order[1]; order[1] = order[j]; order[j] = t;
+    i = 2; d = 1;
+  }
+  for (; i < n; i += 2, d++) {
+    const uint32_t p0 = scratch[d] & 0xFFFFu, p1 = scratch[d] >> 16;
+    uint8_t t = order[i]; order[i] = order[p0]; order[p0] = t;
+    t = order[i + 1]; order[i + 1] = order[p1]; order[p1] = t;
+  }
 }
 
 // std::discrete_distribution<size_t>(weights)(g) (bits/random.tcc:2657-2730); generate_canonical

@@ -98,7 +98,8 @@ struct MgBatch {
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
-  int32_t cfg_words;           // length of cfg in int32 words
+  int32_t cfg_words;           // length of cfg in int32 words, including what mg_create appends to the blob
+  int32_t inv_masks_off;       // appended: per INVCFG record [MG_MAX_LIMITS] member masks, [MG_MAX_LIMITS] modifier masks
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
   // static token templates, built once per config on the host (mg_abi.cu build_templates):
@@ -136,6 +137,7 @@ struct MgBatch {
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]
   double* episode_accum;       // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce)
+  uint32_t* dbg;               // [N][16] cycle counters of the step kernel's phases (builds with -DMG_TIMING only, else null)
   // caller-owned buffers (set_buffers)
   uint8_t* obs;                // [N*A][T][3]
   uint8_t* terminals;          // [N*A]

@@ -1,1 +1,2 @@
-python bench.py --no-cpu-baseline --steps 4 --warmup 3 > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -k regex:mg_export --csv --log-file gpurun_out/launches_export.csv python bench.py --no-cpu-baseline --steps 4 --warmup 3 > gpurun_out/ncu.log 2>&1; tail -2 gpurun_out/ncu.log
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -3 gpurun_out/pytest_gpu.log
+./tools_bench_variants.sh default

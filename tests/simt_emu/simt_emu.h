@@ -28,6 +28,9 @@
 #define MG_DYN_SMEM(name) unsigned char* name = simt_emu::dyn_smem()
 #define MG_LAUNCH_BOUNDS(t, b)
 #define MG_PREFETCH_L1(p) ((void)(p))
+#define MG_PREFETCH_L2(p) ((void)(p))
+#define MG_RED_ADD(p, v) ((void)(*(p) += (v)))
+#define MG_LDCG(p) (*(p))
 #define MG_LDG(p) (*(p))
 #define MG_GRID_CONSTANT
 #define MG_FADD(a, b) ((float)(a) + (float)(b))

@@ -21,11 +21,11 @@ for s in range(20):
     if FLUSH: flush.fill_(s)
     torch.cuda.synchronize()
     b.step(); torch.cuda.synchronize()
-env=b.read_env()
-sp=env['spare'].astype(np.float64)
-names=['load','decide(shuffle,intent,conflicts)','act parallel','act ordered','post(regen,dmg,clip,asm)']
+sp=b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64)
+names=['load: loads+fold','load: reset/stage','load: rest(prefetch,ctx)','decide: intents','decide: shuffle draws','decide: conflicts+apply','act parallel','act ordered','post','finish: rewards+records','', 'finish: write-back']
 tot=sp.sum(1)
 print('N',N,'flush',FLUSH); print('per-env total cycles: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f'%(tot.mean(),np.percentile(tot,50),np.percentile(tot,90),np.percentile(tot,99),tot.max()))
-print('envs with ordered work: %.1f%%' % (100.0*(sp[:,3] > 2000).mean()))
+print('envs with ordered work: %.1f%%' % (100.0*(sp[:,7] > 2000).mean()))
 for i,n in enumerate(names):
+    if not n: continue
     c=sp[:,i]; print('%-34s mean %8.0f p50 %8.0f p99 %8.0f max %8.0f'%(n,c.mean(),np.percentile(c,50),np.percentile(c,99),c.max()))
