@@ -20,6 +20,8 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import Any, Optional, Sequence
 
+import time
+
 import numpy as np
 
 from .batch import Batch
@@ -27,7 +29,7 @@ from .config import MettaGridConfig
 from .layout import L
 from .lowering import LoweredConfig, lower_game_config
 from .maps import MapPool, build_pool, names_to_codes
-from .stats import agent_stat_names, game_stat_names
+from .stats import agent_stat_names, game_stat_names, game_stats_dict
 
 
 @dataclass
@@ -108,6 +110,15 @@ class GpuMettaGridVecEnv:
         self._episodes_reported = 0.0
         self._accum_prev: Optional[np.ndarray] = None
         self.driver_env = self
+        # Episode ends are decided by step counts alone (max_steps, early reset), so the host knows
+        # which envs finish on which step without reading a flag back from the GPU.
+        self.collect_infos = True
+        self._max_steps = int(game.max_steps)
+        self._steps = np.zeros(self.num_envs, dtype=np.int64)
+        self._early = np.zeros(self.num_envs, dtype=np.int64)
+        self._done = np.zeros(self.num_envs, dtype=bool)
+        self._seeds = np.zeros(self.num_envs, dtype=np.int64)
+        self._names_a = [agent_stat_names(lowered, g) for g in range(len(lowered.group_names))]
 
     # ---- pufferlib contract
     def async_reset(self, seed: Optional[int] = None) -> None:
@@ -117,6 +128,10 @@ class GpuMettaGridVecEnv:
         maps = np.arange(self.num_envs) % len(self.pool.codes)
         self.batch.reset(seeds.astype(np.uint32), maps.astype(np.int32))
         self._accum_prev = None
+        self._steps[:] = 0
+        self._done[:] = False
+        self._early[:] = 0
+        self._seeds[:] = seeds
         if self.host:
             self._download()
 
@@ -126,6 +141,15 @@ class GpuMettaGridVecEnv:
 
     def send(self, actions) -> None:
         torch = self._torch
+        # envs that ended on the last step start a new episode at the start of this one
+        # (MettaGridPufferEnv.step), then every env advances by one step
+        self._steps[self._done] = 0
+        self._early[self._done] = 0
+        self._steps += 1
+        limit = np.where(self._early > 0, self._early, np.iinfo(np.int64).max)
+        if self._max_steps > 0:
+            limit = np.minimum(limit, self._max_steps)
+        self._done = self._steps >= limit
         if self.host:
             a = np.ascontiguousarray(np.asarray(actions).reshape(-1), dtype=np.int32)
             self.batch.step_host(a, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
@@ -181,8 +205,52 @@ class GpuMettaGridVecEnv:
                 out["game/" + names_g[int(s)]] = float(acc[2 + S + s])
         return out
 
+    def set_early_reset(self, steps) -> None:
+        """EarlyResetHandler (mettagrid/envs/early_reset_handler.py:12-20): truncate the running episode of
+        env i once its step count reaches steps[i] (0 = never)."""
+        steps = np.ascontiguousarray(steps, dtype=np.uint32)
+        self.batch.set_early_reset(steps)
+        self._early[:] = steps
+
+    def get_episode_rewards(self):
+        """f32 [num_envs, agents_per_env] (MettaGrid::get_episode_rewards; CurriculumEnv takes its mean)."""
+        return self.batch.read_episode_rewards()
+
     def _infos(self) -> list[dict]:
-        return []
+        """One dict per env whose episode ended on the last step, shaped like the reference's
+        StatsTracker.on_episode_end (mettagrid/envs/stats_tracker.py:26-76): ``game`` stats, ``agent``
+        stats averaged over the env's agents, ``attributes``. The stats are still in HBM at this point:
+        the env is rebuilt at the start of the next step."""
+        if not self.collect_infos or not self._done.any():
+            return []
+        idx = np.nonzero(self._done)[0]
+        astats = self.batch.read_agent_stats()[idx].astype(np.float64)   # [n, A, S]
+        gstats = self.batch.read_game_stats()[idx]
+        groups = self.batch.read_agents()["group"][idx]
+        rewards = self.batch.read_episode_rewards()[idx]
+        recs = self.batch.read_env()[idx]
+        now = time.time()
+        out = []
+        A = self.agents_per_env
+        for k, env in enumerate(idx):
+            agent: dict[str, float] = {}
+            for g in np.unique(groups[k]):
+                total = astats[k][groups[k] == g].sum(axis=0)
+                names = self._names_a[int(g)]
+                for slot in np.nonzero(total)[0]:
+                    for n in names.get(int(slot), []):
+                        agent[n] = agent.get(n, 0.0) + float(total[slot])
+            out.append({
+                "game": game_stats_dict(self.lowered, gstats[k], self.pool.codes[int(recs["map_idx"][k])]),
+                "agent": {n: v / A for n, v in agent.items()},
+                "attributes": {
+                    "seed": int(self._seeds[env]), "map_w": int(self.pool.codes.shape[2]), "map_h": int(self.pool.codes.shape[1]),
+                    "steps": int(recs["current_step"][k]), "max_steps": self._max_steps, "completion_time": now,
+                },
+                "episode_rewards": rewards[k].copy(),
+                "env_index": int(env),
+            })
+        return out
 
     def reduce_episode_stats(self):
         """All-reduce (SUM) the episode accumulators over the process group: the only collective of

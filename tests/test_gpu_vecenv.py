@@ -1,0 +1,124 @@
+"""GpuMettaGridVecEnv on a GPU: the pufferlib / TrainingEnvironment contract, episode-end infos
+against the oracle's stats, host mode against device mode, and a rollout loop whose policy reads
+the observation tensor the kernels write."""
+
+import numpy as np
+import pytest
+
+from metta_b200.lowering import lower_game_config
+from metta_b200.maps import names_to_codes
+from metta_b200.stats import agent_stats_dict, game_stats_dict
+from harness import random_actions
+from scenarios import SCENARIOS
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(name, n, **kw):
+    from metta_b200.vecenv import GpuMettaGridVecEnv
+
+    cfg, grid = SCENARIOS[name]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    return cfg, low, codes, GpuMettaGridVecEnv(cfg, n, map_codes=codes[None], seed=11, **kw)
+
+
+def test_contract_and_episode_infos_match_oracle():
+    import torch
+
+    from oracle.oracle import OracleEnv
+
+    n = 6
+    cfg, low, codes, env = _make("tiny_truncating", n)
+    A, T = cfg.game.num_agents, cfg.game.obs.num_tokens
+    assert env.num_agents == n * A and env.single_observation_space.shape == (T, 3)
+    assert env.single_action_space.n == len(low.action_names)
+    obs, info = env.reset(seed=11)
+    assert obs.shape == (n * A, T, 3) and obs.dtype == torch.uint8 and obs.is_cuda and info == {}
+    orcs = [OracleEnv(low.words, codes, 11 + i) for i in range(n)]
+    rng = np.random.RandomState(3)
+    for step in range(1, 2 * cfg.game.max_steps + 1):
+        a = random_actions(rng, cfg, low, n * A)
+        env.send(torch.from_numpy(a).cuda())
+        o, r, d, t, ta, infos, ids, mask = env.recv()
+        if step <= cfg.game.max_steps:
+            for i, orc in enumerate(orcs):
+                orc.step(a[i * A : (i + 1) * A])
+                assert np.array_equal(o[i * A : (i + 1) * A].cpu().numpy(), orc.observations)
+        if step % cfg.game.max_steps == 0:
+            assert bool(t.all()) and len(infos) == n
+        else:
+            assert not bool(t.any()) and infos == []
+        if step == cfg.game.max_steps:
+            groups = env.batch.read_agents()["group"]
+            for i, (orc, inf) in enumerate(zip(orcs, infos)):
+                assert inf["env_index"] == i and inf["attributes"]["steps"] == cfg.game.max_steps
+                assert inf["attributes"]["seed"] == 11 + i
+                assert inf["game"] == game_stats_dict(low, orc.game_stats(), codes)
+                want: dict[str, float] = {}
+                for ai in range(A):
+                    for k, v in agent_stats_dict(low, int(groups[i, ai]), orc.agent_stats()[ai]).items():
+                        want[k] = want.get(k, 0.0) + v
+                want = {k: v / A for k, v in want.items()}
+                assert inf["agent"].keys() == want.keys()
+                for k in want:
+                    assert inf["agent"][k] == pytest.approx(want[k], rel=1e-12), k
+                assert np.array_equal(inf["episode_rewards"], orc.episode_rewards())
+    got = env.get_observations()
+    assert got[6] == slice(0, n * A) and got[8] == n * A
+    env.close()
+
+
+def test_host_mode_equals_device_mode():
+    import torch
+
+    n = 5
+    cfg, low, codes, dev_env = _make("kitchen_sink", n)
+    _, _, _, host_env = _make("kitchen_sink", n, host=True)
+    A = cfg.game.num_agents
+    dev_env.reset(seed=4)
+    h_obs, _ = host_env.reset(seed=4)
+    assert isinstance(h_obs, np.ndarray)
+    assert np.array_equal(h_obs, dev_env.observations.cpu().numpy())
+    rng = np.random.RandomState(8)
+    for _ in range(30):
+        a = random_actions(rng, cfg, low, n * A)
+        o, r, d, t, _ = dev_env.step(torch.from_numpy(a).cuda())
+        ho, hr, hd, ht, _ = host_env.step(a)
+        assert np.array_equal(ho, o.cpu().numpy()) and np.array_equal(hr, r.cpu().numpy())
+        assert np.array_equal(hd, d.cpu().numpy()) and np.array_equal(ht, t.cpu().numpy())
+    dev_env.close()
+    host_env.close()
+
+
+def test_rollout_loop_with_a_torch_policy_reads_the_kernel_output_in_place():
+    """configs[4] in small: env step and policy forward alternate on one stream with no host copy;
+    the policy's input is the tensor the observation kernel writes."""
+    import torch
+
+    from metta_b200.builders import make_arena
+    from metta_b200.maps import arena_maps
+    from metta_b200.vecenv import GpuMettaGridVecEnv
+
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    env = GpuMettaGridVecEnv(cfg, 64, map_codes=arena_maps(low, 8, seed=5), seed=1)
+    env.collect_infos = False
+    obs, _ = env.reset()
+    ptr = obs.data_ptr()
+    torch.manual_seed(0)
+    emb = torch.nn.Embedding(256, 16).cuda()
+    head = torch.nn.Linear(16, env.single_action_space.n).cuda()
+    total = torch.zeros((), device="cuda")
+    with torch.no_grad():
+        for _ in range(20):
+            feats = emb(obs[:, :, 1].long()) * (obs[:, :, 0:1] != 255)   # feature-id embedding, padding masked
+            logits = head(feats.sum(1))
+            actions = torch.distributions.Categorical(logits=logits).sample().to(torch.int32)
+            obs, rew, term, trunc, _ = env.step(actions)
+            assert obs.data_ptr() == ptr
+            total += rew.sum()
+    assert torch.isfinite(total).item()
+    st = env.batch.read_env()
+    assert (st["current_step"] == 20).all()
+    env.close()
