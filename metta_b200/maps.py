@@ -138,3 +138,22 @@ def arena_maps(lowered: LoweredConfig, num_maps: int, seed: int = 0, num_agents:
             r0, c0 = border + (k // cols) * room, border + (k % cols) * room
             out[m, r0 : r0 + room, c0 : c0 + room] = 0
     return out
+
+
+def random_maps(lowered: LoweredConfig, num_maps: int, height: int, width: int, counts: dict[str, int], seed: int = 0,
+                border: int = 1) -> np.ndarray:
+    """Synthetic maps as cell codes [M,H,W]: a wall border and `counts[name]` cells of each named
+    object (agents included, e.g. "agent.agent") scattered uniformly inside. Stands in for the
+    reference's random scene (mapgen/scenes/random.py:19-70) when a test or benchmark needs many maps."""
+    cc = lowered.cell_codes
+    fill = np.concatenate([np.full(n, cc[name], dtype=np.uint8) for name, n in counts.items()])
+    inner_h, inner_w = height - 2 * border, width - 2 * border
+    if len(fill) > inner_h * inner_w:
+        raise ValueError("random_maps: more objects than cells")
+    rng = np.random.default_rng(seed)
+    out = np.full((num_maps, height, width), cc["wall"], dtype=np.uint8)
+    for m in range(num_maps):
+        cells = np.zeros(inner_h * inner_w, dtype=np.uint8)
+        cells[rng.permutation(inner_h * inner_w)[: len(fill)]] = rng.permutation(fill)
+        out[m, border : height - border, border : width - border] = cells.reshape(inner_h, inner_w)
+    return out

@@ -95,5 +95,30 @@ def main():
         run(name, cfg, grid, 7, steps, restarts=restarts, invalid_every=inv)
 
 
+def cogames():
+    """cogames missions (BASELINE configs[3]): the mission's own MettaGridConfig (157 actions: noop, 4
+    moves, 152 vibes; assemblers keyed by vibes, chests, chargers, regen, clipper with clip_period 0)
+    through the reference's own lowering and its own map builder."""
+    sys.path.insert(0, "/root/reference/packages/cogames/src")
+    from cogames.cogs_vs_clips import missions as M
+    from mettagrid.config.mettagrid_c_config import convert_to_cpp_game_config
+
+    for name, mission, cogs, steps in (
+        ("cogames_vibe_check", M.VibeCheckMission, 4, 300),
+        ("cogames_machina_chests", M.Machina1OpenWorldWithChestsMission, 4, 200),
+    ):
+        ref_cfg = mission.model_copy(update={"num_cogs": cogs}).make_env()
+        grid = ref_cfg.game.map_builder.create().build_for_num_agents(ref_cfg.game.num_agents).grid
+        c_cfg = convert_to_cpp_game_config(ref_cfg.game.model_dump())
+        dump = ref_cfg.model_dump()
+        dump["game"]["map_builder"] = None
+        cfg = MettaGridConfig.from_reference(dump)
+        run(name, cfg, grid, 5, steps, c_cfg=c_cfg)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "cogames":
+        cogames()
+    else:
+        main()
+        cogames()

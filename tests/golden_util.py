@@ -6,7 +6,7 @@ import numpy as np
 from metta_b200.config import MettaGridConfig
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-NAMES = ["arena", "kitchen_sink", "tiny_truncating", "clipped_start"]
+NAMES = ["arena", "kitchen_sink", "tiny_truncating", "clipped_start", "cogames_vibe_check", "cogames_machina_chests"]
 
 
 def load(name: str):

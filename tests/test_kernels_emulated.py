@@ -26,6 +26,23 @@ def test_emulated_kernels_match_oracle(name, steps, emu_lib):
     ls.close()
 
 
+@pytest.mark.parametrize("name,steps", [("cogames_vibe_check", 60), ("cogames_machina_chests", 25)])
+def test_emulated_cogames_missions(name, steps, emu_lib):
+    """cogames missions (157 actions, vibe-keyed protocols, chests, chargers, clip_period 0): the
+    reference's own config and map from the golden fixture, kernels vs oracle in lockstep."""
+    from golden_util import load
+
+    cfg, grid, _ = load(name)
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=2, seeds=[5, 6], clib=emu_lib)
+    ls.compare_outputs()
+    rng = np.random.RandomState(21)
+    for s in range(steps):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+    ls.compare_state()
+    ls.close()
+
+
 def test_emulated_arena(emu_lib):
     cfg = make_arena(24)
     low = lower_game_config(cfg.game, 62, 62)
