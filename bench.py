@@ -134,24 +134,31 @@ def cpu_throughput(procs: int, envs_per_proc: int, steps: int):
     return total / slowest, kind, slowest
 
 
+def workload_name(n_envs, agents, tokens):
+    return f"arena, {n_envs} envs x {agents} agents per GPU, random actions, 62x62 synthetic maps, 11x11 window, {tokens} tokens"
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))
     envs_per_proc, steps_per_sample = 4, 100
-    times, value, kind = [], 0.0, "port"
+    times, units, kind = [], 0.0, "port"
     for _ in range(args.warmup):
         cpu_throughput(cores, envs_per_proc, 50)
     for _ in range(args.steps):
-        value, kind, secs = cpu_throughput(cores, envs_per_proc, steps_per_sample)
+        v, kind, secs = cpu_throughput(cores, envs_per_proc, steps_per_sample)
         times.append(secs)
-    sample = f"{cores} processes x {envs_per_proc} arena envs x {steps_per_sample} steps per bench step"
+        units += v * secs
+    value = units / float(np.sum(times))
+    sample = (f"each bench step = {cores} processes x {envs_per_proc} arena envs x {steps_per_sample} env steps of the reference's "
+              f"C++ core ({kind}) on the host cores, a bounded sample of the {args.envs}-env workload")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * float(np.mean(times)), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "arena 24 agents, random actions, reference C++ core on host CPU cores", "sample": sample},
+        "config": {"workload": workload_name(args.envs, AGENTS, 200), "envs_per_gpu": args.envs, "agents_per_env": AGENTS, "sample": sample},
         "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -307,7 +314,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"arena, {N} envs x {A} agents per GPU, random actions, 62x62 synthetic maps, 11x11 window, {T} tokens",
+            "config": {"workload": workload_name(N, A, T),
                        "envs_per_gpu": N, "agents_per_env": A, "l2": "flushed between timed steps (256 MiB fill" + (", then 256 MiB streamed read)" if args.flush == "write+read" else ")"),
                        "parallelism": f"env shards x{world}, no data-path collective"},
             "clocks": clocks,
