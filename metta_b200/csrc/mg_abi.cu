@@ -24,6 +24,17 @@ static thread_local std::string g_err;
 #ifndef MG_CFG_SMEM_LIMIT
 #define MG_CFG_SMEM_LIMIT 0
 #endif
+#ifndef MG_DEFAULT_STEP_MODE
+#define MG_DEFAULT_STEP_MODE 0
+#endif
+// observation CTAs per SM that run beside the step kernel in queue mode (the rest of the SM stays with
+// the step kernel, so it always makes progress), and that join once the step kernel has finished
+#ifndef MG_QUEUE_OBS_CTAS_EARLY
+#define MG_QUEUE_OBS_CTAS_EARLY 4
+#endif
+#ifndef MG_QUEUE_OBS_CTAS_LATE
+#define MG_QUEUE_OBS_CTAS_LATE 4
+#endif
 #define MG_OK 0
 #define MG_ERR_ARG 1
 #define MG_ERR_CUDA 2
@@ -58,6 +69,11 @@ struct MgEnvs {
   cudaStream_t chunk_stream[MG_MAX_CHUNKS], capture_stream;
   cudaEvent_t ev_fork, ev_join[MG_MAX_CHUNKS];
   int chunks;
+  // 1: step and observation kernels run side by side, finished envs handed over through a queue
+  // (enqueue_queue_step); 0: slices of envs, each slice's observation kernel behind its step kernel
+  int step_mode;
+  int sm_count;
+  int q_early, q_late;  // observation CTAs per SM beside / behind the step kernel in queue mode
   bool graph_dirty;
   cudaGraph_t graph;
   cudaGraphExec_t graph_exec;
@@ -304,9 +320,22 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   if (const char* env_chunks = getenv("MG_CHUNKS")) e->chunks = atoi(env_chunks);  // tuning knob
   if (e->chunks < 1) e->chunks = 1;
   if (e->chunks > MG_MAX_CHUNKS) e->chunks = MG_MAX_CHUNKS;
+  e->step_mode = MG_DEFAULT_STEP_MODE;
+  if (const char* env_mode = getenv("MG_STEP_MODE")) e->step_mode = strcmp(env_mode, "queue") == 0 ? 1 : 0;  // tuning knob
+  e->q_early = MG_QUEUE_OBS_CTAS_EARLY;
+  e->q_late = MG_QUEUE_OBS_CTAS_LATE;
+  if (const char* v = getenv("MG_QUEUE_EARLY")) e->q_early = atoi(v);
+  if (const char* v = getenv("MG_QUEUE_LATE")) e->q_late = atoi(v);
+#ifndef MG_SIMT_EMU
+  CUDA_TRY(cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, device));
+#else
+  e->sm_count = 1;
+#endif
+  TRY(dev_alloc(e, &b.qctl, 1));
+  TRY(dev_alloc(e, &b.queue, N));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->capture_stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
-  for (int i = 0; i < e->chunks; i++) {
+  for (int i = 0; i < (e->chunks < 2 ? 2 : e->chunks); i++) {
     CUDA_TRY(cudaStreamCreateWithFlags(&e->chunk_stream[i], cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
   }
@@ -467,6 +496,49 @@ static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* 
   return MG_OK;
 }
 
+#ifndef MG_SIMT_EMU
+static int launch_obs_queue(MgEnvs* e, const MgBatch& b, cudaStream_t s, int ctas_per_sm) {
+  const int slot = (b.T * 3 + 16 + 15) & ~15;
+  const int cpl = (b.obs_cells + 31) / 32;
+  const int cpl_t = cpl <= 1 ? 1 : cpl <= 2 ? 2 : cpl <= 4 ? 4 : 8;
+  const size_t smem = (size_t)(slot + MG_OBS_DESC_BYTES(cpl_t)) * MG_OBS_WARPS;
+  const int grid = e->sm_count * ctas_per_sm;
+  if (cpl_t == 1) { MG_LAUNCH(mg_obs_queue_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b); }
+  else if (cpl_t == 2) { MG_LAUNCH(mg_obs_queue_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b); }
+  else if (cpl_t == 4) { MG_LAUNCH(mg_obs_queue_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, b); }
+  else { MG_LAUNCH(mg_obs_queue_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, b); }
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+// Queue mode: [begin] -> { step kernel (one env per CTA) -> late observation CTAs } beside { early
+// observation CTAs }, joined back into `s`. Observation tasks are handed out in the order envs finish.
+static int enqueue_queue_step(MgEnvs* e, cudaStream_t s) {
+  const MgBatch& b = e->b;
+  int rc;
+  MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaEventRecord(e->ev_fork, s));
+  cudaStream_t sa = e->chunk_stream[0], sb = e->chunk_stream[1];
+  CUDA_TRY(cudaStreamWaitEvent(sa, e->ev_fork, 0));
+  CUDA_TRY(cudaStreamWaitEvent(sb, e->ev_fork, 0));
+  const int n = b.env_end - b.env_begin;
+  if (b.A <= 32) { MG_LAUNCH(mg_step_queue_kernel<32>, n, 32, sizeof(StepSmem<32>), sa, b); }
+  else { MG_LAUNCH(mg_step_queue_kernel<MG_MAX_AGENTS>, n, 32, sizeof(StepSmem<MG_MAX_AGENTS>), sa, b); }
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (e->q_early > 0 && (rc = launch_obs_queue(e, b, sb, e->q_early)) != MG_OK) return rc;
+  if (e->q_late > 0 && (rc = launch_obs_queue(e, b, sa, e->q_late)) != MG_OK) return rc;
+  CUDA_TRY(cudaEventRecord(e->ev_join[0], sa));
+  CUDA_TRY(cudaEventRecord(e->ev_join[1], sb));
+  CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[0], 0));
+  CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[1], 0));
+  return MG_OK;
+}
+#endif
+
 // Start episodes: seeds u32 [N], map index i32 [N], optional mask u8 [N] (host pointers; null mask = all).
 // Writes the initial observation and clears rewards/terminals/truncations of the reset envs
 // (MettaGrid ctor + set_buffers/_init_buffers, mettagrid_c.cpp:46-155,264-289).
@@ -511,7 +583,7 @@ static int capture_step_graph(MgEnvs* e, const MgHostTargets* ht, cudaGraph_t* g
   if (*graph) { cudaGraphDestroy(*graph); *graph = nullptr; }
   const long long before = e->launches;
   CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
-  int rc = enqueue_chunked_step(e, e->capture_stream, ht);
+  int rc = (e->step_mode == 1 && ht == nullptr) ? enqueue_queue_step(e, e->capture_stream) : enqueue_chunked_step(e, e->capture_stream, ht);
   cudaError_t end = cudaStreamEndCapture(e->capture_stream, graph);
   e->launches = before;
   if (rc != MG_OK) return rc;
@@ -526,7 +598,7 @@ int mg_step(void* h, void* stream) {
   if (!e) return fail(MG_ERR_ARG, "mg_step: null handle");
   if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_step: maps or buffers missing");
   cudaStream_t s = (cudaStream_t)stream;
-  if (e->chunks <= 1) {
+  if (e->chunks <= 1 && e->step_mode != 1) {
     int rc = launch_step_slice(e, e->b, s);
     return rc != MG_OK ? rc : launch_obs(e, s, nullptr);
   }
@@ -539,7 +611,7 @@ int mg_step(void* h, void* stream) {
     e->graph_dirty = false;
   }
   CUDA_TRY(cudaGraphLaunch(e->graph_exec, s));
-  e->launches += 2LL * e->chunks;
+  e->launches += e->step_mode == 1 ? 2 + (e->q_early > 0) + (e->q_late > 0) : 2LL * e->chunks;
   return MG_OK;
 #endif
 }
@@ -821,6 +893,11 @@ int mg_sync(void* h) {
   if (!e) return fail(MG_ERR_ARG, "mg_sync: null handle");
   CUDA_TRY(cudaSetDevice(e->device));
   CUDA_TRY(cudaDeviceSynchronize());
+  if (e->b.qctl != nullptr) {
+    MgQueueCtl ctl;
+    CUDA_TRY(cudaMemcpy(&ctl, e->b.qctl, sizeof(ctl), cudaMemcpyDeviceToHost));
+    if (ctl.error != 0) return fail(MG_ERR_CUDA, "mg_sync: an observation CTA gave up waiting for the step kernel (queue mode); results are incomplete");
+  }
   return MG_OK;
 }
 

@@ -859,6 +859,26 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
   if (lane == 0) b.env[env] = er;
 }
 
+// One env, one warp: the five phases.
+template <int MAXA>
+MG_DEVICE inline void step_env_warp(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
+#ifdef MG_TIMING
+  if (lane == 0) { sm.tick_last = clock64(); for (int i = 0; i < 16; i++) sm.ticks[i] = 0; }
+#endif
+  step_phase_load<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 2);
+  step_phase_decide<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 5);
+  step_phase_act<MAXA>(b, sm, lane);
+  step_phase_post<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 8);
+  step_phase_finish<MAXA>(b, sm, env, lane);
+  MG_SM_TICK(sm, 11);
+#ifdef MG_TIMING
+  if (lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = sm.ticks[lane];
+#endif
+}
+
 // MAXA: agents per env the shared-memory staging is sized for (32 or MG_MAX_AGENTS)
 template <int MAXA>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_kernel(const MG_GRID_CONSTANT MgBatch b_param, int cfg_bytes_in_smem) {
@@ -887,52 +907,70 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   const MgBatch& b = batch_s;
   const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
   if (env >= b.env_end) return;
-  StepSmem<MAXA>& sm = smem[warp];
-#ifdef MG_TIMING
-  if (lane == 0) { sm.tick_last = clock64(); for (int i = 0; i < 16; i++) sm.ticks[i] = 0; }
-#endif
-  step_phase_load<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 2);
-  step_phase_decide<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 5);
-  step_phase_act<MAXA>(b, sm, lane);
-  step_phase_post<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 8);
-  step_phase_finish<MAXA>(b, sm, env, lane);
-  MG_SM_TICK(sm, 11);
-#ifdef MG_TIMING
-  if (lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = sm.ticks[lane];
-#endif
+  step_env_warp<MAXA>(b, smem[warp], env, lane);
 }
 
-// ---------------------------------------------------------------- observations
-template <int CPL>
-MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
-  MG_DYN_SMEM(dyn);
+#ifndef MG_SIMT_EMU
+// ---- the same step with one env per CTA, handing every finished env to the observation kernel that
+// runs beside it (mg_obs_queue_kernel) instead of making it wait for the slowest env of a slice.
+// One-warp CTAs give their registers back as soon as their env is done, which is what lets the
+// observation CTAs in.
+#ifndef MG_QUEUE_STEP_MIN_CTAS
+#define MG_QUEUE_STEP_MIN_CTAS 24
+#endif
+template <int MAXA>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(32, MG_QUEUE_STEP_MIN_CTAS) mg_step_queue_kernel(const MG_GRID_CONSTANT MgBatch b) {
+  MG_DYN_SMEM(dyn_smem);
+  StepSmem<MAXA>& sm = *reinterpret_cast<StepSmem<MAXA>*>(dyn_smem);
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
-  if (ai >= b.A) return;
-  if (mask != nullptr && !mask[env]) return;
+  const int env = b.env_begin + (int)blockIdx.x;
+  if (env >= b.env_end) return;
+  step_env_warp<MAXA>(b, sm, env, lane);
+  // publish: every lane's writes first, then the entry
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) {
+    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&b.qctl->epoch);
+    const uint32_t pos = atomicAdd(&b.qctl->tail, 1u);
+    *reinterpret_cast<volatile unsigned long long*>(b.queue + pos) = ((unsigned long long)epoch << 32) | (unsigned long long)(uint32_t)env;
+  }
+}
+
+MG_GLOBAL void mg_queue_begin_kernel(MgQueueCtl* ctl) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    ctl->epoch += 1u;
+    ctl->tail = 0u;
+    ctl->head = 0u;
+  }
+}
+#endif  // !MG_SIMT_EMU
+
+// ---------------------------------------------------------------- observations
+// One agent's row by one warp. `warp_smem`: this warp's (slot + MG_OBS_DESC_BYTES(CPL)) bytes of shared
+// memory, 16-byte aligned: [row image | cell descriptors].
+template <int CPL>
+MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* warp_smem) {
   const size_t g = (size_t)env * b.A + ai;  // global agent index
   const int row_bytes = b.T * 3;
   const int slot = (row_bytes + 16 + 15) & ~15;  // room to mirror the row's misalignment
   uint8_t* out = b.obs + (size_t)g * row_bytes;
   const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
-  uint8_t* base = dyn + (size_t)warp * (slot + MG_OBS_DESC_BYTES(CPL));  // 16-byte aligned: [row image | cell descriptors]
+  uint8_t* base = warp_smem;  // 16-byte aligned: [row image | cell descriptors]
   uint8_t* row = base + mis;                     // row and out are congruent mod 16
   uint2* desc = reinterpret_cast<uint2*>(base + slot);
   {
     uint4 ff;
     ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
     uint4* p = reinterpret_cast<uint4*>(base);
-    const int n16 = slot >> 4;
+    const int n16 = slot >> 4;  // 39 for 200 tokens: two rounds, spelled out; the loop is for longer rows
+    if (lane < n16) p[lane] = ff;
+    if (lane + 32 < n16) p[lane + 32] = ff;
 #pragma unroll 1
-    for (int i = lane; i < n16; i += 32) p[i] = ff;
+    for (int i = lane + 64; i < n16; i += 32) p[i] = ff;
   }
   __syncwarp();
   const uint32_t current_step = b.env[env].current_step;
-  const int attempted = obs_encode_agent_warp<CPL, true>(b, env, ai, lane, row, desc, current_step);
+  const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step);
   __syncwarp();
   // store: bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
   const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
@@ -942,8 +980,10 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   {
     const uint4* s = reinterpret_cast<const uint4*>(row + head);
     uint4* d = reinterpret_cast<uint4*>(out + head);
+    if (lane < n16) d[lane] = s[lane];
+    if (lane + 32 < n16) d[lane + 32] = s[lane + 32];
 #pragma unroll 1
-    for (int i = lane; i < n16; i += 32) d[i] = s[i];
+    for (int i = lane + 64; i < n16; i += 32) d[i] = s[i];
   }
   if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
   if (lane == 0) {
@@ -952,6 +992,63 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
     tc[1] = (uint16_t)attempted;
   }
 }
+
+template <int CPL>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
+  MG_DYN_SMEM(dyn);
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
+  if (ai >= b.A) return;
+  if (mask != nullptr && !mask[env]) return;
+  const int slot = (b.T * 3 + 16 + 15) & ~15;
+  obs_row_warp<CPL>(b, env, ai, lane, dyn + (size_t)warp * (slot + MG_OBS_DESC_BYTES(CPL)));
+}
+
+#ifndef MG_SIMT_EMU
+// The consumer side of the queue: CTAs take (env, group of MG_OBS_WARPS agents) tasks in the order
+// envs finish their step. A task whose env has not been published yet is waited for (the step kernel
+// is resident and makes progress on its own); the wait is bounded so that a broken launch ends with
+// an error flag instead of a hung GPU.
+#define MG_QUEUE_WAIT_CYCLES 6000000000ll /* ~3 s */
+template <int CPL>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_queue_kernel(const MG_GRID_CONSTANT MgBatch b) {
+  MG_DYN_SMEM(dyn);
+  MG_SHARED int s_task[2];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int slot = (b.T * 3 + 16 + 15) & ~15;
+  uint8_t* warp_smem = dyn + (size_t)warp * (slot + MG_OBS_DESC_BYTES(CPL));
+  const int groups = (b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS;
+  const uint32_t total = (uint32_t)(b.env_end - b.env_begin) * (uint32_t)groups;
+  for (;;) {
+    if (threadIdx.x == 0) {
+      int env = -1, group = 0;
+      const uint32_t t = atomicAdd(&b.qctl->head, 1u);
+      if (t < total) {
+        const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&b.qctl->epoch);
+        const volatile unsigned long long* entry = b.queue + t / (uint32_t)groups;
+        const long long t0 = clock64();
+        for (;;) {
+          const unsigned long long v = *entry;
+          if ((uint32_t)(v >> 32) == epoch) { env = (int)(uint32_t)v; break; }
+          if (clock64() - t0 > MG_QUEUE_WAIT_CYCLES) { atomicExch(&b.qctl->error, 1u); break; }
+          MG_NANOSLEEP(200);
+        }
+        group = (int)(t % (uint32_t)groups);
+        __threadfence();
+      }
+      s_task[0] = env;
+      s_task[1] = group;
+    }
+    __syncthreads();
+    const int env = s_task[0], ai = s_task[1] * MG_OBS_WARPS + warp;
+    __syncthreads();
+    if (env < 0) return;
+    if (ai < b.A) obs_row_warp<CPL>(b, env, ai, lane, warp_smem);
+  }
+}
+#endif  // !MG_SIMT_EMU
 
 // Host export of observations for mg_step_host (page-locked caller buffer, written over PCIe by the
 // SMs): a row only differs from what the host already holds in its first max(previous, current)

@@ -141,6 +141,119 @@ MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, in
   return n_global + (total & 0xFFFF);
 }
 
+// The emitting encoder the observation kernels use. Same result as obs_encode_agent_warp<CPL, true>,
+// arranged for fewer issued instructions: most window cells are empty, so after the grid gather the
+// warp compacts its non-empty cells (ballots + popcounts, window order kept) into shared memory and
+// then looks at one OBJECT per lane (record header, cooldown, token count, prefix sum, descriptor)
+// instead of CPL cells per lane. The cell list shares `desc`'s second half: an entry is read before the
+// descriptors written in the same round can reach it (descriptors are 8 bytes, at most one per object).
+template <int CPL>
+MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step) {
+  const int32_t* cfg = b.cfg;
+  const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
+  const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
+  const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
+  const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
+  const int T = b.T;
+  uint32_t* cells = reinterpret_cast<uint32_t*>(desc) + CPL * 32;
+
+  // ---- global tokens: prepared by the step kernel, copied byte by byte
+  const uint8_t* gt = b.gtok + ((size_t)env * b.A + ai) * MG_GTOK_STRIDE;
+  const int n_global = gt[0];
+  {
+    const int nb = (n_global < T ? n_global : T) * 3;  // <= 63 bytes (MG_GTOK_STRIDE)
+    if (lane < nb) row[lane] = gt[1 + lane];
+    if (lane + 32 < nb) row[lane + 32] = gt[33 + lane];
+  }
+
+  // ---- pass 1a: grid values of my CPL cells; non-empty ones go to the cell list in window order
+  const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);
+  uint32_t cell[CPL];  // grid value | location << 16, 0 = nothing there
+  const uint32_t lower = (1u << lane) - 1u;
+  int rank = 0, n_obj = 0;
+#pragma unroll
+  for (int j = 0; j < CPL; j++) {
+    const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
+    const int r = my_r + (int)(loc >> 4) - hr, c = my_c + (int)(loc & 0xF) - wr;
+    uint32_t g = 0;
+    if (loc != 0xFFu && (unsigned)r < (unsigned)b.H && (unsigned)c < (unsigned)b.W) g = grid[r * b.W + c];
+    cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
+  }
+#pragma unroll
+  for (int j = 0; j < CPL; j++) {
+    const uint32_t m = __ballot_sync(MG_FULL_MASK, cell[j] != 0u);
+    rank += __popc(m & lower);
+    n_obj += __popc(m);
+  }
+#pragma unroll
+  for (int j = 0; j < CPL; j++)
+    if (cell[j] != 0u) cells[rank++] = cell[j];
+  __syncwarp();
+
+  // ---- pass 1b: one object per lane: header of its token record, token offset, descriptor
+  const uint8_t* ebase = b.etok + (((size_t)env * b.rec_slots) << b.rec_shift);
+  const uint64_t kind_base = (uint64_t)b.rec_kind_base_lo | ((uint64_t)b.rec_kind_base_hi << 32);
+  int pos_base = n_global, di_base = 0;
+#pragma unroll 1
+  for (int o0 = 0; o0 < n_obj; o0 += 32) {
+    const int o = o0 + lane;
+    const uint32_t cv = o < n_obj ? cells[o] : 0u;
+    uint32_t slot = 0, rem = 0;
+    int tokens = 0;
+    if (cv != 0u) {
+      const uint32_t g = cv & 0xFFFFu;
+      slot = ((uint32_t)(kind_base >> (MG_GRID_KIND(g) * 16u)) & 0xFFFFu) + MG_GRID_INDEX(g);
+      const uint2 h = *reinterpret_cast<const uint2*>(ebase + ((size_t)slot << b.rec_shift));
+      rem = h.y > current_step ? h.y - current_step : 0u;  // Assembler::cooldown_remaining, capped for the token
+      rem = rem > 255u ? 255u : rem;
+      tokens = (int)(h.x & 0xFFu) + (rem != 0u ? 1 : 0);
+    }
+    int total;
+    const int offset = warp_exclusive_scan(tokens != 0 ? tokens | 0x10000 : 0, lane, &total);
+    __syncwarp();  // every lane has read its cell before descriptors overwrite the list's neighbourhood
+    if (tokens != 0) {
+      const int pos = pos_base + (offset & 0xFFFF);
+      const uint32_t loc = cv >> 16;
+      uint2 dv;
+      dv.x = slot | ((uint32_t)pos << 16);
+      dv.y = loc | (rem << 8);
+      desc[di_base + (offset >> 16)] = dv;
+      if (pos < T) row[pos * 3] = (uint8_t)loc;
+    }
+    pos_base += total & 0xFFFF;
+    di_base += total >> 16;
+  }
+  __syncwarp();
+
+  // ---- pass 2: one token per lane
+  const int end = pos_base < T ? pos_base : T;
+  const uint32_t cooldown_feature = (uint32_t)cfg[MGC_FEAT_COOLDOWN];
+  int before = 0;  // descriptors that start before this group of 32 tokens
+  for (int t0 = n_global; t0 < end; t0 += 32) {
+    const int t = t0 + lane;
+    uint8_t* out = row + t * 3;
+    const bool live = t < end;
+    const uint32_t starts = __ballot_sync(MG_FULL_MASK, live && out[0] != 0xFFu);
+    if (live) {
+      const uint2 d = desc[before + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1];
+      const int k = t - (int)(d.x >> 16);
+      const uint32_t rem = (d.y >> 8) & 0xFFu;
+      uint32_t tok;
+      if (rem != 0u && k == 0) {
+        tok = cooldown_feature | (rem << 8);
+      } else {
+        const uint8_t* rec = ebase + ((size_t)(d.x & 0xFFFFu) << b.rec_shift) + MG_REC_TOKENS;
+        tok = reinterpret_cast<const uint16_t*>(rec)[k - (rem != 0u ? 1 : 0)];
+      }
+      out[0] = (uint8_t)d.y;
+      out[1] = (uint8_t)tok;
+      out[2] = (uint8_t)(tok >> 8);
+    }
+    before += __popc(starts);
+  }
+  return pos_base;
+}
+
 // Count-only pass used by the reset path (any window size).
 MG_DEVICE inline int obs_count_agent_warp(const MgBatch& b, int env, int ai, int lane, uint32_t current_step) {
   const int cpl = (b.obs_cells + 31) >> 5;

@@ -28,6 +28,7 @@
 // stall); code that reads such a slot later in the same kernel reads it at L2, past any stale L1 line.
 #define MG_RED_ADD(p, v) ((void)atomicAdd((p), (v)))
 #define MG_LDCG(p) __ldcg(p)
+#define MG_NANOSLEEP(ns) __nanosleep(ns)
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif
 

@@ -91,6 +91,16 @@ struct alignas(16) EnvRec {
 };
 static_assert(sizeof(EnvRec) == 64, "EnvRec must be 64 bytes");
 
+// Hand-over of finished envs from the step kernel to the observation kernel running beside it
+// (mg_step_queue_kernel / mg_obs_queue_kernel): an entry is epoch << 32 | env, valid for the launch
+// whose epoch it carries, so nothing has to be cleared between steps.
+struct MgQueueCtl {
+  uint32_t epoch;  // bumped by mg_queue_begin_kernel before every step
+  uint32_t tail;   // entries published so far
+  uint32_t head;   // observation tasks handed out so far
+  uint32_t error;  // set if a consumer gave up waiting (never in a healthy run)
+};
+
 // Everything a kernel needs, passed by value.
 struct MgBatch {
   int32_t num_envs, A, H, W, T, R, S, GS, max_asm, max_chest, num_maps, has_clipper;
@@ -137,6 +147,8 @@ struct MgBatch {
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]
   double* episode_accum;       // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce)
+  MgQueueCtl* qctl;            // queue control block and entries [N] (see above)
+  unsigned long long* queue;
   uint32_t* dbg;               // [N][16] cycle counters of the step kernel's phases (builds with -DMG_TIMING only, else null)
   // caller-owned buffers (set_buffers)
   uint8_t* obs;                // [N*A][T][3]

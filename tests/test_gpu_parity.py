@@ -102,6 +102,23 @@ def test_arena_auto_reset_and_map_rotation(lib):
     ls.close()
 
 
+def test_queue_mode_matches_oracle(lib, monkeypatch):
+    """MG_STEP_MODE=queue: step kernel with one env per CTA handing finished envs to observation CTAs
+    that run beside it. Same results as the default sliced launch."""
+    monkeypatch.setenv("MG_STEP_MODE", "queue")
+    cfg = make_arena(24, max_steps=25)
+    cfg.game.episode_truncates = True
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 40
+    ls = Lockstep(cfg, arena_maps(low, 4, seed=6), num_envs=n, seeds=np.arange(n) + 70, cuda=True)
+    rng = np.random.RandomState(9)
+    for s in range(60):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.compare_state()
+    ls.batch.sync()
+    ls.close()
+
+
 @pytest.mark.skipif(not ref_loader.available(), reason="compiled reference (oracle/_ref) not present")
 def test_arena_vs_compiled_reference(lib):
     cfg = make_arena(24)
