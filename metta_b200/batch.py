@@ -191,8 +191,14 @@ class Batch:
         self._check(self._c.mg_set_early_reset(self._h, s.ctypes.data))
 
     def set_inventory(self, env: int, agent: int, inventory: dict[int, int]) -> None:
+        """MettaGrid::set_inventory (mettagrid_c.cpp:1007-1041). The reference receives the dict as an
+        unordered_map and applies it in that map's iteration order (agent.cpp:68-71), which decides the
+        order of the inventory tokens afterwards; the same order is computed here."""
+        from .lowering import map_order
+
         n = len(inventory)
-        buf = np.asarray(list(inventory.keys()) + list(inventory.values()), dtype=np.int32)
+        pairs = map_order([(int(k), int(v)) for k, v in inventory.items()])
+        buf = np.asarray([p[0] for p in pairs] + [p[1] for p in pairs], dtype=np.int32)
         self._check(self._c.mg_set_inventory(self._h, env, agent, buf.ctypes.data if n else None, n))
 
     def sync(self) -> None:

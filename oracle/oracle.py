@@ -129,8 +129,12 @@ class OracleEnv:
         return out
 
     def set_inventory(self, agent: int, inventory: dict[int, int]) -> None:
-        items = np.asarray(list(inventory.keys()), dtype=np.int32)
-        amounts = np.asarray(list(inventory.values()), dtype=np.int32)
+        # applied in the iteration order of the unordered_map pybind11 builds from the dict (agent.cpp:68-71)
+        from metta_b200.lowering import map_order
+
+        pairs = map_order([(int(k), int(v)) for k, v in inventory.items()])
+        items = np.asarray([p[0] for p in pairs], dtype=np.int32)
+        amounts = np.asarray([p[1] for p in pairs], dtype=np.int32)
         lib().mgo_set_inventory(self._h, agent, items.ctypes.data, amounts.ctypes.data, len(items))
 
     def close(self) -> None:

@@ -1,0 +1,186 @@
+"""Runs the REFERENCE'S OWN Python test-suite with the oracle riding along. TEST INFRASTRUCTURE.
+
+Build container only (needs /root/reference and oracle/_ref). Every `Simulation` the reference's
+tests construct gets an oracle twin built from the same config, map and seed; every `step()` is
+replayed on the twin with the same actions and observations, rewards, terminals, truncations and
+episode rewards are compared byte for byte; `set_inventory` calls are mirrored. A mismatch raises
+inside the reference's test, so it shows up as a failure of that test. Configs the lowering does
+not cover (collectives, activation handlers ...) run without a twin and are counted as such.
+
+    python oracle/reference_suite_lockstep.py            # writes tests/golden/reference_suite_lockstep.txt
+
+The summary file is committed so that the pinning travels with the repo; this script is how it was made.
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+from collections import Counter
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+
+from oracle.ref_loader import load_reference_python  # noqa: E402
+
+load_reference_python()
+
+import pytest  # noqa: E402
+import mettagrid.builder.envs  # noqa: E402,F401  (import order: breaks the config <-> simulator import cycle)
+from mettagrid.simulator import simulator as sim_mod  # noqa: E402
+
+from metta_b200.config import MettaGridConfig  # noqa: E402
+from metta_b200.lowering import lower_game_config  # noqa: E402
+from metta_b200.maps import names_to_codes  # noqa: E402
+from oracle.oracle import OracleEnv  # noqa: E402
+
+STATS = Counter()
+UNCOVERED = Counter()
+PER_TEST = {}
+_current_test = ["?"]
+_last_ctor = {}
+
+_RealCpp = sim_mod.MettaGridCpp
+
+
+def _capturing_ctor(c_cfg, map_grid, seed):
+    _last_ctor["map"], _last_ctor["seed"] = map_grid, seed
+    return _RealCpp(c_cfg, map_grid, seed)
+
+
+sim_mod.MettaGridCpp = _capturing_ctor
+_orig_init = sim_mod.Simulation.__init__
+_orig_step = sim_mod.Simulation.step
+_orig_close = sim_mod.Simulation.close
+
+
+def _twin_init(self, *args, **kwargs):
+    _last_ctor.clear()
+    _orig_init(self, *args, **kwargs)
+    self._oracle_twin = None
+    STATS["simulations"] += 1
+    try:
+        dump = self._config.model_dump()
+        dump["game"]["map_builder"] = None
+        cfg = MettaGridConfig.from_reference(dump)
+        grid = np.asarray(_last_ctor["map"])
+        low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+        twin = OracleEnv(low.words, names_to_codes(low, grid), int(_last_ctor["seed"]))
+    except Exception as exc:  # not lowered: outside the hot path's scope
+        UNCOVERED[f"{type(exc).__name__}: {str(exc)[:90]}"] += 1
+        return
+    c = self._Simulation__c_sim
+    if not np.array_equal(twin.observations, c.observations()):
+        raise AssertionError("oracle twin: initial observations differ from the reference")
+    self._oracle_twin = twin
+    STATS["twinned"] += 1
+    PER_TEST[_current_test[0]] = PER_TEST.get(_current_test[0], 0)
+
+
+def _twin_step(self):
+    twin = getattr(self, "_oracle_twin", None)
+    c = self._Simulation__c_sim
+    actions = np.array(c.actions(), dtype=np.int32).copy() if twin is not None else None
+    _orig_step(self)
+    if twin is None:
+        return
+    twin.step(actions)
+    for name, got, want in (
+        ("observations", twin.observations, c.observations()),
+        ("rewards", twin.rewards, c.rewards()),
+        ("terminals", twin.terminals, c.terminals()),
+        ("truncations", twin.truncations, c.truncations()),
+        ("episode rewards", twin.episode_rewards(), c.get_episode_rewards()),
+        ("action success", np.asarray(twin.action_success(), dtype=bool), np.asarray(c.action_success(), dtype=bool)),
+    ):
+        if not np.array_equal(np.asarray(got), np.asarray(want)):
+            raise AssertionError(f"oracle twin: {name} differ from the reference at step {c.current_step} ({_current_test[0]})")
+    STATS["steps compared"] += 1
+    PER_TEST[_current_test[0]] = PER_TEST.get(_current_test[0], 0) + 1
+
+
+def _twin_close(self):
+    twin = getattr(self, "_oracle_twin", None)
+    if twin is not None:
+        twin.close()
+        self._oracle_twin = None
+    _orig_close(self)
+
+
+def _twin_set_inventory(self, inventory):
+    ids = {self._sim.resource_names.index(name): int(amount) for name, amount in inventory.items()}
+    self._sim._c_sim.set_inventory(self._agent_id, ids)
+    twin = getattr(self._sim, "_oracle_twin", None)
+    if twin is not None:
+        twin.set_inventory(self._agent_id, ids)
+        STATS["set_inventory mirrored"] += 1
+
+
+sim_mod.Simulation.__init__ = _twin_init
+sim_mod.Simulation.step = _twin_step
+sim_mod.Simulation.close = _twin_close
+sim_mod.SimulationAgent.set_inventory = _twin_set_inventory
+
+
+class _Plugin:
+    def __init__(self):
+        self.outcomes = Counter()
+        self.failed = []
+        self.uncollected = []
+
+    def pytest_collectreport(self, report):
+        if report.failed:
+            why = str(report.longrepr).strip().splitlines()[-1] if report.longrepr else ""
+            self.uncollected.append((os.path.basename(str(getattr(report, "fspath", "")) or str(report.nodeid)) or "?", why[:120]))
+
+    def pytest_runtest_setup(self, item):
+        _current_test[0] = f"{item.path.name}::{item.nodeid.split('::', 1)[-1]}"
+
+    def pytest_runtest_logreport(self, report):
+        if report.when == "call" or (report.when == "setup" and report.outcome != "passed"):
+            self.outcomes[report.outcome] += 1
+            if report.outcome == "failed":
+                self.failed.append((f"{os.path.basename(report.location[0])}::{report.nodeid.split('::', 1)[-1]}", str(report.longrepr)[-400:]))
+
+
+def main():
+    tests_dir = "/root/reference/packages/mettagrid/tests"
+    files = sorted(f for f in os.listdir(tests_dir) if f.startswith("test_") and f.endswith(".py"))
+    plugin = _Plugin()
+    with tempfile.TemporaryDirectory() as tmp:
+        args = [os.path.join(tests_dir, f) for f in files] + [
+            "-q", "-x" if "--stop" in sys.argv else "--continue-on-collection-errors", "-p", "no:cacheprovider",
+            "--rootdir", tmp, "-o", "python_files=test_*.py", "--no-header", "-W", "ignore",
+        ]
+        rc = pytest.main(args, plugins=[plugin])
+    covered = {k: v for k, v in PER_TEST.items()}
+    lines = [
+        "Reference test-suite (packages/mettagrid/tests/test_*.py) run with an oracle twin behind every Simulation",
+        "(oracle/reference_suite_lockstep.py, build container, reference core compiled by oracle/build_ref.sh).",
+        "",
+        f"pytest exit code {int(rc)}; test outcomes: " + ", ".join(f"{k} {v}" for k, v in sorted(plugin.outcomes.items())),
+        f"simulations constructed {STATS['simulations']}, with an oracle twin {STATS['twinned']}, "
+        f"steps compared byte for byte {STATS['steps compared']}, set_inventory calls mirrored {STATS['set_inventory mirrored']}",
+        "",
+        "Simulations without a twin (config outside the hot path):",
+    ]
+    lines += [f"  {n} x {k}" for k, n in UNCOVERED.most_common()] or ["  none"]
+    lines += ["", "Failed tests (any 'oracle twin' message is a parity failure; others fail without the twin too):"]
+    lines += [f"  {nid}\n      {msg.strip().splitlines()[-1] if msg.strip() else ''}" for nid, msg in plugin.failed] or ["  none"]
+    lines += ["", "Test files that could not be imported here (third-party packages absent from this image):"]
+    lines += [f"  {n}: {why}" for n, why in plugin.uncollected] or ["  none"]
+    lines += ["", "Reference tests that stepped a twinned simulation (test: steps compared):"]
+    lines += [f"  {k}: {v}" for k, v in sorted(covered.items()) if v > 0]
+    out = os.path.join(ROOT, "tests", "golden", "reference_suite_lockstep.txt")
+    with open(out, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    print("\n".join(lines[:12]))
+    print("written", out)
+
+
+if __name__ == "__main__":
+    main()

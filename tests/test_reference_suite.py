@@ -1,0 +1,45 @@
+"""The reference's own Python test-suite with an oracle twin behind every Simulation
+(oracle/reference_suite_lockstep.py). Runs where /root/reference and oracle/_ref exist (the build
+container); elsewhere the committed summary of the last run is checked instead."""
+
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SUMMARY = os.path.join(ROOT, "tests", "golden", "reference_suite_lockstep.txt")
+
+
+def _check(text: str) -> None:
+    m = re.search(r"simulations constructed (\d+), with an oracle twin (\d+), steps compared byte for byte (\d+)", text)
+    assert m, "summary line missing"
+    built, twinned, steps = (int(x) for x in m.groups())
+    assert twinned >= 450 and twinned >= built - 5 and steps >= 500
+    failed = text.split("Failed tests")[1].split("Test files that could not")[0]
+    assert "none" in failed and "oracle twin:" not in failed, failed
+
+
+def test_committed_summary_reports_no_parity_failure():
+    with open(SUMMARY) as f:
+        _check(f.read())
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/packages/mettagrid/tests"), reason="reference tree not present")
+def test_reference_suite_passes_with_oracle_twins(tmp_path):
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("oracle/_ref not built")
+    keep = open(SUMMARY).read()
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "reference_suite_lockstep.py")], capture_output=True,
+                           text=True, timeout=900)
+        assert "written" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+        with open(SUMMARY) as f:
+            _check(f.read())
+    finally:
+        with open(SUMMARY, "w") as f:  # completion_time-free file, but keep the committed copy byte-stable
+            f.write(keep)
