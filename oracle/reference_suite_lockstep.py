@@ -38,6 +38,41 @@ from metta_b200.lowering import lower_game_config  # noqa: E402
 from metta_b200.maps import names_to_codes  # noqa: E402
 from oracle.oracle import OracleEnv  # noqa: E402
 
+# A second twin: the CUDA kernel sources themselves, compiled for the host on tests/simt_emu and driven
+# through the C-ABI (one env per Simulation). Slower; on by default, KERNEL_TWIN=0 turns it off.
+KERNEL_TWIN = os.environ.get("KERNEL_TWIN", "1") != "0"
+if KERNEL_TWIN:
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from emu_build import load_emu  # noqa: E402
+    from harness import HostBuffers  # noqa: E402
+
+    from metta_b200.batch import Batch  # noqa: E402
+    from metta_b200.maps import build_pool  # noqa: E402
+
+    _EMU = load_emu()
+
+
+class _KernelTwin:
+    def __init__(self, low, codes, seed):
+        self.A = int(low.num_agents)
+        self.batch = Batch(low, build_pool(low, codes[None]), 1, clib=_EMU)
+        self.batch.set_options(auto_reset=False, map_stride=0)
+        self.buf = HostBuffers(self.A, int(low.words[L_OBS_TOKENS]), cuda=False)
+        self.batch.set_buffers(*self.buf.ptrs)
+        self.batch.reset(np.array([seed], np.uint32), np.array([0], np.int32))
+
+    def step(self, actions):
+        self.buf.set_actions(actions)
+        self.batch.step()
+
+    def close(self):
+        self.batch.close()
+
+
+from metta_b200.layout import L as _L  # noqa: E402
+
+L_OBS_TOKENS = _L.MGC_NUM_TOKENS
+
 STATS = Counter()
 UNCOVERED = Counter()
 PER_TEST = {}
@@ -77,6 +112,13 @@ def _twin_init(self, *args, **kwargs):
     if not np.array_equal(twin.observations, c.observations()):
         raise AssertionError("oracle twin: initial observations differ from the reference")
     self._oracle_twin = twin
+    self._kernel_twin = None
+    if KERNEL_TWIN:
+        kt = _KernelTwin(low, names_to_codes(low, grid), int(_last_ctor["seed"]))
+        if not np.array_equal(kt.buf.obs, c.observations()):
+            raise AssertionError("kernel twin: initial observations differ from the reference")
+        self._kernel_twin = kt
+        STATS["kernel twins"] += 1
     STATS["twinned"] += 1
     PER_TEST[_current_test[0]] = PER_TEST.get(_current_test[0], 0)
 
@@ -101,6 +143,20 @@ def _twin_step(self):
             raise AssertionError(f"oracle twin: {name} differ from the reference at step {c.current_step} ({_current_test[0]})")
     STATS["steps compared"] += 1
     PER_TEST[_current_test[0]] = PER_TEST.get(_current_test[0], 0) + 1
+    kt = getattr(self, "_kernel_twin", None)
+    if kt is not None:
+        kt.step(actions)
+        for name, got, want in (
+            ("observations", kt.buf.obs, c.observations()),
+            ("rewards", kt.buf.rew, c.rewards()),
+            ("terminals", kt.buf.term.astype(bool), c.terminals()),
+            ("truncations", kt.buf.trunc.astype(bool), c.truncations()),
+            ("episode rewards", kt.batch.read_episode_rewards()[0], c.get_episode_rewards()),
+            ("action success", kt.batch.read_action_success()[0], np.asarray(c.action_success(), dtype=bool)),
+        ):
+            if not np.array_equal(np.asarray(got), np.asarray(want)):
+                raise AssertionError(f"kernel twin: {name} differ from the reference at step {c.current_step} ({_current_test[0]})")
+        STATS["kernel steps compared"] += 1
 
 
 def _twin_close(self):
@@ -108,6 +164,10 @@ def _twin_close(self):
     if twin is not None:
         twin.close()
         self._oracle_twin = None
+    kt = getattr(self, "_kernel_twin", None)
+    if kt is not None:
+        kt.close()
+        self._kernel_twin = None
     _orig_close(self)
 
 
@@ -118,6 +178,9 @@ def _twin_set_inventory(self, inventory):
     if twin is not None:
         twin.set_inventory(self._agent_id, ids)
         STATS["set_inventory mirrored"] += 1
+    kt = getattr(self._sim, "_kernel_twin", None)
+    if kt is not None:
+        kt.batch.set_inventory(0, self._agent_id, ids)
 
 
 sim_mod.Simulation.__init__ = _twin_init
@@ -165,6 +228,8 @@ def main():
         f"pytest exit code {int(rc)}; test outcomes: " + ", ".join(f"{k} {v}" for k, v in sorted(plugin.outcomes.items())),
         f"simulations constructed {STATS['simulations']}, with an oracle twin {STATS['twinned']}, "
         f"steps compared byte for byte {STATS['steps compared']}, set_inventory calls mirrored {STATS['set_inventory mirrored']}",
+        f"kernel twins (the CUDA sources on tests/simt_emu, through the C-ABI) {STATS['kernel twins']}, "
+        f"steps compared byte for byte {STATS['kernel steps compared']}",
         "",
         "Simulations without a twin (config outside the hot path):",
     ]

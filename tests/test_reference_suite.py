@@ -18,8 +18,10 @@ def _check(text: str) -> None:
     assert m, "summary line missing"
     built, twinned, steps = (int(x) for x in m.groups())
     assert twinned >= 450 and twinned >= built - 5 and steps >= 500
+    k = re.search(r"kernel twins .* (\d+), steps compared byte for byte (\d+)", text)
+    assert k and int(k.group(1)) == twinned and int(k.group(2)) == steps, "the kernel sources (emulated) must have ridden along on every twinned step"
     failed = text.split("Failed tests")[1].split("Test files that could not")[0]
-    assert "none" in failed and "oracle twin:" not in failed, failed
+    assert "none" in failed and "oracle twin:" not in failed and "kernel twin:" not in failed, failed
 
 
 def test_committed_summary_reports_no_parity_failure():
