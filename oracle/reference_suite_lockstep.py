@@ -212,6 +212,8 @@ class _Plugin:
 
 def main():
     tests_dir = "/root/reference/packages/mettagrid/tests"
+    if "--cogames" in sys.argv:  # exploratory: the cogames package's tests (not part of the committed summary)
+        tests_dir = "/root/reference/packages/cogames/tests"
     files = sorted(f for f in os.listdir(tests_dir) if f.startswith("test_") and f.endswith(".py"))
     plugin = _Plugin()
     with tempfile.TemporaryDirectory() as tmp:
@@ -241,6 +243,8 @@ def main():
     lines += ["", "Reference tests that stepped a twinned simulation (test: steps compared):"]
     lines += [f"  {k}: {v}" for k, v in sorted(covered.items()) if v > 0]
     out = os.path.join(ROOT, "tests", "golden", "reference_suite_lockstep.txt")
+    if "--cogames" in sys.argv:
+        out = "/tmp/reference_suite_lockstep_cogames.txt"
     with open(out, "w") as f:
         f.write("\n".join(lines) + "\n")
     print("\n".join(lines[:12]))

@@ -220,10 +220,14 @@ def test_host_buffer_step_matches_oracle(pinned, changed_only, lib):
     b.close()
 
 
-def test_changed_rows_export_follows_resets(lib):
+@pytest.mark.parametrize("chunks", ["1", "3"])
+def test_changed_rows_export_follows_resets(chunks, lib, monkeypatch):
     """Export mode 1 across episode ends (token counts drop back at a reset), a second buffer and a
-    mode switch: the page-locked host buffer always equals the device observations."""
+    mode switch: the page-locked host buffer always equals the device observations. With MG_CHUNKS=3
+    the export kernels run inside the captured step graph, one per slice of envs."""
     import torch
+
+    monkeypatch.setenv("MG_CHUNKS", chunks)
 
     cfg, grid = SCENARIOS["tiny_truncating"]()
     low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
