@@ -500,7 +500,8 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
     const int distributed = shared_update(e, outputs, item, MG_OUT_AMOUNT(i));
     if (distributed > 0) {
       // integer-valued float counter: the sum does not depend on the order of the additions
-      MG_RED_ADD(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
+      if (e.concurrent) atomicAdd(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);  // several lanes may create the same item
+      else MG_RED_ADD(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
     }
   }
 #undef MG_IN_AMOUNT
@@ -766,7 +767,7 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
       const float* sp = agent_stat(e, ai, rw[MG_RWD_AGENT_STAT]);
       v = rw[MG_RWD_AGENT_STAT] < MG_HOT_STATS && e.hot != nullptr ? *sp : MG_LDCG(sp);
     }
-    v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LDCG(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
+    v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LD_L2(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));
     if (rw[MG_RWD_HAS_MAX]) {
       float cap = MG_INT_AS_FLOAT(rw[MG_RWD_MAX]);

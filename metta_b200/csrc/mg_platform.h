@@ -24,10 +24,21 @@
 #define MG_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
 #define MG_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #define MG_LDG(p) __ldg(p)
-// Counters in HBM that nobody needs back within the step are bumped with a reduction (no load, no
-// stall); code that reads such a slot later in the same kernel reads it at L2, past any stale L1 line.
+// Stat counters in HBM. Measured both ways on B200 (arena, 4096 envs): bumping them with reductions
+// (no load, no stall) and reading the few the rewards need at L2 (__ldcg, past any stale L1 line) is
+// SLOWER than plain read-modify-write on lines the load phase prefetched into L1 (step kernel 123.5 us
+// vs 119 us): the reward reads are on the critical path, the bumps are not. -DMG_STAT_RED selects the
+// reduction variant.
+#ifdef MG_STAT_RED
 #define MG_RED_ADD(p, v) ((void)atomicAdd((p), (v)))
 #define MG_LDCG(p) __ldcg(p)
+#else
+#define MG_RED_ADD(p, v) ((void)(*(p) += (v)))
+#define MG_LDCG(p) (*(p))
+#undef MG_PREFETCH_L2
+#define MG_PREFETCH_L2(p) MG_PREFETCH_L1(p)
+#endif
+#define MG_LD_L2(p) __ldcg(p) /* read at L2: for words other lanes may have bumped with atomics */
 #define MG_NANOSLEEP(ns) __nanosleep(ns)
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif

@@ -31,6 +31,7 @@
 #define MG_PREFETCH_L2(p) ((void)(p))
 #define MG_RED_ADD(p, v) ((void)(*(p) += (v)))
 #define MG_LDCG(p) (*(p))
+#define MG_LD_L2(p) (*(p))
 #define MG_NANOSLEEP(ns) ((void)0)
 #define MG_LDG(p) (*(p))
 #define MG_GRID_CONSTANT
