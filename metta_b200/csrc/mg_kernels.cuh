@@ -46,6 +46,7 @@ struct StepSmem {
   uint8_t order[MAXA];
   int32_t scratch[2 * MG_RES_STRIDE + 8];
   uint32_t rngbuf[32];
+  uint32_t rng_base, rng_n;  // rngbuf holds state words [rng_base, rng_base + rng_n) of the env's generator
   uint32_t intent[MAXA];  // per agent: bit 0 = act in the parallel pass, bits 8..15 action kind, 16..31 argument
   uint32_t ordered_mask;
   long long tick_last;
@@ -514,6 +515,11 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       tc_v[k] = ai < A ? *reinterpret_cast<const uint32_t*>(tc + ai * 2) : 0xFFFF0000u;
     }
     float gs3 = lane < 3 ? gs[MG_GS_TOKENS_WRITTEN + lane] : 0.0f;
+    // the generator words the shuffle will draw from: one more load in this batch instead of an HBM
+    // round trip of its own in the next phase
+    const uint32_t rng_first = er.rng_idx;
+    const uint32_t rng_n = rng_first < MT_N ? (MT_N - rng_first < 32u ? MT_N - rng_first : 32u) : 0u;
+    const uint32_t rng_w = (uint32_t)lane < rng_n ? b.rng[(size_t)env * MT_N + rng_first + lane] : 0u;
 
     // fold the pending token counts (written | attempted << 16; attempted 0xFFFF = nothing pending)
     {
@@ -575,6 +581,8 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
         sm.success[ai] = 0;
       }
     }
+    sm.rngbuf[lane] = rng_w;
+    if (lane == 0) { sm.rng_base = rng_first; sm.rng_n = rng_n; }
     break;
   }
   __syncwarp();
@@ -650,7 +658,11 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
   MG_SM_TICK(sm, 3);
   // random processing order (mettagrid_c.cpp:591-593); the words it needs are fetched in one go
   MtStream rs = mt_stream(mt, sm.er.rng_idx);
-  mt_prefetch_warp(rs, sm.rngbuf, lane);
+  if (sm.rng_n != 0u && sm.rng_base == rs.idx) {  // staged by the load phase
+    rs.buf = sm.rngbuf; rs.buf_base = sm.rng_base; rs.buf_n = sm.rng_n;
+  } else {
+    mt_prefetch_warp(rs, sm.rngbuf, lane);
+  }
   // the draws are always taken; the swaps are only applied if somebody needs the order (below)
   uint32_t* draws = reinterpret_cast<uint32_t*>(sm.scratch);
   const bool fast_shuffle = std_shuffle_draws_warp(rs, lane, A, draws);
