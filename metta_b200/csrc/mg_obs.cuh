@@ -6,11 +6,12 @@
 // (systems/observation_encoder.hpp:107-117), counting the overflow.
 //
 // Here nothing is rebuilt per observer: every object, static or not, has a token record
-// (mg_tokens.cuh) and every agent a record of its global tokens. Each lane owns a run of the
-// Manhattan-ordered cells: it reads the 8-byte header of its cells' records (token count,
-// cooldown end), a warp prefix sum turns counts into token offsets, and then the warp emits the
-// row one token per lane (2 bytes fetched from the object's record, behind the location byte) into
-// a shared-memory image of the agent's row, which is then stored to HBM with 16-byte stores.
+// (mg_tokens.cuh) and every agent a record of its global tokens. Each lane gathers a run of the
+// Manhattan-ordered window cells; the warp compacts the non-empty ones (most of a window is empty),
+// reads one record header per lane (token count, cooldown end), turns the counts into token offsets
+// with a prefix sum, and then emits the row one token per lane (2 bytes fetched from the object's
+// record, behind the location byte) into a shared-memory image of the agent's row, which is stored
+// to HBM with 16-byte stores.
 #ifndef MG_OBS_CUH_
 #define MG_OBS_CUH_
 
@@ -39,110 +40,40 @@ MG_DEVICE inline uint64_t load_pattern_run(const uint8_t* pattern, int lane) {
 // Bytes of shared memory one warp needs besides its row image: one 8-byte descriptor per window cell.
 #define MG_OBS_DESC_BYTES(cpl) ((cpl) * 32 * 8)
 
-// Encodes agent `ai` of env `env` into `row` (shared-memory image of its T*3 bytes, pre-filled with
-// 0xFF) when EMIT, or only counts tokens. Must be called by all 32 lanes. CPL = window cells per
-// lane (CPL * 32 >= obs_h * obs_w). `desc` is shared memory for CPL*32 descriptors (EMIT only).
-// Returns the number of tokens attempted.
-//
-// Emission is token-parallel. Pass 1 (cell-parallel) leaves, for every cell that has tokens, a
-// descriptor {record slot, first token index, location, cooldown_remaining} in window order and puts
-// the cell's location byte where its first token will go. Pass 2 walks the row 32 tokens at a time:
-// a token slot whose first byte is no longer 0xFF starts a new cell, so a ballot and two popcounts
-// tell every lane which descriptor its token belongs to, and the lane fetches that one token.
-template <int CPL, bool EMIT>
-MG_DEVICE inline int obs_encode_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step) {
+// Token count of agent `ai`'s observation (what the encoder below would attempt to write), without
+// writing anything: the reset path counts the observation passes the reference makes in its
+// constructor (tokens_written / dropped / free_space stats). Must be called by all 32 lanes; CPL =
+// window cells per lane (CPL * 32 >= obs_h * obs_w).
+template <int CPL>
+MG_DEVICE inline int obs_count_cells_warp(const MgBatch& b, int env, int ai, int lane, uint32_t current_step) {
   const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
   const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
   const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
-  const int T = b.T;
-
-  // ---- global tokens: prepared by the action kernel, copied byte by byte
-  const uint8_t* gt = b.gtok + ((size_t)env * b.A + ai) * MG_GTOK_STRIDE;
-  const int n_global = gt[0];
-  if (EMIT) {
-    const int nb = (n_global < T ? n_global : T) * 3;  // <= 63 bytes (MG_GTOK_STRIDE)
-    if (lane < nb) row[lane] = gt[1 + lane];
-    if (lane + 32 < nb) row[lane + 32] = gt[33 + lane];
-  }
-
-  // ---- pass 1: my cells' records and token counts
+  const int n_global = b.gtok[((size_t)env * b.A + ai) * MG_GTOK_STRIDE];
   const uint8_t* ebase = b.etok + (((size_t)env * b.rec_slots) << b.rec_shift);
   const uint64_t kind_base = (uint64_t)b.rec_kind_base_lo | ((uint64_t)b.rec_kind_base_hi << 32);
   const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);
-  uint32_t slot[CPL];
-  uint32_t cnt[CPL];  // tokens | cooldown_remaining << 8
-  int mine = 0;       // tokens | cells with tokens << 16
+  int mine = 0;
 #pragma unroll
   for (int j = 0; j < CPL; j++) {
     const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
+    const int r = my_r + (int)(loc >> 4) - hr, c = my_c + (int)(loc & 0xF) - wr;
     uint32_t g = 0;
-    {
-      const int r = my_r + (int)(loc >> 4) - hr, c = my_c + (int)(loc & 0xF) - wr;
-      if (loc != 0xFFu && (unsigned)r < (unsigned)b.H && (unsigned)c < (unsigned)b.W) g = grid[r * b.W + c];
-    }
-    uint32_t n = 0;
-    slot[j] = 0;
+    if (loc != 0xFFu && (unsigned)r < (unsigned)b.H && (unsigned)c < (unsigned)b.W) g = grid[r * b.W + c];
     if (g != 0) {
-      slot[j] = ((uint32_t)(kind_base >> (MG_GRID_KIND(g) * 16u)) & 0xFFFFu) + MG_GRID_INDEX(g);
-      const uint2 h = *reinterpret_cast<const uint2*>(ebase + ((size_t)slot[j] << b.rec_shift));
-      uint32_t rem = h.y > current_step ? h.y - current_step : 0u;  // Assembler::cooldown_remaining, capped for the token
-      rem = rem > 255u ? 255u : rem;
-      n = (h.x & 0xFFu) | (rem << 8);
-      const int tokens = (int)(h.x & 0xFFu) + (rem != 0u ? 1 : 0);
-      mine += tokens != 0 ? tokens | 0x10000 : 0;
+      const uint32_t slot = ((uint32_t)(kind_base >> (MG_GRID_KIND(g) * 16u)) & 0xFFFFu) + MG_GRID_INDEX(g);
+      const uint2 h = *reinterpret_cast<const uint2*>(ebase + ((size_t)slot << b.rec_shift));
+      mine += (int)(h.x & 0xFFu) + (h.y > current_step ? 1 : 0);  // + the cooldown_remaining token while it is > 0
     }
-    cnt[j] = n;
   }
   int total;
-  const int offset = warp_exclusive_scan(mine, lane, &total);
-  if (EMIT) {
-    int pos = n_global + (offset & 0xFFFF), di = offset >> 16;
-#pragma unroll
-    for (int j = 0; j < CPL; j++) {
-      if (cnt[j] == 0) continue;
-      const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
-      uint2 dv;
-      dv.x = slot[j] | ((uint32_t)pos << 16);
-      dv.y = loc | (cnt[j] & 0xFF00u);
-      desc[di++] = dv;
-      if (pos < T) row[pos * 3] = (uint8_t)loc;
-      pos += (int)(cnt[j] & 0xFFu) + (cnt[j] > 0xFFu ? 1 : 0);
-    }
-    __syncwarp();
-    // ---- pass 2: one token per lane
-    const int end = n_global + (total & 0xFFFF) < T ? n_global + (total & 0xFFFF) : T;
-    const uint32_t cooldown_feature = (uint32_t)cfg[MGC_FEAT_COOLDOWN];
-    int before = 0;  // descriptors that start before this group of 32 tokens
-    for (int t0 = n_global; t0 < end; t0 += 32) {
-      const int t = t0 + lane;
-      uint8_t* out = row + t * 3;
-      const bool live = t < end;
-      const uint32_t starts = __ballot_sync(MG_FULL_MASK, live && out[0] != 0xFFu);
-      if (live) {
-        const uint2 d = desc[before + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1];
-        const int k = t - (int)(d.x >> 16);
-        const uint32_t rem = (d.y >> 8) & 0xFFu;
-        uint32_t tok;
-        if (rem != 0u && k == 0) {
-          tok = cooldown_feature | (rem << 8);
-        } else {
-          const uint8_t* rec = ebase + ((size_t)(d.x & 0xFFFFu) << b.rec_shift) + MG_REC_TOKENS;
-          tok = reinterpret_cast<const uint16_t*>(rec)[k - (rem != 0u ? 1 : 0)];
-        }
-        out[0] = (uint8_t)d.y;
-        out[1] = (uint8_t)tok;
-        out[2] = (uint8_t)(tok >> 8);
-      }
-      before += __popc(starts);
-    }
-  }
-  return n_global + (total & 0xFFFF);
+  warp_exclusive_scan(mine, lane, &total);
+  return n_global + total;
 }
 
-// The emitting encoder the observation kernels use. Same result as obs_encode_agent_warp<CPL, true>,
-// arranged for fewer issued instructions: most window cells are empty, so after the grid gather the
+// The encoder the observation kernels use, arranged for few issued instructions: most window cells are empty, so after the grid gather the
 // warp compacts its non-empty cells (ballots + popcounts, window order kept) into shared memory and
 // then looks at one OBJECT per lane (record header, cooldown, token count, prefix sum, descriptor)
 // instead of CPL cells per lane. The cell list shares `desc`'s second half: an entry is read before the
@@ -257,8 +188,8 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
 // Count-only pass used by the reset path (any window size).
 MG_DEVICE inline int obs_count_agent_warp(const MgBatch& b, int env, int ai, int lane, uint32_t current_step) {
   const int cpl = (b.obs_cells + 31) >> 5;
-  if (cpl <= 4) return obs_encode_agent_warp<4, false>(b, env, ai, lane, nullptr, nullptr, current_step);
-  return obs_encode_agent_warp<8, false>(b, env, ai, lane, nullptr, nullptr, current_step);
+  if (cpl <= 4) return obs_count_cells_warp<4>(b, env, ai, lane, current_step);
+  return obs_count_cells_warp<8>(b, env, ai, lane, current_step);
 }
 
 #endif  // MG_OBS_CUH_
