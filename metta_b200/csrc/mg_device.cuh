@@ -763,9 +763,14 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
   for (int i = 0; i < n; i++) {
     const int32_t* rw = grp + MG_GRP_REWARDS + i * MG_RWD_WORDS;
     float v = 0.0f;
-    if (rw[MG_RWD_AGENT_STAT] >= 0) {
-      const float* sp = agent_stat(e, ai, rw[MG_RWD_AGENT_STAT]);
-      v = rw[MG_RWD_AGENT_STAT] < MG_HOT_STATS && e.hot != nullptr ? *sp : MG_LDCG(sp);
+    const int as = rw[MG_RWD_AGENT_STAT];
+    if (as >= MG_AS_AMOUNT && as < MG_AS_AMOUNT + MG_MAX_RESOURCES) {
+      // "<resource>.amount" is by construction the agent's current amount (on_inventory_change writes
+      // it at every change, the initial inventory included): read it from the record, not from HBM
+      v = (float)a->amt[as - MG_AS_AMOUNT];
+    } else if (as >= 0) {
+      const float* sp = agent_stat(e, ai, as);
+      v = as < MG_HOT_STATS && e.hot != nullptr ? *sp : MG_LDCG(sp);
     }
     v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LD_L2(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));

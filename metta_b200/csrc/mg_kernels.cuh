@@ -593,7 +593,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     const float* st = b.agent_stats + (abase + ai) * b.S;
     for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
       const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
-      if (slot >= MG_HOT_STATS) MG_PREFETCH_L2(st + slot);
+      if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) MG_PREFETCH_L2(st + slot);
     }
   }
   if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L2(b.game_stats + (size_t)env * b.GS + lane * 32);
