@@ -202,6 +202,27 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   b.cfg = d_cfg;
   b.cfg_words = (int32_t)cfg_ext.size();
   b.inv_masks_off = (int32_t)n_words;
+  {
+    const int32_t* res = cfg + cfg[MGC_OFF_ACTION_RES];
+    for (int k = 0; k < 3; k++) {
+      b.req_mask[k] = b.con_mask[k] = 0u;
+      for (int i = 0; i < MG_MAX_RESOURCES; i++) {
+        if ((res[k * MG_ACTRES_WORDS + MG_ACTRES_REQUIRED + i] & 0xFFFF) != 0) b.req_mask[k] |= 1u << i;
+        if ((res[k * MG_ACTRES_WORDS + MG_ACTRES_CONSUMED + i] & 0xFFFF) != 0) b.con_mask[k] |= 1u << i;
+      }
+    }
+    b.any_damage = b.reward_stat_prefetch = b.reward_game_stats = 0;
+    for (int g = 0; g < cfg[MGC_NUM_GROUPS]; g++) {
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + (size_t)g * MG_GRP_WORDS;
+      if (grp[MG_GRP_DAMAGE_ENABLED] != 0) b.any_damage = 1;
+      for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
+        const int32_t* rw = grp + MG_GRP_REWARDS + i * MG_RWD_WORDS;
+        const int slot = rw[MG_RWD_AGENT_STAT];
+        if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) b.reward_stat_prefetch = 1;
+        if (rw[MG_RWD_GAME_STAT] >= 0) b.reward_game_stats = 1;
+      }
+    }
+  }
   std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
   pat.resize(((pat.size() + 255) / 256 + 1) * 256, 0xFF);  // padded: lanes read whole runs of cells
   TRY(dev_alloc(e, &d_pat, pat.size()));

@@ -587,38 +587,29 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
   }
   __syncwarp();
   MG_SM_TICK(sm, 1);
-  // the stat slots the rewards will read at the end of the step (at L2, see MG_LDCG): start pulling them in now
-  for (int ai = lane; ai < A; ai += 32) {
-    const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
-    const float* st = b.agent_stats + (abase + ai) * b.S;
-    for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
-      const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
-      if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) MG_PREFETCH_L2(st + slot);
+  // the stat slots the rewards will read at the end of the step: start pulling them in now (configs whose
+  // rewards only look at hot counters and <res>.amount, like the arena, have none)
+  if (b.reward_stat_prefetch) {
+    for (int ai = lane; ai < A; ai += 32) {
+      const int32_t* grp = cfg + cfg[MGC_OFF_GROUPS] + sm.ag[ai].group * MG_GRP_WORDS;
+      const float* st = b.agent_stats + (abase + ai) * b.S;
+      for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
+        const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
+        if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) MG_PREFETCH_L2(st + slot);
+      }
     }
   }
-  if (lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L2(b.game_stats + (size_t)env * b.GS + lane * 32);
+  if (b.reward_game_stats && lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L2(b.game_stats + (size_t)env * b.GS + lane * 32);
   er.current_step += 1;
-  if (lane == 0) sm.er = er;
-  EnvCtx& e = sm.ctx;
-  {
-    // which resources each action kind requires / consumes: most configs name none or one, so the
-    // per-action checks iterate set bits instead of all resources
-    const int32_t* res = cfg + cfg[MGC_OFF_ACTION_RES];
-    uint32_t rqm[3], cnm[3];
-    for (int k = 0; k < 3; k++) {
-      const bool rq = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_REQUIRED + lane] & 0xFFFF) != 0;
-      const bool cn = lane < MG_MAX_RESOURCES && (res[k * MG_ACTRES_WORDS + MG_ACTRES_CONSUMED + lane] & 0xFFFF) != 0;
-      rqm[k] = __ballot_sync(MG_FULL_MASK, rq);
-      cnm[k] = __ballot_sync(MG_FULL_MASK, cn);
-    }
-    if (lane == 0) {
-      e = make_ctx(b, env, sm.ag, er);
-      e.hot = sm.hot;
-      e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
-      for (int k = 0; k < 3; k++) { e.req_mask[k] = rqm[k]; e.con_mask[k] = cnm[k]; }
-    }
-    __syncwarp();
+  if (lane == 0) {
+    sm.er = er;
+    EnvCtx& e = sm.ctx;
+    e = make_ctx(b, env, sm.ag, er);
+    e.hot = sm.hot;
+    e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
+    for (int k = 0; k < 3; k++) { e.req_mask[k] = b.req_mask[k]; e.con_mask[k] = b.con_mask[k]; }
   }
+  __syncwarp();
 }
 
 // Phase 2: processing order, every agent's intent, and who may act independently of the order.
@@ -801,10 +792,7 @@ MG_DEVICE MG_NOINLINE void step_phase_post(const MgBatch& b, StepSmem<MAXA>& sm,
   }
 
   // damage (agent.cpp:134-177): agent order, draws from the env rng
-  bool any_damage = false;
-  for (int gidx = 0; gidx < cfg[MGC_NUM_GROUPS]; gidx++)
-    any_damage = any_damage || cfg[cfg[MGC_OFF_GROUPS] + gidx * MG_GRP_WORDS + MG_GRP_DAMAGE_ENABLED] != 0;
-  if (any_damage) damage_pass_warp(b, e, sm.scratch, rs, lane);
+  if (b.any_damage) damage_pass_warp(b, e, sm.scratch, rs, lane);
   // clipper (clipper.hpp:203-238): draws from its private rng copy
   if (b.has_clipper) {
     uint32_t cidx = er.clip_rng_idx;

@@ -109,6 +109,11 @@ struct MgBatch {
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
   int32_t cfg_words;           // length of cfg in int32 words, including what mg_create appends to the blob
+  // derived from the config once, on the host (mg_create):
+  uint32_t req_mask[3], con_mask[3];  // per action kind: resources it requires / consumes (bit per item)
+  int32_t any_damage;          // some agent group has damage enabled
+  int32_t reward_stat_prefetch;  // some reward term reads a stat slot that lives in HBM (not a hot slot, not <res>.amount)
+  int32_t reward_game_stats;   // some reward term reads a game stat
   int32_t inv_masks_off;       // appended: per INVCFG record [MG_MAX_LIMITS] member masks, [MG_MAX_LIMITS] modifier masks
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
