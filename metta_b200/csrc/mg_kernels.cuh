@@ -759,11 +759,21 @@ MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, 
     __syncwarp();
   }
   MG_SM_TICK(sm, 6);
-  // the ordered action pass: later agents see what earlier agents did
+  // the ordered action pass: later agents see what earlier agents did. The agents that need it are
+  // first pulled out of the shuffled order (one ballot), so that the serial loop only visits them.
+  int n_ordered = A;
+  if (A <= 32 && ordered_mask != 0u) {
+    const int ai = lane < A ? (int)sm.order[lane] : 0;
+    const bool mine = lane < A && ((ordered_mask >> ai) & 1u) != 0u;
+    const uint32_t picks = __ballot_sync(MG_FULL_MASK, mine);
+    __syncwarp();
+    if (mine) sm.order[__popc(picks & ((1u << lane) - 1u))] = (uint8_t)ai;  // slot <= lane: never ahead of an unread entry
+    n_ordered = __popc(picks);
+    __syncwarp();
+  }
   if (lane == 0 && ordered_mask != 0u) {
-    for (int k = 0; k < A; k++) {
+    for (int k = 0; k < n_ordered; k++) {
       const int ai = sm.order[k];
-      if (A <= 32 && !((ordered_mask >> ai) & 1u)) continue;
       const int a = sm.action[ai];
       if (a < 0 || a >= nact) continue;
       const bool ok = handle_action(e, ai, acts[a * MG_ACT_WORDS + MG_ACT_KIND], acts[a * MG_ACT_WORDS + MG_ACT_ARG]);
@@ -889,22 +899,22 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   unsigned char* cfg_smem = dyn_smem + sizeof(StepSmem<MAXA>) * MG_STEP_WARPS;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  // The rules consult the lowered config constantly (dependent lookups: section offset -> record ->
-  // field). From global memory those loads miss L1 most of the time here (the per-env state streams
-  // through it), so each CTA first copies the config next to its envs; every lookup is then a
-  // shared-memory access. Configs too large for the launch's dynamic shared memory stay in HBM/L2.
-  const bool cfg_fits = cfg_bytes_in_smem >= b_param.cfg_words * 4;
+  // Optionally (cfg_bytes_in_smem, off by default: measured slower on B200) each CTA first copies the
+  // lowered config next to its envs, so that the rules' dependent lookups (section offset -> record ->
+  // field) are shared-memory accesses; otherwise they go to HBM through L1 and the launch parameters are
+  // used where they are (the constant bank).
+  const bool cfg_fits = cfg_bytes_in_smem > 0 && cfg_bytes_in_smem >= b_param.cfg_words * 4;
   if (cfg_fits) {
     const uint4* src = reinterpret_cast<const uint4*>(b_param.cfg);
     uint4* dst = reinterpret_cast<uint4*>(cfg_smem);
     for (int i = threadIdx.x; i < (b_param.cfg_words + 3) / 4; i += blockDim.x) dst[i] = src[i];
+    if (threadIdx.x == 0) {
+      batch_s = b_param;
+      batch_s.cfg = reinterpret_cast<const int32_t*>(cfg_smem);
+    }
+    __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    batch_s = b_param;
-    if (cfg_fits) batch_s.cfg = reinterpret_cast<const int32_t*>(cfg_smem);
-  }
-  __syncthreads();
-  const MgBatch& b = batch_s;
+  const MgBatch& b = cfg_fits ? batch_s : b_param;
   const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
   if (env >= b.env_end) return;
   step_env_warp<MAXA>(b, smem[warp], env, lane);
