@@ -857,13 +857,21 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
   __syncwarp();
   MG_SM_TICK(sm, 9);
   {
+    // records and hot stat slots back to HBM, 16 bytes per lane and round (4 chunks per agent each)
+    static_assert(MG_HOT_STATS == 16, "four 16-byte chunks of hot stats per agent, like the record");
+    constexpr int NV = MAXA * 4 / 32;
     uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
     const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
-    for (int i = lane; i < A * 4; i += 32) dst[i] = src[i];
-    float* gst = b.agent_stats + (size_t)env * A * b.S;
-    for (int i = lane; i < A * (MG_HOT_STATS / 4); i += 32) {
-      const int ai = i / (MG_HOT_STATS / 4), q = i % (MG_HOT_STATS / 4);
-      *reinterpret_cast<uint4*>(gst + (size_t)ai * b.S + q * 4) = reinterpret_cast<const uint4*>(sm.hot)[i];
+    const uint4* hot = reinterpret_cast<const uint4*>(sm.hot);
+    float* gst = b.agent_stats + (size_t)env * A * b.S + (size_t)(lane >> 2) * b.S + (lane & 3) * 4;  // agent lane/4, chunk lane%4
+    const size_t round_stride = (size_t)8 * b.S;  // 32 lanes = 8 agents further
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      const int i = lane + 32 * k;
+      if (i < A * 4) {
+        dst[i] = src[i];
+        *reinterpret_cast<uint4*>(gst + k * round_stride) = hot[i];
+      }
     }
   }
   if (lane == 0) b.env[env] = er;
