@@ -57,8 +57,8 @@ struct StepSmem {
   EnvCtx ctx;  // warp-uniform; lives here so that passing it to out-of-line functions costs no stack traffic
 };
 
-MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
-  EnvCtx e;
+// Fills `e` where it lives (the step kernel keeps it in shared memory: no copy through registers).
+MG_DEVICE inline void init_ctx(EnvCtx& e, const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
   e.cfg = b.cfg;
   e.env = env;
   e.H = b.H; e.W = b.W; e.A = b.A; e.R = b.R; e.S = b.S;
@@ -78,6 +78,11 @@ MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const 
   e.n_asm = er.n_asm;
   e.clip_enabled = b.has_clipper;
   e.clip_length_scale = er.clip_length_scale;
+}
+
+MG_DEVICE inline EnvCtx make_ctx(const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
+  EnvCtx e;
+  init_ctx(e, b, env, ag, er);
   return e;
 }
 
@@ -604,7 +609,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
   if (lane == 0) {
     sm.er = er;
     EnvCtx& e = sm.ctx;
-    e = make_ctx(b, env, sm.ag, er);
+    init_ctx(e, b, env, sm.ag, er);
     e.hot = sm.hot;
     e.asm_records_on_use = cfg[MGC_HAS_VIBE_ASM] == 0;
     for (int k = 0; k < 3; k++) { e.req_mask[k] = b.req_mask[k]; e.con_mask[k] = b.con_mask[k]; }
