@@ -105,9 +105,9 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
 #pragma unroll
   for (int j = 0; j < CPL; j++) {
     const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
-    const int r = my_r + (int)(loc >> 4) - hr, c = my_c + (int)(loc & 0xF) - wr;
+    const uint32_t r = (uint32_t)(my_r - hr) + (loc >> 4), c = (uint32_t)(my_c - wr) + (loc & 0xFu);  // wraps below zero: fails the range test
     uint32_t g = 0;
-    if (loc != 0xFFu && (unsigned)r < (unsigned)b.H && (unsigned)c < (unsigned)b.W) g = grid[r * b.W + c];
+    if (r < (uint32_t)b.H && c < (uint32_t)b.W && loc != 0xFFu) g = grid[r * (uint32_t)b.W + c];
     cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
   }
 #pragma unroll

@@ -1,2 +1,5 @@
-MG_CHUNKS=1 python bench.py --no-cpu-baseline --steps 5 --warmup 3 > gpurun_out/plain2.log 2>&1 && MG_CHUNKS=1 ncu --set full --clock-control none --import-source on -k regex:mg_step_kernel -s 6 -c 1 -o gpurun_out/prof_r1h_step -f python bench.py --no-cpu-baseline --steps 5 --warmup 3 > gpurun_out/ncu_s.log 2>&1
-tail -1 gpurun_out/ncu_s.log | cut -c1-100
+for c in 10 12 14 10 12 14 8; do MG_CHUNKS=$c python bench.py --no-cpu-baseline --steps 100 > gpurun_out/bench_c$c.log 2>&1; python - $c <<'PY'
+import json,sys
+d=json.loads(open(f'gpurun_out/bench_c{sys.argv[1]}.log').read().strip().splitlines()[-1]); print('chunks', sys.argv[1], 'M/s %.1f ms/step %.4f free %.1f'%(d['value']/1e6, d['ms_per_step'], d['free_running']['value']/1e6))
+PY
+done
