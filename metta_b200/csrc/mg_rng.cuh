@@ -27,7 +27,7 @@ MG_DEVICE inline void mt_seed_serial(uint32_t* mt, uint32_t seed) {
 // lane reads old[i], old[i+1] and the word 397 ahead before anyone writes; across chunks the
 // order of the serial algorithm is kept, so word i+397 (mod 624) is old for i < 227 and already
 // regenerated for i >= 227, and word 623 sees the new word 0.
-MG_DEVICE inline void mt_twist_warp(uint32_t* mt, int lane) {
+MG_DEVICE MG_NOINLINE void mt_twist_warp(uint32_t* mt, int lane) {  // once per 624 words: kept out of line, out of the hot code
   for (int s = 0; s < MT_N; s += 32) {
     int i = s + lane;
     uint32_t v = 0;
@@ -105,7 +105,7 @@ MG_DEVICE inline uint32_t uniform_below_warp(MtStream& s, int lane, uint32_t ran
 
 // std::shuffle over n indices (bits/stl_algo.h:3742-3800, two swap positions per draw).
 // Every lane runs the same loop so the draws stay warp-uniform; lane 0 owns `order`.
-MG_DEVICE inline void std_shuffle_warp(MtStream& s, int lane, uint8_t* order, int n) {
+MG_DEVICE MG_NOINLINE void std_shuffle_warp(MtStream& s, int lane, uint8_t* order, int n) {  // the fallback path
   if (lane == 0)
     for (int i = 0; i < n; i++) order[i] = (uint8_t)i;
   if (n <= 1) return;

@@ -33,6 +33,7 @@
 #define MG_LDCG(p) (*(p))
 #define MG_LD_L2(p) (*(p))
 #define MG_NANOSLEEP(ns) ((void)0)
+#define MG_ROLLED
 #define MG_LDG(p) (*(p))
 #define MG_GRID_CONSTANT
 #define MG_FADD(a, b) ((float)(a) + (float)(b))
