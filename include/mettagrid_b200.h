@@ -63,10 +63,12 @@ int mg_step_host(void* handle, const int32_t* actions_host, uint8_t* obs_host, f
 /* How mg_step_host fills a page-locked obs_host (no counterpart in the reference, whose
  * _compute_observations rewrites every byte of the caller's buffer each step, mettagrid_c.cpp:557-563,
  * 580). mode 0 (default): the whole buffer crosses the host link every call. mode 1: after one full
- * copy, a kernel writes only the leading tokens of each row that can differ from what the buffer
- * holds (the rest of a row is 0xFF padding in both); the buffer ends up byte-identical to mode 0 as
- * long as nothing but this library writes to it between calls. Another buffer address, or calling
- * this again, starts over with a full copy. Pageable buffers always take the full, staged copy. */
+ * copy, a kernel writes only what can differ from what the buffer holds: of each row the leading
+ * tokens (the rest of a row is 0xFF padding in both), and of those only the 64-byte pieces that differ
+ * from a device-side copy of the buffer's contents (allocated by this call: one more observation
+ * buffer in HBM). The buffer ends up byte-identical to mode 0 as long as nothing but this library
+ * writes to it between calls. Another buffer address, or calling this again, starts over with a full
+ * copy. Pageable buffers always take the full, staged copy. */
 int mg_set_host_export(void* handle, int32_t mode);
 
 /* Bytes mg_step_host has moved host->device and device->host through this handle so far. */

@@ -83,6 +83,7 @@ struct MgEnvs {
   int host_export_mode;
   const void* host_obs_last;      // the host buffer whose contents d_prev_counts describes (nullptr = none)
   uint16_t* d_prev_counts;        // [N*A] tokens the host row holds
+  uint8_t* d_shadow;              // [N*A][T*3] what the host buffer holds (allocated when export mode 1 is selected)
   unsigned long long* d_export_bytes;
   unsigned long long* h_export_bytes;  // pinned mirror of the counter
   unsigned long long h2d_total, d2h_total;
@@ -488,8 +489,13 @@ static int launch_export(MgEnvs* e, const MgBatch& b, cudaStream_t s, const MgHo
   const int per_cta = MG_EXPORT_WARPS * MG_EXPORT_ROWS;
   const int grid = (row_end - row_begin + per_cta - 1) / per_cta;
   if (grid <= 0) return MG_OK;
+  // the 64-byte comparison needs the three images congruent modulo 64
+  uint8_t* shadow = e->d_shadow;
+  if (ht.obs == nullptr || ((reinterpret_cast<uintptr_t>(b.obs) | reinterpret_cast<uintptr_t>(ht.obs) | reinterpret_cast<uintptr_t>(shadow)) & 63) != 0)
+    shadow = nullptr;
   MG_LAUNCH(mg_export_rows_kernel, grid, MG_EXPORT_WARPS * 32, 0, s, (const uint8_t*)b.obs, (const float*)b.rewards, (const uint8_t*)b.terminals,
-            (const uint8_t*)b.truncations, ht, (const uint16_t*)b.tok_counts, e->d_prev_counts, row_begin, row_end, b.T * 3, e->d_export_bytes);
+            (const uint8_t*)b.truncations, ht, (const uint16_t*)b.tok_counts, e->d_prev_counts, shadow, row_begin, row_end, b.T * 3,
+            e->d_export_bytes);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   return MG_OK;
@@ -751,8 +757,9 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)obs : (void*)(st + off_obs), b.obs, obs_bytes, cudaMemcpyDeviceToHost, s));
   e->d2h_total += obs_bytes;
   e->host_obs_last = nullptr;
-  if (direct && e->host_export_mode == 1) {  // from now on the host buffer is known row by row
+  if (direct && e->host_export_mode == 1) {  // from now on the host buffer is known row by row (and byte by byte)
     TRY(launch_export(e, b, s, ht, 0, (int)NA));
+    if (e->d_shadow) CUDA_TRY(cudaMemcpyAsync(e->d_shadow, b.obs, obs_bytes, cudaMemcpyDeviceToDevice, s));
     e->host_obs_last = obs;
   }
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)rewards : (void*)(st + off_rew), b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
@@ -778,6 +785,11 @@ int mg_set_host_export(void* h, int32_t mode) {
   if (!e || (mode != 0 && mode != 1)) return fail(MG_ERR_ARG, "mg_set_host_export: mode must be 0 or 1");
   e->host_export_mode = mode;
   e->host_obs_last = nullptr;
+  if (mode == 1 && e->d_shadow == nullptr) {  // allocated here so that mg_step_host itself never allocates
+    CUDA_TRY(cudaSetDevice(e->device));
+    int rc;
+    TRY(dev_alloc(e, &e->d_shadow, (size_t)e->b.num_envs * e->b.A * e->b.T * 3, false));
+  }
   return MG_OK;
 }
 

@@ -1092,7 +1092,8 @@ struct MgHostTargets {  // device-visible addresses of the caller's page-locked 
 };
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_EXPORT_WARPS * 32, 4)
     mg_export_rows_kernel(const uint8_t* obs, const float* rewards, const uint8_t* terminals, const uint8_t* truncations, MgHostTargets host,
-                          const uint16_t* tok_counts, uint16_t* prev, int row_begin, int row_end, int row_bytes, unsigned long long* bytes_out) {
+                          const uint16_t* tok_counts, uint16_t* prev, uint8_t* shadow, int row_begin, int row_end, int row_bytes,
+                          unsigned long long* bytes_out) {
   const int lane = threadIdx.x & 31;
   const int cta_first = row_begin + (int)blockIdx.x * (MG_EXPORT_WARPS * MG_EXPORT_ROWS);
   const int first = cta_first + (int)(threadIdx.x >> 5) * MG_EXPORT_ROWS;
@@ -1109,6 +1110,42 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_EXPORT_WARPS * 32, 4)
     host.truncations[r] = truncations[r];
   }
   if (host.obs == nullptr) return;
+  if (shadow != nullptr) {
+    // With a device copy of what the host buffer holds (`shadow`), a row's prefix is compared 64 bytes
+    // at a time (the unit the writes cross PCIe in: 8 lanes x 8 bytes, aligned) and only the pieces that
+    // differ are written, to the host and to the shadow. An agent that stood still keeps most of its row.
+    unsigned long long total = 0;
+#pragma unroll 1
+    for (int k = 0; k < MG_EXPORT_ROWS; k++) {
+      const int c = __shfl_sync(MG_FULL_MASK, cur, k), p = __shfl_sync(MG_FULL_MASK, pv, k);
+      if (first + k >= row_end) break;
+      const int n = c > p ? c : p;
+      if (n == 0) continue;
+      int nb = (n * 3 + 7) & ~7;
+      nb = nb < row_bytes ? nb : row_bytes;
+      const size_t lo = (size_t)(first + k) * row_bytes, hi = lo + nb;
+#pragma unroll 1
+      for (size_t w = lo & ~(size_t)63; w < hi; w += 256) {
+        const size_t piece = w + (size_t)lane * 8;
+        const bool in_range = piece >= lo && piece < hi;
+        uint2 nv, sv;
+        nv.x = nv.y = sv.x = sv.y = 0u;
+        if (in_range) {
+          nv = *reinterpret_cast<const uint2*>(obs + piece);
+          sv = *reinterpret_cast<const uint2*>(shadow + piece);
+        }
+        const uint32_t differ = __ballot_sync(MG_FULL_MASK, in_range && (nv.x != sv.x || nv.y != sv.y));
+        const bool write = in_range && ((differ >> (lane & 24)) & 0xFFu) != 0u;
+        if (write) {
+          *reinterpret_cast<uint2*>(host.obs + piece) = nv;
+          *reinterpret_cast<uint2*>(shadow + piece) = nv;
+        }
+        total += 8ull * (unsigned long long)__popc(__ballot_sync(MG_FULL_MASK, write));
+      }
+    }
+    if (lane == 0 && total != 0) atomicAdd(bytes_out, total);
+    return;
+  }
   const bool sector_aligned = MG_EXPORT_ALIGN > 8 && ((reinterpret_cast<uintptr_t>(obs) | reinterpret_cast<uintptr_t>(host.obs)) & (MG_EXPORT_ALIGN - 1)) == 0;
   unsigned long long total = 0;
 #pragma unroll 1
