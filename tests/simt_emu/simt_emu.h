@@ -100,20 +100,27 @@ static inline T emu_exchange(T v, int src_lane) {
   simt_emu::warp_barrier();
   return out;
 }
+// width: the warp is split into segments of `width` lanes (a power of two), as the hardware does
 template <typename T>
-static inline T __shfl_sync(unsigned, T v, int src, int = 32) { return emu_exchange(v, src & 31); }
-template <typename T>
-static inline T __shfl_up_sync(unsigned, T v, unsigned d, int = 32) {
+static inline T __shfl_sync(unsigned, T v, int src, int width = 32) {
   int lane = (int)(threadIdx.x & 31);
-  return emu_exchange(v, lane - (int)d >= 0 ? lane - (int)d : lane);
+  return emu_exchange(v, (lane & ~(width - 1)) | (src & (width - 1)));
 }
 template <typename T>
-static inline T __shfl_down_sync(unsigned, T v, unsigned d, int = 32) {
-  int lane = (int)(threadIdx.x & 31);
-  return emu_exchange(v, lane + (int)d < 32 ? lane + (int)d : lane);
+static inline T __shfl_up_sync(unsigned, T v, unsigned d, int width = 32) {
+  int lane = (int)(threadIdx.x & 31), in_seg = lane & (width - 1);
+  return emu_exchange(v, in_seg - (int)d >= 0 ? lane - (int)d : lane);
 }
 template <typename T>
-static inline T __shfl_xor_sync(unsigned, T v, int m, int = 32) { return emu_exchange(v, (int)(threadIdx.x & 31) ^ m); }
+static inline T __shfl_down_sync(unsigned, T v, unsigned d, int width = 32) {
+  int lane = (int)(threadIdx.x & 31), in_seg = lane & (width - 1);
+  return emu_exchange(v, in_seg + (int)d < width ? lane + (int)d : lane);
+}
+template <typename T>
+static inline T __shfl_xor_sync(unsigned, T v, int m, int width = 32) {
+  int lane = (int)(threadIdx.x & 31), target = lane ^ m;
+  return emu_exchange(v, (target & ~(width - 1)) == (lane & ~(width - 1)) ? target : lane);
+}
 static inline unsigned __ballot_sync(unsigned, int pred) {
   simt_emu::State& s = simt_emu::st();
   simt_emu::WarpState& w = s.warps[s.cur / 32];
