@@ -116,9 +116,30 @@ def cogames():
         run(name, cfg, grid, 5, steps, c_cfg=c_cfg)
 
 
+def cogames_clipper_config():
+    """RepairMission (clipper with clip_period 50): config and map only. Which assembler the reference's
+    clipper picks depends on heap addresses, so its outputs are not a fixture; the config
+    is used for oracle <-> kernel lockstep."""
+    sys.path.insert(0, "/root/reference/packages/cogames/src")
+    from cogames.cogs_vs_clips import missions as M
+
+    ref_cfg = M.RepairMission.model_copy(update={"num_cogs": 4}).make_env()
+    grid = ref_cfg.game.map_builder.create().build_for_num_agents(ref_cfg.game.num_agents).grid
+    dump = ref_cfg.model_dump()
+    dump["game"]["map_builder"] = None
+    cfg = MettaGridConfig.from_reference(dump)
+    np.savez_compressed(os.path.join(HERE, "cogames_repair_config.npz"), grid=grid)
+    with open(os.path.join(HERE, "cogames_repair_config.json"), "w") as f:
+        json.dump(cfg.model_dump(), f, indent=1, sort_keys=False, default=str)
+    print("cogames_repair_config", grid.shape, "clip_period", cfg.game.clipper.clip_period if cfg.game.clipper else None)
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "cogames":
+    if len(sys.argv) > 1 and sys.argv[1] == "clipper":
+        cogames_clipper_config()
+    elif len(sys.argv) > 1 and sys.argv[1] == "cogames":
         cogames()
     else:
         main()
         cogames()
+        cogames_clipper_config()

@@ -97,3 +97,27 @@ def test_cogames_mission_8k_envs(lib):
     codes = names_to_codes(low, grid)[None]
     env, _ = _run(cfg, low, codes, 8192, 60, sample=[0, 7, 4095, 4096, 8191], map_stride=0, twin_offset=4096)
     assert np.all(env["current_step"] == 60)
+
+
+def test_cogames_clipper_mission_lockstep(lib):
+    """RepairMission (clipper with clip_period 50) on the GPU against the oracle, 48 envs x 300 steps."""
+    import json
+    import os
+
+    from golden_util import GOLDEN
+    from harness import Lockstep
+
+    from metta_b200.config import MettaGridConfig
+
+    with open(os.path.join(GOLDEN, "cogames_repair_config.json")) as f:
+        cfg = MettaGridConfig.from_reference(json.load(f))
+    grid = np.load(os.path.join(GOLDEN, "cogames_repair_config.npz"))["grid"]
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    n = 48
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=n, seeds=np.arange(n) + 200, cuda=True)
+    rng = np.random.RandomState(32)
+    for s in range(300):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+    ls.compare_state()
+    assert (ls.batch.read_assemblers()["flags"] & 1).any()
+    ls.close()

@@ -43,6 +43,30 @@ def test_emulated_cogames_missions(name, steps, emu_lib):
     ls.close()
 
 
+def test_emulated_cogames_clipper(emu_lib):
+    """RepairMission: clipper with clip_period 50 (its own generator copy, infection weights, unclip
+    protocols). Oracle <-> kernels only: the reference's pick order depends on heap addresses."""
+    import json
+    import os
+
+    from golden_util import GOLDEN
+
+    from metta_b200.config import MettaGridConfig
+
+    with open(os.path.join(GOLDEN, "cogames_repair_config.json")) as f:
+        cfg = MettaGridConfig.from_reference(json.load(f))
+    grid = np.load(os.path.join(GOLDEN, "cogames_repair_config.npz"))["grid"]
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=2, seeds=[8, 9], clib=emu_lib)
+    rng = np.random.RandomState(31)
+    for s in range(160):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+    ls.compare_state()
+    asm = ls.batch.read_assemblers()
+    assert (asm["flags"] & 1).any(), "the clipper should have clipped something within 160 steps at period 50"
+    ls.close()
+
+
 def test_emulated_arena(emu_lib):
     cfg = make_arena(24)
     low = lower_game_config(cfg.game, 62, 62)
