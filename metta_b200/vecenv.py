@@ -107,6 +107,8 @@ class GpuMettaGridVecEnv:
             self._h_term = np.zeros(NA, dtype=np.bool_)
             self._h_trunc = np.zeros(NA, dtype=np.bool_)
         self._seed = seed
+        self._map_stride = map_stride
+        self._pending = None
         self._episodes_reported = 0.0
         self._accum_prev: Optional[np.ndarray] = None
         self.driver_env = self
@@ -124,6 +126,8 @@ class GpuMettaGridVecEnv:
     def async_reset(self, seed: Optional[int] = None) -> None:
         if seed is not None:
             self._seed = seed
+        if self._pending is not None:
+            self._apply_pending_config()
         seeds = (np.arange(self.num_envs, dtype=np.int64) + int(self._seed)) & 0xFFFFFFFF
         maps = np.arange(self.num_envs) % len(self.pool.codes)
         self.batch.reset(seeds.astype(np.uint32), maps.astype(np.int32))
@@ -211,6 +215,60 @@ class GpuMettaGridVecEnv:
         steps = np.ascontiguousarray(steps, dtype=np.uint32)
         self.batch.set_early_reset(steps)
         self._early[:] = steps
+
+    # ---- the read-only properties of MettaGrid (mettagrid_c.cpp:1007-1041) that callers ask for
+    @property
+    def obs_width(self) -> int:
+        return int(self.cfg.game.obs.width)
+
+    @property
+    def obs_height(self) -> int:
+        return int(self.cfg.game.obs.height)
+
+    @property
+    def max_steps(self) -> int:
+        return self._max_steps
+
+    @property
+    def map_width(self) -> int:
+        return int(self.pool.codes.shape[2])
+
+    @property
+    def map_height(self) -> int:
+        return int(self.pool.codes.shape[1])
+
+    @property
+    def resource_names(self) -> list[str]:
+        return list(self.lowered.resource_names)
+
+    @property
+    def object_type_names(self) -> list[str]:
+        n = max(self.lowered.type_names) + 1 if self.lowered.type_names else 0
+        return [self.lowered.type_names.get(i, "") for i in range(n)]
+
+    @property
+    def current_step(self) -> np.ndarray:
+        """Steps taken in the running episode, per env (host mirror, no device read-back)."""
+        return self._steps.copy()
+
+    def action_success(self) -> np.ndarray:
+        """bool [num_envs, agents_per_env]: MettaGrid::action_success of the last step."""
+        return self.batch.read_action_success()
+
+    def set_mg_config(self, cfg, maps: Optional[Sequence] = None, map_codes: Optional[np.ndarray] = None) -> None:
+        """CurriculumEnv's hook (metta/rl/.../curriculum_env.py:105-117): the next `async_reset` builds the
+        batch from this config (and these maps; the current pool is kept when none are given and the map
+        cell names still resolve)."""
+        self._pending = (cfg, maps, map_codes)
+
+    def _apply_pending_config(self) -> None:
+        cfg, maps, map_codes = self._pending
+        self._pending = None
+        if maps is None and map_codes is None:
+            map_codes = self.pool.codes
+        self.batch.close()
+        self.__init__(cfg, self.num_envs, maps=maps, map_codes=map_codes, seed=self._seed, device=self.device, host=self.host,
+                      map_stride=self._map_stride)
 
     def get_episode_rewards(self):
         """f32 [num_envs, agents_per_env] (MettaGrid::get_episode_rewards; CurriculumEnv takes its mean)."""

@@ -122,3 +122,27 @@ def test_rollout_loop_with_a_torch_policy_reads_the_kernel_output_in_place():
     st = env.batch.read_env()
     assert (st["current_step"] == 20).all()
     env.close()
+
+
+def test_properties_and_config_swap():
+    import torch
+
+    n = 3
+    cfg, low, codes, env = _make("tiny_truncating", n)
+    assert (env.obs_width, env.obs_height) == (cfg.game.obs.width, cfg.game.obs.height)
+    assert env.max_steps == cfg.game.max_steps and env.map_height == codes.shape[0] and env.map_width == codes.shape[1]
+    assert env.resource_names == list(low.resource_names) and "wall" in env.object_type_names
+    env.reset(seed=2)
+    A = cfg.game.num_agents
+    env.step(torch.zeros(n * A, dtype=torch.int32, device="cuda"))
+    assert env.action_success().shape == (n, A) and (env.current_step == 1).all()
+    # CurriculumEnv.set_mg_config: another task from the next reset on
+    cfg2, grid2 = SCENARIOS["kitchen_sink"]()
+    env.set_mg_config(cfg2, maps=[grid2])
+    obs, _ = env.reset(seed=5)
+    assert env.agents_per_env == cfg2.game.num_agents and obs.shape == (n * cfg2.game.num_agents, cfg2.game.obs.num_tokens, 3)
+    _, _, _, ref = _make("kitchen_sink", n)
+    ref_obs, _ = ref.reset(seed=5)
+    assert torch.equal(obs, ref_obs)
+    env.close()
+    ref.close()
