@@ -119,17 +119,16 @@ MG_DEVICE inline int inv_free_space(const InvView& v, int item) {
 MG_DEVICE inline void order_push_front(uint64_t* order, int item) { *order = (*order << 4) | (uint64_t)item; }
 
 MG_DEVICE inline void order_erase(uint64_t* order, int item) {
-  uint64_t o = *order;
-  MG_ROLLED
-  for (int k = 0; k < 16; k++) {
-    if (((o >> (4 * k)) & 0xF) == (uint64_t)item) {
-      uint64_t low = k == 0 ? 0ull : (o & ((1ull << (4 * k)) - 1ull));
-      uint64_t high = (o >> (4 * (k + 1))) << (4 * k);
-      if (k == 15) high = 0;
-      *order = low | high | (0xFull << 60);
-      return;
-    }
-  }
+  // find the nibble equal to `item` (ids are 0..12, 0xF ends the list): xor with the id in every nibble,
+  // then the classic zero-nibble test; the lowest hit is the entry (an id occurs at most once)
+  const uint64_t o = *order;
+  const uint64_t x = o ^ ((uint64_t)item * 0x1111111111111111ull);
+  const uint64_t hit = (x - 0x1111111111111111ull) & ~x & 0x8888888888888888ull;
+  if (hit == 0ull) return;
+  const int k = (__ffsll((long long)hit) - 1) >> 2;  // nibble index
+  const uint64_t low = k == 0 ? 0ull : (o & ((1ull << (4 * k)) - 1ull));
+  const uint64_t high = k == 15 ? 0ull : ((o >> (4 * (k + 1))) << (4 * k));
+  *order = low | high | (0xFull << 60);
 }
 
 MG_DEVICE int inv_update(EnvCtx& e, InvView& v, int item, int attempted_delta, bool ignore_limits, int depth);
@@ -236,6 +235,10 @@ MG_DEVICE inline InvView inv_list_view(const EnvCtx& e, const InvList& l, int i)
 MG_DEVICE MG_NOINLINE int shared_update(EnvCtx& e, const InvList& l, int item, int delta) {
   const int n = inv_list_size(l);
   if (n == 0) return 0;
+  if (n == 1) {  // one inventory: both branches below come down to this single update with the whole delta
+    InvView v = inv_list_view(e, l, 0);
+    return inv_update(e, v, item, delta, false, 0);
+  }
   int delta_remaining = delta;
   uint64_t active = n >= 64 ? ~0ull : ((1ull << n) - 1ull);  // inventories still to consider, in order
   int num_remaining = n;

@@ -151,6 +151,7 @@ static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |
 static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
 static inline long long clock64() { return 0; }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
+static inline int __ffsll(long long x) { return __builtin_ffsll(x); }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline double atomicAdd(double* p, double v) { double o = *p; *p += v; return o; }
 static inline float atomicAdd(float* p, float v) { float o = *p; *p += v; return o; }

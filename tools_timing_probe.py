@@ -16,11 +16,14 @@ act=torch.randint(0,5,(N*A,),dtype=torch.int32).to(dev)
 b.set_buffers(obs.data_ptr(),term.data_ptr(),trunc.data_ptr(),rew.data_ptr(),act.data_ptr())
 b.reset((np.arange(N)+42).astype(np.uint32),(np.arange(N)%256).astype(np.int32))
 flush=torch.empty(256*1024*1024,dtype=torch.uint8,device=dev)
-for s in range(20):
+STEPS=int(sys.argv[3]) if len(sys.argv)>3 else 20
+for s in range(STEPS):
     act.copy_(torch.randint(0,5,(N*A,),dtype=torch.int32))
     if FLUSH: flush.fill_(s)
     torch.cuda.synchronize()
+    if s == STEPS-1: uses0 = b.read_assemblers()["uses_count"].astype(np.int64).sum(1)
     b.step(); torch.cuda.synchronize()
+uses = b.read_assemblers()["uses_count"].astype(np.int64).sum(1) - uses0
 sp=b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64)
 names=['load: loads+fold','load: reset/stage','load: rest(prefetch,ctx)','decide: intents','decide: shuffle draws','decide: conflicts+apply','act parallel','act ordered','post','finish: rewards+records','', 'finish: write-back']
 tot=sp.sum(1)
@@ -29,3 +32,10 @@ print('envs with ordered work: %.1f%%' % (100.0*(sp[:,7] > 2000).mean()))
 for i,n in enumerate(names):
     if not n: continue
     c=sp[:,i]; print('%-34s mean %8.0f p50 %8.0f p99 %8.0f max %8.0f'%(n,c.mean(),np.percentile(c,50),np.percentile(c,99),c.max()))
+
+par, orde = sp[:,6], sp[:,7]
+for k in range(0, 6):
+    m = uses == k
+    if m.sum(): print('envs with %d successful assembler uses in the step: %5d  act parallel mean %7.0f  ordered mean %7.0f  total mean %7.0f' % (k, m.sum(), par[m].mean(), orde[m].mean(), tot[m].mean()))
+m = uses >= 6
+if m.sum(): print('envs with >=6 uses: %d  act parallel mean %.0f total mean %.0f' % (m.sum(), par[m].mean(), tot[m].mean()))
