@@ -364,6 +364,23 @@ MG_DEVICE inline int asm_current_protocol(const EnvCtx& e, const AsmRec* a) {
   return p;
 }
 
+// The same from a neighbourhood that has already been scanned (key of sorted vibes, agent count).
+MG_DEVICE inline int asm_protocol_for(const EnvCtx& e, const AsmRec* a, uint64_t key, int num_agents) {
+  int first, n;
+  if (a->flags & MG_ASMF_CLIPPED) {
+    if (a->unclip_protocol < 0) return -1;
+    first = a->unclip_protocol;
+    n = 1;
+  } else {
+    const int32_t* t = asm_type_cfg(e.cfg, a->cell);
+    first = t[MG_ASM_FIRST_PROTOCOL];
+    n = t[MG_ASM_NUM_PROTOCOLS];
+  }
+  int p = find_protocol(e.cfg, first, n, key, num_agents);
+  if (p < 0 && key != 0) p = find_protocol(e.cfg, first, n, 0, num_agents);
+  return p;
+}
+
 // ---------------------------------------------------------------- clipper bookkeeping (systems/clipper.hpp)
 MG_DEVICE inline int asm_cheb(const AsmRec* a, const AsmRec* b) {
   int dr = (int)a->r - (int)b->r, dc = (int)a->c - (int)b->c;
@@ -431,6 +448,9 @@ MG_DEVICE inline bool list_has_positive(const ItemList& l) {
 }
 
 MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
+#ifdef MG_TIMING
+  long long tk0 = clock64(), tk1 = 0, tk2 = 0, tk3 = 0;
+#endif
   AsmRec* a = &e.asms[asm_idx];
   const int32_t* t = asm_type_cfg(e.cfg, a->cell);
   uint32_t max_uses = (uint32_t)t[MG_ASM_MAX_USES];
@@ -438,7 +458,33 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   uint32_t remaining = a->cooldown_end <= e.current_step ? 0u : a->cooldown_end - e.current_step;  // :318-323
   bool partial = t[MG_ASM_ALLOW_PARTIAL] != 0;
   if (remaining > 0 && !partial) return false;
-  int pi = asm_current_protocol(e, a);
+  // One pass over the eight cells around the assembler, in the ring order of get_surrounding_agents
+  // (:48-92: NW,N,NE,W,E,SW,S,SE): who stands there (agent index per ring position, 0xFF = nobody), how
+  // many, and their non-zero vibes sorted into the protocol key (get_local_vibe :353-375). The key is
+  // kept sorted in a register (smallest vibe in the highest used byte), not in an array.
+  const int ar = (int)a->r, ac = (int)a->c;
+  uint64_t ring = ~0ull, key = 0ull;
+  int num_agents = 0, nv = 0;
+  MG_ROLLED
+  for (int k = 0; k < 8; k++) {
+    const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
+    if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+    const uint16_t g = grid_at(e, rr, cc);
+    if (MG_GRID_KIND(g) != MG_GK_AGENT) continue;
+    const uint32_t idx = MG_GRID_INDEX(g);
+    ring = (ring & ~(0xFFull << (8 * k))) | ((uint64_t)idx << (8 * k));
+    num_agents++;
+    const uint32_t vb = e.ag[idx].vibe;
+    if (vb != 0u) {
+      int gt = 0;  // entries already in the key that are larger: they sit at the low end
+      while (gt < nv && ((key >> (8 * gt)) & 0xFFull) > vb) gt++;
+      const uint64_t low = gt == 0 ? 0ull : (key & ((1ull << (8 * gt)) - 1ull));
+      const uint64_t high = gt >= 7 ? 0ull : ((key >> (8 * gt)) << (8 * (gt + 1)));
+      key = high | ((uint64_t)vb << (8 * gt)) | low;
+      nv++;
+    }
+  }
+  int pi = asm_protocol_for(e, a, key, num_agents);
   if (pi < 0) return false;
   const int32_t* p = proto_cfg(e.cfg, pi);
   bool clipped = (a->flags & MG_ASMF_CLIPPED) != 0;
@@ -455,23 +501,17 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   MG_ROLLED
   for (int i = 0; i < n_out; i++) has_output = has_output || MG_OUT_AMOUNT(i) > 0;
   if (scaled && !has_output && p[MG_PROTO_HAS_OUTPUT] && !clipped) return false;
-  // get_surrounding_agents(&actor) :48-92: NW,N,NE,W,E,SW,S,SE restricted to valid cells, starting at the actor
-  const int ar = (int)a->r, ac = (int)a->c;
+  // the inputs: the ring again, starting at the actor's position
   int start = 0;
   MG_ROLLED
-  for (int k = 0; k < 8; k++) {
-    const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
-    if (rr == (int)e.ag[actor].r && cc == (int)e.ag[actor].c) start = k;
-  }
+  for (int k = 0; k < 8; k++)
+    if (((ring >> (8 * k)) & 0xFFull) == (uint64_t)actor) start = k;
   InvList inputs;
   inputs.agents = 0; inputs.n_agents = 0; inputs.n_chests = 0; inputs.chests = nullptr;
   MG_ROLLED
   for (int j = 0; j < 8; j++) {
-    const int k = (start + j) & 7;
-    const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
-    if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
-    const uint16_t g = grid_at(e, rr, cc);
-    if (MG_GRID_KIND(g) == MG_GK_AGENT) inputs.agents |= (uint64_t)MG_GRID_INDEX(g) << (8 * inputs.n_agents++);
+    const uint64_t idx = (ring >> (8 * ((start + j) & 7))) & 0xFFull;
+    if (idx != 0xFFull) inputs.agents |= idx << (8 * inputs.n_agents++);
   }
   uint16_t chest_idx[MG_MAX_SHARED - 8];
   const int dist = t[MG_ASM_CHEST_DISTANCE];
@@ -489,6 +529,9 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
       }
   }
   const int nin = inv_list_size(inputs);
+#ifdef MG_TIMING
+  tk1 = clock64();
+#endif
   MG_ROLLED
   for (int i = 0; i < n_in; i++) {  // can_afford_protocol :124-137 (u16 accumulation)
     const int item = lin[MG_LIST_ITEM(i)];
@@ -532,6 +575,9 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
     }
   }
   if (!can_receive && !clipped) return false;
+#ifdef MG_TIMING
+  tk2 = clock64();
+#endif
   MG_ROLLED
   for (int i = 0; i < n_in; i++) shared_update(e, inputs, lin[MG_LIST_ITEM(i)], -MG_IN_AMOUNT(i));
   MG_ROLLED
@@ -555,7 +601,20 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   } else {
     a->uses_count++;
   }
+#ifdef MG_TIMING
+  tk3 = clock64();
+#endif
   if (e.asm_records_on_use) write_asm_tokens(*e.batch, a, e.current_step, token_record(*e.batch, e.env, MG_GK_ASM, (uint32_t)asm_idx));
+#ifdef MG_TIMING
+  if (e.batch->dbg != nullptr) {  // successful uses only: set-up and scans | checks | consume and give | record
+    uint32_t* d = e.batch->dbg + (size_t)e.env * 16 + 12;
+    const long long tk4 = clock64();
+    atomicAdd(d + 0, (uint32_t)(tk1 - tk0));
+    atomicAdd(d + 1, (uint32_t)(tk2 - tk1));
+    atomicAdd(d + 2, (uint32_t)(tk3 - tk2));
+    atomicAdd(d + 3, (uint32_t)(tk4 - tk3));
+  }
+#endif
   return true;
 }
 

@@ -887,6 +887,8 @@ template <int MAXA>
 MG_DEVICE inline void step_env_warp(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
 #ifdef MG_TIMING
   if (lane == 0) { sm.tick_last = clock64(); for (int i = 0; i < 16; i++) sm.ticks[i] = 0; }
+  if (lane >= 12 && lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = 0u;
+  __syncwarp();
 #endif
   step_phase_load<MAXA>(b, sm, env, lane);
   MG_SM_TICK(sm, 2);
@@ -898,7 +900,7 @@ MG_DEVICE inline void step_env_warp(const MgBatch& b, StepSmem<MAXA>& sm, int en
   step_phase_finish<MAXA>(b, sm, env, lane);
   MG_SM_TICK(sm, 11);
 #ifdef MG_TIMING
-  if (lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = sm.ticks[lane];
+  if (lane < 12 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = sm.ticks[lane];  // 12..15: assembler_on_use adds to them
 #endif
 }
 

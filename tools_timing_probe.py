@@ -39,3 +39,8 @@ for k in range(0, 6):
     if m.sum(): print('envs with %d successful assembler uses in the step: %5d  act parallel mean %7.0f  ordered mean %7.0f  total mean %7.0f' % (k, m.sum(), par[m].mean(), orde[m].mean(), tot[m].mean()))
 m = uses >= 6
 if m.sum(): print('envs with >=6 uses: %d  act parallel mean %.0f total mean %.0f' % (m.sum(), par[m].mean(), tot[m].mean()))
+
+su = sp[:,12:16]
+m = uses == 1
+if m.sum():
+    print('one successful use: set-up+scans %.0f | checks %.0f | consume+give %.0f | record %.0f  (sum %.0f)' % (su[m,0].mean(), su[m,1].mean(), su[m,2].mean(), su[m,3].mean(), su[m].sum(1).mean()))
