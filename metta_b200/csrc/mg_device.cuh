@@ -462,11 +462,18 @@ MG_DEVICE MG_NOINLINE bool assembler_on_use(EnvCtx& e, int asm_idx, int actor) {
   // (:48-92: NW,N,NE,W,E,SW,S,SE): who stands there (agent index per ring position, 0xFF = nobody), how
   // many, and their non-zero vibes sorted into the protocol key (get_local_vibe :353-375). The key is
   // kept sorted in a register (smallest vibe in the highest used byte), not in an array.
+  // In the parallel pass none of this is needed: an agent only gets there when no other agent stands in
+  // or moves into the block (step_phase_decide, rule 3), so the actor is the whole neighbourhood.
   const int ar = (int)a->r, ac = (int)a->c;
   uint64_t ring = ~0ull, key = 0ull;
   int num_agents = 0, nv = 0;
+  if (e.concurrent) {
+    ring = (ring & ~0xFFull) | (uint64_t)actor;
+    num_agents = 1;
+    key = e.ag[actor].vibe;
+  }
   MG_ROLLED
-  for (int k = 0; k < 8; k++) {
+  for (int k = e.concurrent ? 8 : 0; k < 8; k++) {
     const int rr = ar + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = ac + (int)((0x9224u >> (2 * k)) & 3u) - 1;
     if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
     const uint16_t g = grid_at(e, rr, cc);
