@@ -31,8 +31,8 @@ MAP_POOL = 256
 ALG_BYTES_OBS = 890  # per agent-step, observation kernel: 600 obs + 242 window gather + 48 agent record
 ALG_BYTES_ACT = 58  # action kernel: 4 action + 4 reward + 2 flags + 48 agent record write-back
 # DRAM traffic of one observation-kernel launch over 4096 envs x 24 agents, from the committed ncu capture
-# (profiles/r01i_ncu_full_summary.txt): 68.89 MB read + 22.44 MB written (algorithmic: 87.49 MB)
-NCU_OBS_TRAFFIC_BYTES = 68888832 + 22443008
+# (profiles/r01k_ncu_full_summary.txt): 68.92 MB read + 23.40 MB written (algorithmic: 87.49 MB)
+NCU_OBS_TRAFFIC_BYTES = 68916736 + 23396352
 METRIC = "arena agent-steps/sec"
 
 
@@ -338,7 +338,7 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "mg_obs_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": NCU_OBS_TRAFFIC_BYTES if N == ENVS_PER_GPU else None,
-                         "traffic_source": "profiles/r01i_ncu_full_summary.txt (ncu --set full, one launch over 4096 envs: dram__bytes_read.sum + dram__bytes_write.sum)",
+                         "traffic_source": "profiles/r01k_ncu_full_summary.txt (ncu --set full, one launch over 4096 envs: dram__bytes_read.sum + dram__bytes_write.sum)",
                          "peak_source": peak_kind,
                          "kernel_ms": obs_mean_ms, "alg_bytes_per_launch": ALG_BYTES_OBS * N * A,
                          "step_kernel_ms": act_mean_ms, "whole_step_frac": (ALG_BYTES_OBS + ALG_BYTES_ACT) * N * A / ((obs_mean_ms + act_mean_ms) / 1000.0) / 1e9 / peak},
