@@ -57,6 +57,14 @@ struct StepSmem {
   EnvCtx ctx;  // warp-uniform; lives here so that passing it to out-of-line functions costs no stack traffic
 };
 
+// An EnvRec moves as four 16-byte words, not field by field.
+MG_DEVICE inline void copy_env_rec(EnvRec* dst, const EnvRec* src) {
+  const uint4* s4 = reinterpret_cast<const uint4*>(src);
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+  const uint4 a = s4[0], b = s4[1], c = s4[2], d = s4[3];
+  d4[0] = a; d4[1] = b; d4[2] = c; d4[3] = d;
+}
+
 // Fills `e` where it lives (the step kernel keeps it in shared memory: no copy through registers).
 MG_DEVICE inline void init_ctx(EnvCtx& e, const MgBatch& b, int env, AgentRec* ag, const EnvRec& er) {
   e.cfg = b.cfg;
@@ -489,7 +497,8 @@ template <int MAXA>
 MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
   const int32_t* cfg = b.cfg;
   const int A = b.A;
-  EnvRec er = b.env[env];
+  EnvRec er;
+  copy_env_rec(&er, &b.env[env]);
   // ---- bring the env in. Every load that does not depend on another is issued before the first
   // use, so the whole stage costs about one HBM round trip instead of one per array: agent records
   // and their 16 per-step stat slots (16-byte loads), actions, the pending token counts of the last
@@ -607,7 +616,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
   if (b.reward_game_stats && lane < (b.GS * 4 + 127) / 128) MG_PREFETCH_L2(b.game_stats + (size_t)env * b.GS + lane * 32);
   er.current_step += 1;
   if (lane == 0) {
-    sm.er = er;
+    copy_env_rec(&sm.er, &er);
     EnvCtx& e = sm.ctx;
     init_ctx(e, b, env, sm.ag, er);
     e.hot = sm.hot;
@@ -830,7 +839,8 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
   const int32_t* cfg = b.cfg;
   const int A = b.A;
   EnvCtx& e = sm.ctx;
-  EnvRec er = sm.er;
+  EnvRec er;
+  copy_env_rec(&er, &sm.er);
   // rewards, episode totals, truncation (mettagrid_c.cpp:655-677) and the write-back
   const uint32_t max_steps = (uint32_t)cfg[MGC_MAX_STEPS];
   bool term = false, trunc = false;
@@ -879,7 +889,7 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
       }
     }
   }
-  if (lane == 0) b.env[env] = er;
+  if (lane == 0) copy_env_rec(&b.env[env], &er);
 }
 
 // One env, one warp: the five phases.
