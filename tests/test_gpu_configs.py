@@ -121,3 +121,17 @@ def test_cogames_clipper_mission_lockstep(lib):
     ls.compare_state()
     assert (ls.batch.read_assemblers()["flags"] & 1).any()
     ls.close()
+
+
+def test_arena_long_run_with_episode_ends(lib):
+    """Arena, 1024 envs, 2000 steps with episodes of 450 steps (so every env is rebuilt from the map pool
+    four times, with map rotation): sampled envs in lockstep with the oracle the whole way."""
+    from metta_b200.builders import make_arena
+    from metta_b200.maps import arena_maps
+
+    cfg = make_arena(24, max_steps=450)
+    cfg.game.episode_truncates = True
+    low = lower_game_config(cfg.game, 62, 62)
+    codes = arena_maps(low, 32, seed=21)
+    env, episodes = _run(cfg, low, codes, 1024, 2000, sample=[0, 511, 513, 1023], map_stride=3, twin_offset=512, seed0=900)
+    assert np.all(env["episodes"] == 4) and episodes == 4 * 4
