@@ -1,2 +1,8 @@
-timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest tests/test_gpu_parity.py -x -q -k "fixture or host_buffer" > gpurun_out/sanitizer_mem.log 2>&1; echo "memcheck rc=$?"; tail -5 gpurun_out/sanitizer_mem.log
-timeout 900 compute-sanitizer --tool racecheck --error-exitcode 9 python -m pytest tests/test_gpu_parity.py -x -q -k "fixture" > gpurun_out/sanitizer_race.log 2>&1; echo "racecheck rc=$?"; tail -5 gpurun_out/sanitizer_race.log
+export MG_STEP_MODE=queue MG_QUEUE_EARLY=8 MG_QUEUE_LATE=0
+MG_LIB_PATH=build_variants/lib_q32.so timeout 300 python bench.py --no-cpu-baseline > gpurun_out/bench_q32.log 2>&1
+tail -c 300 gpurun_out/bench_q32.log
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_q32.log').read().strip().splitlines()[-1])
+print('queue q32 M/s %.1f ms/step %.4f'%(d['value']/1e6, d['ms_per_step']))
+PY
