@@ -1,8 +1,2 @@
-export MG_STEP_MODE=queue MG_QUEUE_EARLY=8 MG_QUEUE_LATE=0
-MG_LIB_PATH=build_variants/lib_q32.so timeout 300 python bench.py --no-cpu-baseline > gpurun_out/bench_q32.log 2>&1
-tail -c 300 gpurun_out/bench_q32.log
-python - <<'PY'
-import json
-d=json.loads(open('gpurun_out/bench_q32.log').read().strip().splitlines()[-1])
-print('queue q32 M/s %.1f ms/step %.4f'%(d['value']/1e6, d['ms_per_step']))
-PY
+MG_CHUNKS=1 ncu --set full --clock-control none --import-source on -k regex:mg_obs_kernel -s 215 -c 1 -o gpurun_out/prof_r1k_obs_late -f python bench.py --no-cpu-baseline --steps 200 --warmup 10 > gpurun_out/ncu_o2.log 2>&1
+tail -1 gpurun_out/ncu_o2.log | cut -c1-100

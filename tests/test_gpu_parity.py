@@ -102,6 +102,23 @@ def test_arena_auto_reset_and_map_rotation(lib):
     ls.close()
 
 
+def test_rebinding_buffers_recaptures_the_step_graph(lib, monkeypatch):
+    """set_buffers with other tensors in the middle of a run (the captured step graph holds the old
+    addresses and has to be rebuilt), several slices."""
+    monkeypatch.setenv("MG_CHUNKS", "4")
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 20
+    ls = Lockstep(cfg, arena_maps(low, 3, seed=8), num_envs=n, seeds=np.arange(n) + 5, cuda=True)
+    rng = np.random.RandomState(13)
+    for s in range(30):
+        if s in (10, 20):
+            ls.buf = HostBuffers(ls.N * ls.A, ls.T, cuda=True)
+            ls.batch.set_buffers(*ls.buf.ptrs)
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.close()
+
+
 def test_queue_mode_matches_oracle(lib, monkeypatch):
     """MG_STEP_MODE=queue: step kernel with one env per CTA handing finished envs to observation CTAs
     that run beside it. Same results as the default sliced launch."""
