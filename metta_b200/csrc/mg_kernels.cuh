@@ -1091,7 +1091,9 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_queue
 // (rounded up to 8 bytes: the device row is right for every byte, so copying too much is harmless)
 // of MG_EXPORT_ROWS rows; the CTA's first warp also writes the rows' rewards and flags.
 // host.obs == nullptr only records the counts (after a full copy).
+#ifndef MG_EXPORT_ROWS
 #define MG_EXPORT_ROWS 4
+#endif
 #ifndef MG_EXPORT_ALIGN
 #define MG_EXPORT_ALIGN 32
 #endif
