@@ -235,6 +235,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &b.asms, N * (size_t)b.max_asm));
   TRY(dev_alloc(e, &b.chests, N * (size_t)b.max_chest));
   TRY(dev_alloc(e, &b.agent_stats, N * A * (size_t)b.S));
+  TRY(dev_alloc(e, &b.hot_stats, N * A * (size_t)MG_HOT_STATS));
   TRY(dev_alloc(e, &b.game_stats, N * (size_t)b.GS));
   TRY(dev_alloc(e, &b.rng, N * MT_N));
   if (b.has_clipper) TRY(dev_alloc(e, &b.clip_rng, N * MT_N));
@@ -882,6 +883,13 @@ int mg_read(void* h, int32_t what, void* host_out, int64_t nbytes) {
     CUDA_TRY(cudaDeviceSynchronize());
   }
   CUDA_TRY(cudaMemcpy(host_out, p, bytes, cudaMemcpyDeviceToHost));
+  if (what == MG_ST_AGENT_STATS) {  // slots 0..MG_HOT_STATS-1 of every agent live in an array of their own
+    const size_t NA = (size_t)e->b.num_envs * e->b.A;
+    std::vector<float> hot(NA * MG_HOT_STATS);
+    CUDA_TRY(cudaMemcpy(hot.data(), e->b.hot_stats, hot.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    float* out = reinterpret_cast<float*>(host_out);
+    for (size_t a = 0; a < NA; a++) memcpy(out + a * e->b.S, hot.data() + a * MG_HOT_STATS, MG_HOT_STATS * sizeof(float));
+  }
   return MG_OK;
 }
 
@@ -895,6 +903,13 @@ int mg_write(void* h, int32_t what, const void* host_in, int64_t nbytes) {
   if ((size_t)nbytes != bytes) return fail(MG_ERR_ARG, "mg_write: size mismatch, expected " + std::to_string(bytes));
   CUDA_TRY(cudaDeviceSynchronize());
   CUDA_TRY(cudaMemcpy(p, host_in, bytes, cudaMemcpyHostToDevice));
+  if (what == MG_ST_AGENT_STATS) {
+    const size_t NA = (size_t)e->b.num_envs * e->b.A;
+    std::vector<float> hot(NA * MG_HOT_STATS);
+    const float* in = reinterpret_cast<const float*>(host_in);
+    for (size_t a = 0; a < NA; a++) memcpy(hot.data() + a * MG_HOT_STATS, in + a * e->b.S, MG_HOT_STATS * sizeof(float));
+    CUDA_TRY(cudaMemcpy(e->b.hot_stats, hot.data(), hot.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
   return MG_OK;
 }
 

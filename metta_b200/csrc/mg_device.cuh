@@ -26,7 +26,8 @@ struct EnvCtx {
   AsmRec* asms;       // global
   ChestRec* chests;   // global
   float* astats;      // global [A][S]
-  float* hot;         // shared copy of the first MG_HOT_STATS slots of every agent (null: use astats)
+  float* hot;         // shared copy of the first MG_HOT_STATS slots of every agent (null: use hotg)
+  float* hotg;        // global [A][MG_HOT_STATS]: where those slots live in HBM
   float* gstats;      // global [GS]
   int n_asm;
   int clip_enabled, clip_length_scale;
@@ -40,9 +41,8 @@ struct EnvCtx {
 // The per-step counters of an agent (action success/failure, frozen ticks, motion) live in the first
 // MG_HOT_STATS slots; the step kernel stages them in shared memory so that the ordered action pass
 // does not wait on HBM for every agent.
-#define MG_HOT_STATS 16
 MG_DEVICE inline float* agent_stat(const EnvCtx& e, int ai, int slot) {
-  if (slot < MG_HOT_STATS && e.hot != nullptr) return e.hot + ai * MG_HOT_STATS + slot;
+  if (slot < MG_HOT_STATS) return (e.hot != nullptr ? e.hot : e.hotg) + ai * MG_HOT_STATS + slot;
   return e.astats + (size_t)ai * e.S + slot;
 }
 
@@ -899,7 +899,7 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
       v = (float)a->amt[as - MG_AS_AMOUNT];
     } else if (as >= 0) {
       const float* sp = agent_stat(e, ai, as);
-      v = as < MG_HOT_STATS && e.hot != nullptr ? *sp : MG_LDCG(sp);
+      v = as < MG_HOT_STATS ? *sp : MG_LDCG(sp);
     }
     v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LD_L2(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));

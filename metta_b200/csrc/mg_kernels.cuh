@@ -77,6 +77,7 @@ MG_DEVICE inline void init_ctx(EnvCtx& e, const MgBatch& b, int env, AgentRec* a
   e.chests = b.chests + (size_t)env * b.max_chest;
   e.astats = b.agent_stats + (size_t)env * b.A * b.S;
   e.hot = nullptr;
+  e.hotg = b.hot_stats + (size_t)env * b.A * MG_HOT_STATS;
   e.concurrent = false;
   e.batch = &b;
   e.asm_records_on_use = false;
@@ -201,6 +202,7 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   er.clip_rng_idx = MT_N;
   float* astats = b.agent_stats + (size_t)env * b.A * b.S;
   for (int i = lane; i < b.A * b.S; i += 32) astats[i] = 0.0f;
+  for (int i = lane; i < b.A * MG_HOT_STATS; i += 32) b.hot_stats[(size_t)env * b.A * MG_HOT_STATS + i] = 0.0f;
   float* gstats = b.game_stats + (size_t)env * b.GS;
   for (int i = lane; i < b.GS; i += 32) gstats[i] = 0.0f;
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
@@ -349,7 +351,8 @@ MG_DEVICE MG_NOINLINE void accumulate_episode_warp(const MgBatch& b, int env, in
   }
   for (int s = lane; s < b.S; s += 32) {
     double v = 0.0;
-    for (int ai = 0; ai < b.A; ai++) v += (double)astats[(size_t)ai * b.S + s];
+    for (int ai = 0; ai < b.A; ai++)
+      v += (double)(s < MG_HOT_STATS ? b.hot_stats[((size_t)env * b.A + ai) * MG_HOT_STATS + s] : astats[(size_t)ai * b.S + s]);
     if (v != 0.0) atomicAdd(&b.episode_accum[2 + s], v);
   }
   for (int s = lane; s < b.GS; s += 32)
@@ -511,7 +514,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     int32_t act_v[NA];
     uint32_t tc_v[NA];
     const uint4* ag_src = reinterpret_cast<const uint4*>(b.agents + abase);
-    const float* gst = b.agent_stats + abase * b.S;
+    const uint4* hot_src = reinterpret_cast<const uint4*>(b.hot_stats + abase * MG_HOT_STATS);
     uint16_t* tc = b.tok_counts + abase * 2;
     float* gs = b.game_stats + (size_t)env * b.GS;
 #pragma unroll
@@ -519,7 +522,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       const int i = lane + 32 * k;
       if (i < A * 4) {
         ag_v[k] = ag_src[i];
-        hot_v[k] = *reinterpret_cast<const uint4*>(gst + (size_t)(i >> 2) * b.S + (i & 3) * 4);
+        hot_v[k] = hot_src[i];
       }
     }
 #pragma unroll
@@ -872,20 +875,19 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
   __syncwarp();
   MG_SM_TICK(sm, 9);
   {
-    // records and hot stat slots back to HBM, 16 bytes per lane and round (4 chunks per agent each)
+    // records and hot stat slots back to HBM, 16 bytes per lane and round (both arrays are dense per env)
     static_assert(MG_HOT_STATS == 16, "four 16-byte chunks of hot stats per agent, like the record");
     constexpr int NV = MAXA * 4 / 32;
     uint4* dst = reinterpret_cast<uint4*>(b.agents + (size_t)env * A);
     const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
     const uint4* hot = reinterpret_cast<const uint4*>(sm.hot);
-    float* gst = b.agent_stats + (size_t)env * A * b.S + (size_t)(lane >> 2) * b.S + (lane & 3) * 4;  // agent lane/4, chunk lane%4
-    const size_t round_stride = (size_t)8 * b.S;  // 32 lanes = 8 agents further
+    uint4* hot_dst = reinterpret_cast<uint4*>(b.hot_stats + (size_t)env * A * MG_HOT_STATS);
 #pragma unroll
     for (int k = 0; k < NV; k++) {
       const int i = lane + 32 * k;
       if (i < A * 4) {
         dst[i] = src[i];
-        *reinterpret_cast<uint4*>(gst + k * round_stride) = hot[i];
+        hot_dst[i] = hot[i];
       }
     }
   }

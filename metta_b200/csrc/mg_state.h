@@ -28,6 +28,7 @@
 #define MG_GK_ASM 2
 #define MG_GK_CHEST 3
 
+#define MG_HOT_STATS 16 /* agent stat slots 0..15: touched by nearly every action, kept in an array of their own */
 #define MG_GTOK_STRIDE 64
 #define MG_REC_TOKENS 8 /* byte offset of the tokens inside a token record */
 
@@ -142,7 +143,8 @@ struct MgBatch {
   AgentRec* agents;            // [N][A]
   AsmRec* asms;                // [N][max_asm]
   ChestRec* chests;            // [N][max_chest]
-  float* agent_stats;          // [N][A][S]
+  float* agent_stats;          // [N][A][S]; slots below MG_HOT_STATS live in hot_stats instead
+  float* hot_stats;            // [N][A][MG_HOT_STATS]: the per-step counters, dense so that a warp brings its env's in with 16-byte loads
   float* game_stats;           // [N][GS]
   uint32_t* rng;               // [N][624]
   uint32_t* clip_rng;          // [N][624] (only with a clipper)
