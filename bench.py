@@ -3,9 +3,20 @@
     python bench.py --gpus N --steps K --warmup W            # our arm (torchrun for N > 1)
     python bench.py --impl reference --gpus N --steps K ...  # the reference core on the host CPUs
 
-Workload (BASELINE.json configs[1]): arena, 4096 envs x 24 agents per GPU, random actions,
-synthetic maps, 11x11 window, 200 tokens. One step = one simulator step of every env.
-Prints ONE JSON line (rank 0).
+Workload (BASELINE.json configs[1]): arena, 4096 envs x 24 agents per GPU, random actions, the
+reference's own MapGen maps (256 of them, committed as data), 11x11 window, 200 tokens. One step = one
+simulator step of every env.
+
+Steady state: before anything is timed the batch is rolled forward by one whole episode length (10 000
+untimed steps) with every env's first episode cut short at its own offset (EarlyResetHandler), so that
+the envs sit at evenly staggered phases of their episodes, as they would late in a long training run:
+inventories, cooldowns and token counts are those of a running system, and episodes end (auto-reset from
+the map pool inside the step kernel) at a rate of N / max_steps per step inside every timed region. The
+result therefore does not depend on --steps / --warmup.
+
+Prints ONE JSON line (rank 0). `roofline.frac` is the whole step against the HBM roofline by SURVEY.md
+8(d)'s formula (value per GPU x 948 algorithmic bytes / measured copy bandwidth); the two kernels' own
+figures are beside it in `roofline.per_kernel`.
 """
 
 from __future__ import annotations
@@ -29,19 +40,47 @@ AGENTS = 24
 TOKENS = 200
 MAP_POOL = 256
 ALG_BYTES_OBS = 890  # per agent-step, observation kernel: 600 obs + 242 window gather + 48 agent record
-ALG_BYTES_ACT = 58  # action kernel: 4 action + 4 reward + 2 flags + 48 agent record write-back
-# DRAM traffic of one observation-kernel launch over 4096 envs x 24 agents, from the committed ncu capture
-# (profiles/r01k_ncu_full_summary.txt): 68.92 MB read + 23.40 MB written (algorithmic: 87.49 MB)
-NCU_OBS_TRAFFIC_BYTES = 68916736 + 23396352
+ALG_BYTES_ACT = 58  # step kernel: 4 action + 4 reward + 2 flags + 48 agent record write-back
+ALG_BYTES_STEP = ALG_BYTES_OBS + ALG_BYTES_ACT  # 948, SURVEY.md 8(d)
 METRIC = "arena agent-steps/sec"
+PHASE_STRIDE = 6181  # env i's first episode is cut at 1 + (i * PHASE_STRIDE) mod (max_steps - 1): low-discrepancy phases, coprime with 9999
 
 
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the two kernels from the committed ncu capture, with the commit it was taken on."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def cpu_info() -> dict:
+    model, phys, cores_per = "unknown", set(), 0
+    try:
+        pid = None
+        for line in open("/proc/cpuinfo"):
+            k, _, v = line.partition(":")
+            k, v = k.strip(), v.strip()
+            if k == "model name":
+                model = v
+            elif k == "physical id":
+                pid = v
+                phys.add(v)
+            elif k == "cpu cores":
+                cores_per = int(v)
+    except Exception:
+        pass
+    return {"model": model, "sockets": len(phys) or None, "physical_cores": (len(phys) or 1) * cores_per or None,
+            "logical_cpus": os.cpu_count(), "usable_cpus": len(os.sched_getaffinity(0))}
 
 
 class ClockSampler:
@@ -85,60 +124,100 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------ reference / CPU baseline
-def _cpu_worker(args):
-    """Steps `envs` reference (or oracle-port) envs for `steps` steps; returns (agent_steps, seconds)."""
-    kind, envs, steps, seed = args
-    sys.path.insert(0, ROOT)
+def _arena_inputs(n_maps):
     from metta_b200.builders import make_arena
     from metta_b200.lowering import lower_game_config
-    from metta_b200.maps import arena_maps, codes_to_names
+    from metta_b200.maps import arena_mapgen_pool
 
     cfg = make_arena(AGENTS)
     low = lower_game_config(cfg.game, 62, 62)
-    codes = arena_maps(low, envs, seed=seed)
-    if kind == "reference":
-        from oracle.ref_bridge import RefEnv, to_reference_config
+    return cfg, low, arena_mapgen_pool(low, n_maps)
 
-        c_cfg = to_reference_config(cfg.game)
-        sims = [RefEnv(cfg.game, codes_to_names(low, codes[i]), seed + i, c_cfg=c_cfg) for i in range(envs)]
-    else:
+
+def _cpu_worker_loop(conn, kind, envs, first_env, preroll):
+    """One host process: `envs` reference (or oracle-port) arena envs, each rolled forward to its own episode
+    phase first (the same staggering as the GPU arm), then stepped on request. Replies (agent_steps, seconds)."""
+    sys.path.insert(0, ROOT)
+    from metta_b200.maps import codes_to_names
+
+    cfg, low, codes = _arena_inputs(MAP_POOL)
+    max_steps = int(cfg.game.max_steps)
+    rng = np.random.RandomState(1000 + first_env)
+
+    def make(i):
+        g = first_env + i
+        if kind == "reference":
+            from oracle.ref_bridge import RefEnv
+
+            return RefEnv(cfg.game, codes_to_names(low, codes[g % MAP_POOL]), 42 + g, c_cfg=make.c_cfg)
         from oracle.oracle import OracleEnv
 
-        sims = [OracleEnv(low.words, codes[i], seed + i) for i in range(envs)]
-    rng = np.random.RandomState(seed)
-    acts = rng.randint(0, 5, size=(steps, envs, AGENTS)).astype(np.int32)
-    for s in range(min(20, steps)):  # warm-up
+        return OracleEnv(low.words, codes[g % MAP_POOL], 42 + g)
+
+    if kind == "reference":
+        from oracle.ref_bridge import to_reference_config
+
+        make.c_cfg = to_reference_config(cfg.game)
+    sims = [make(i) for i in range(envs)]
+    if preroll:
         for i, sim in enumerate(sims):
-            sim.step(acts[s, i])
-    t0 = time.perf_counter()
-    for s in range(steps):
-        for i, sim in enumerate(sims):
-            sim.step(acts[s, i])
-    dt = time.perf_counter() - t0
-    return envs * AGENTS * steps, dt
+            phase = ((first_env + i) * PHASE_STRIDE) % (max_steps - 1)
+            acts = rng.randint(0, 5, size=(phase, AGENTS)).astype(np.int32)
+            for s in range(phase):
+                sim.step(acts[s])
+    conn.send("ready")
+    while True:
+        steps = conn.recv()
+        if steps is None:
+            break
+        acts = rng.randint(0, 5, size=(steps, envs, AGENTS)).astype(np.int32)
+        t0 = time.perf_counter()
+        for s in range(steps):
+            for i, sim in enumerate(sims):
+                if sim.truncations.all() or sim.terminals.all():  # MettaGridPufferEnv.step: new sim, same seed
+                    sims[i] = sim = make(i)
+                sim.step(acts[s, i])
+        conn.send((envs * AGENTS * steps, time.perf_counter() - t0))
 
 
-def cpu_throughput(procs: int, envs_per_proc: int, steps: int):
-    from oracle import ref_loader
+class CpuArm:
+    """`procs` worker processes that stay alive between samples (envs are built and pre-rolled once)."""
 
-    kind = "reference" if ref_loader.available() else "port"
-    if kind == "port":
-        from oracle import oracle as orc
+    def __init__(self, procs: int, envs_per_proc: int, preroll: bool = True):
+        from oracle import ref_loader
 
-        orc.build()
-    jobs = [(kind, envs_per_proc, steps, 1000 + 17 * p) for p in range(procs)]
-    if procs == 1:
-        res = [_cpu_worker(jobs[0])]
-    else:
-        with mp.get_context("fork").Pool(procs) as pool:
-            res = pool.map(_cpu_worker, jobs)
-    total = sum(r[0] for r in res)
-    slowest = max(r[1] for r in res)
-    return total / slowest, kind, slowest
+        self.kind = "reference" if ref_loader.available() else "port"
+        if self.kind == "port":
+            from oracle import oracle as orc
+
+            orc.build()
+        ctx = mp.get_context("fork")
+        self.workers = []
+        for p in range(procs):
+            parent, child = ctx.Pipe()
+            pr = ctx.Process(target=_cpu_worker_loop, args=(child, self.kind, envs_per_proc, p * envs_per_proc, preroll), daemon=True)
+            pr.start()
+            self.workers.append((pr, parent))
+        for _, c in self.workers:
+            assert c.recv() == "ready"
+
+    def sample(self, steps: int):
+        for _, c in self.workers:
+            c.send(steps)
+        res = [c.recv() for _, c in self.workers]
+        slowest = max(r[1] for r in res)
+        return sum(r[0] for r in res) / slowest, slowest
+
+    def close(self):
+        for pr, c in self.workers:
+            c.send(None)
+        for pr, _ in self.workers:
+            pr.join(timeout=5)
 
 
 def workload_name(n_envs, agents, tokens):
-    return f"arena, {n_envs} envs x {agents} agents per GPU, random actions, 62x62 synthetic maps, 11x11 window, {tokens} tokens"
+    return (f"arena, {n_envs} envs x {agents} agents per GPU, random actions, 62x62 maps from the reference's MapGen, "
+            f"11x11 window, {tokens} tokens, envs at staggered episode phases (max_steps 10000)")
 
 
 def run_reference(args):
@@ -147,22 +226,25 @@ def run_reference(args):
         return
     cores = len(os.sched_getaffinity(0))
     envs_per_proc, steps_per_sample = 4, 100
-    times, units, kind = [], 0.0, "port"
+    arm = CpuArm(cores, envs_per_proc)
+    times, units = [], 0.0
     for _ in range(args.warmup):
-        cpu_throughput(cores, envs_per_proc, 50)
+        arm.sample(50)
     for _ in range(args.steps):
-        v, kind, secs = cpu_throughput(cores, envs_per_proc, steps_per_sample)
+        v, secs = arm.sample(steps_per_sample)
         times.append(secs)
         units += v * secs
+    arm.close()
     value = units / float(np.sum(times))
     sample = (f"each bench step = {cores} processes x {envs_per_proc} arena envs x {steps_per_sample} env steps of the reference's "
-              f"C++ core ({kind}) on the host cores, a bounded sample of the {args.envs}-env workload")
+              f"C++ core ({arm.kind}) on the host cores, envs pre-rolled to staggered episode phases; a bounded sample of the "
+              f"{args.envs}-env workload")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * float(np.mean(times)), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": workload_name(args.envs, AGENTS, 200), "envs_per_gpu": args.envs, "agents_per_env": AGENTS, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": cores, "kind": kind, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": cores, "kind": arm.kind, "sample": sample, "cpu": cpu_info()},
         "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -170,14 +252,171 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------ our arm
+class Rig:
+    """One batch of envs with torch-owned buffers, a ring of pre-generated actions and an L2 flush."""
+
+    def __init__(self, torch, low, pool, n_envs, agents, tokens, n_actions, dev, seeds, maps, gen_seed, flush_mode="write+read"):
+        from metta_b200.batch import Batch
+
+        self.torch, self.dev, self.N, self.A, self.T = torch, dev, n_envs, agents, tokens
+        self.batch = Batch(low, pool, n_envs, device=dev.index)
+        NA = n_envs * agents
+        self.obs = torch.full((NA, tokens, 3), 255, dtype=torch.uint8, device=dev)
+        self.term = torch.zeros(NA, dtype=torch.uint8, device=dev)
+        self.trunc = torch.zeros(NA, dtype=torch.uint8, device=dev)
+        self.rew = torch.zeros(NA, dtype=torch.float32, device=dev)
+        g = torch.Generator().manual_seed(gen_seed)
+        self.ring = 16
+        self.act_ring = torch.randint(0, n_actions, (self.ring, NA), generator=g, dtype=torch.int32).to(dev)
+        self.act = self.act_ring[0].clone()  # the bound action buffer, refreshed from the ring every step (device copy)
+        self.batch.set_buffers(self.obs.data_ptr(), self.term.data_ptr(), self.trunc.data_ptr(), self.rew.data_ptr(), self.act.data_ptr())
+        self.batch.reset(seeds, maps)
+        self.stream = torch.cuda.current_stream(dev).cuda_stream
+        self.flush_mode = flush_mode
+        self.i = 0
+
+    def one_step(self):
+        self.act.copy_(self.act_ring[self.i % self.ring], non_blocking=True)  # what a policy's sampling kernel would write
+        self.batch.step(self.stream)
+        self.i += 1
+
+    def stagger(self, max_steps: int, first_global_env: int):
+        """Cut every env's first episode at its own offset and roll the batch forward by one episode length."""
+        g = first_global_env + np.arange(self.N, dtype=np.int64)
+        self.batch.set_early_reset((1 + (g * PHASE_STRIDE) % (max_steps - 1)).astype(np.uint32))
+        for _ in range(max_steps):
+            self.one_step()
+        self.torch.cuda.synchronize()
+
+    def timed_steps(self, k: int, flush) -> list:
+        torch = self.torch
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(k)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(k)]
+        torch.cuda.synchronize()
+        for i in range(k):
+            flush(i)
+            starts[i].record()
+            self.one_step()
+            ends[i].record()
+        torch.cuda.synchronize()
+        return [s.elapsed_time(e) for s, e in zip(starts, ends)]
+
+    def close(self):
+        self.batch.close()
+
+
+def make_flush(torch, dev, mode):
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB of L2
+    flush_rd = torch.zeros(64 * 1024 * 1024, dtype=torch.int32, device=dev)  # 256 MiB, only ever read
+
+    def flush_l2(i):
+        # write a buffer larger than L2, then stream another one through: the write evicts everything the
+        # simulator touched, the read pushes the dirty lines of the write out to HBM so that the timed step
+        # does not pay for writing back the flush itself
+        flush.fill_(i & 0xFF)
+        if mode == "write+read":
+            flush_rd.sum()
+
+    return flush_l2
+
+
+def other_configs(torch, dist, dev, rank, world, flush, peak):
+    """Short runs of BASELINE.json configs[2..4]: value, ms per step, whole-step roofline."""
+    from metta_b200.builders import make_navigation
+    from metta_b200.lowering import lower_game_config
+    from metta_b200.maps import build_pool, names_to_codes, random_maps
+
+    out = {}
+
+    def measure(name, rig, steps, note):
+        for _ in range(10):
+            rig.one_step()
+        ms = rig.timed_steps(steps, flush)
+        t = torch.tensor([float(sum(ms))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        units = world * rig.N * rig.A * steps
+        v = units / (float(t) / 1000.0)
+        out[name] = {"value": v, "unit": "agent-steps/s", "ms_per_step": float(t) / steps, "steps": steps,
+                     "frac": v / world * ALG_BYTES_STEP / 1e9 / peak, "episodes_finished": float(rig.batch.read_episode_accum()[0]),
+                     "workload": note}
+        rig.close()
+
+    # C3: navigation / object-use maps with auto-reset, 16384 envs in total, sharded over the ranks
+    n3 = 16384 // world
+    cfg = make_navigation(num_agents=4, max_steps=100)
+    cfg.game.episode_truncates = True
+    low = lower_game_config(cfg.game, 40, 40)
+    codes = random_maps(low, 64, 40, 40, {"wall": 120, "assembler": 24, "agent.agent": 4}, seed=3)
+    g0 = rank * n3
+    rig = Rig(torch, low, build_pool(low, codes), n3, 4, int(cfg.game.obs.num_tokens), len(low.action_names), dev,
+              ((np.arange(n3) + g0 + 7) & 0xFFFFFFFF).astype(np.uint32), ((np.arange(n3) + g0) % 64).astype(np.int32), 100 + rank)
+    rig.batch.set_options(auto_reset=True, map_stride=5)
+    rig.stagger(100, g0)
+    measure("navigation_16k", rig, 60, f"configs[2]: navigation/object-use, 40x40 maps (walls, heart assemblers), 4 agents, episodes of 100 steps "
+            f"with auto-reset from a 64-map pool, 16384 envs over {world} GPU(s)")
+    # C4: a cogames mission, 8192 envs per GPU (the reference's own config and map, from the golden fixture)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from golden_util import load
+
+    cfg, grid, _ = load("cogames_vibe_check")
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    n4, A4 = 8192, cfg.game.num_agents
+    rig = Rig(torch, low, build_pool(low, names_to_codes(low, grid)[None]), n4, A4, int(cfg.game.obs.num_tokens), len(low.action_names), dev,
+              ((np.arange(n4) + rank * n4 + 11) & 0xFFFFFFFF).astype(np.uint32), np.zeros(n4, np.int32), 200 + rank)
+    for _ in range(150):
+        rig.one_step()
+    measure("cogames_8k_per_gpu", rig, 60, f"configs[3]: cogames VibeCheckMission ({len(low.action_names)} actions uniform, vibe-keyed assemblers, "
+            f"chests, chargers, regen), {A4} cogs, 8192 envs per GPU, steps 160+ of the episode")
+    return out
+
+
+def rollout_config(torch, dist, dev, rank, world, peak):
+    """configs[4]: env + torch policy in one loop on the device, observations read where the kernel wrote them."""
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    from rollout import run_rollout
+
+    r = run_rollout(envs=ENVS_PER_GPU, steps=100, warmup=20, shim="both", quiet=True)
+    v = r["agent_steps_per_s"]
+    return {"value": v, "unit": "agent-steps/s", "ms_per_step": r["ms_per_step"], "steps": 100, "frac": v / world * ALG_BYTES_STEP / 1e9 / peak,
+            "ms_per_step_by_shim": r["ms_per_step_by_shim"],
+            "workload": f"configs[4]: arena rollout loop, {ENVS_PER_GPU} envs x 24 agents per GPU with a bag-of-tokens MLP policy and categorical "
+                        f"sampling in the loop, policy input truncated to the kernel's max_flip (mg_set_obs_aux)"}
+
+
+def host_link_ceiling(torch, dist, dev, world):
+    """Plain pinned cudaMemcpyAsync device->host of 10 MB and 60 MB (the sizes of a changed-rows and a full
+    export), all ranks at once: what the box's host link gives this rank while its neighbours use it too."""
+    out = {}
+    for mb in (10, 60):
+        d = torch.empty(mb * 1000 * 1000, dtype=torch.uint8, device=dev)
+        h = torch.empty(mb * 1000 * 1000, dtype=torch.uint8, pin_memory=True)
+        for _ in range(2):
+            h.copy_(d, non_blocking=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            h.copy_(d, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        gbs = torch.tensor([10 * mb / e0.elapsed_time(e1)], dtype=torch.float64, device=dev)  # MB/ms = GB/s
+        lo = gbs.clone()
+        if world > 1:
+            dist.all_reduce(gbs, op=dist.ReduceOp.SUM)
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        out[f"d2h_{mb}MB_gbs_all_ranks"] = float(gbs)
+        out[f"d2h_{mb}MB_gbs_slowest_rank"] = float(lo)
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
-    from metta_b200.batch import Batch
-    from metta_b200.builders import make_arena
-    from metta_b200.lowering import lower_game_config
-    from metta_b200.maps import arena_maps, build_pool
+    from metta_b200.maps import build_pool
     from metta_b200.sharding import reduce_episode_accumulators, shard_maps, shard_seeds
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -197,42 +436,24 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
 
     N, A, T = args.envs, AGENTS, TOKENS
-    cfg = make_arena(A)
-    low = lower_game_config(cfg.game, 62, 62)
-    # env shards are independent: maps and seeds derive from the GLOBAL env index
-    codes = arena_maps(low, MAP_POOL, seed=1234)
+    cfg, low, codes = _arena_inputs(MAP_POOL)
+    max_steps = int(cfg.game.max_steps)
     pool = build_pool(low, codes)
-    batch = Batch(low, pool, N, device=local)
-    obs = torch.full((N * A, T, 3), 255, dtype=torch.uint8, device=dev)
-    term = torch.zeros(N * A, dtype=torch.uint8, device=dev)
-    trunc = torch.zeros(N * A, dtype=torch.uint8, device=dev)
-    rew = torch.zeros(N * A, dtype=torch.float32, device=dev)
-    g = torch.Generator().manual_seed(rank)
-    ring = 16
-    act_ring = torch.randint(0, 5, (ring, N * A), generator=g, dtype=torch.int32).to(dev)
-    act = act_ring[0].clone()  # the bound action buffer; every step starts by refreshing it from the ring (device copy)
-    batch.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act.data_ptr())
+    # env shards are independent: maps, seeds and episode phases derive from the GLOBAL env index
     seeds = shard_seeds(rank, world, N, 42)
     maps = shard_maps(rank, world, N, MAP_POOL)
-    batch.reset(seeds, maps)
-    stream = torch.cuda.current_stream(dev).cuda_stream
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB of L2
-    flush_rd = torch.zeros(64 * 1024 * 1024, dtype=torch.int32, device=dev)  # 256 MiB, only ever read
+    rig = Rig(torch, low, pool, N, A, T, 5, dev, seeds, maps, rank, args.flush)
+    batch = rig.batch
+    flush_l2 = make_flush(torch, dev, args.flush)
+    t_pre = time.perf_counter()
+    if not args.no_stagger:
+        rig.stagger(max_steps, rank * N)
+    preroll_s = time.perf_counter() - t_pre
+    steps_now = batch.read_env()["current_step"].astype(np.int64)
+    episodes_before = float(batch.read_episode_accum()[0])
 
-    def flush_l2(i):
-        # write a buffer larger than L2, then stream another one through: the write evicts everything
-        # the simulator touched, the read pushes the dirty lines of the write out to HBM so that the
-        # timed step does not pay for writing back the flush itself
-        flush.fill_(i & 0xFF)
-        if args.flush == "write+read":
-            flush_rd.sum()
-
-    def one_step(i):
-        act.copy_(act_ring[i % ring], non_blocking=True)  # what a policy's sampling kernel would write
-        batch.step(stream)
-
-    for i in range(args.warmup):
-        one_step(i)
+    for _ in range(args.warmup):
+        rig.one_step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -241,114 +462,138 @@ def run_ours(args):
         sampler.start()
     launches0 = batch.kernel_launches
     # ---- timed region 1: K steps, L2 flushed between steps, CUDA events around each step
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    torch.cuda.synchronize()
-    for i in range(args.steps):
-        flush_l2(i)
-        starts[i].record()
-        one_step(args.warmup + i)
-        ends[i].record()
-    torch.cuda.synchronize()
-    step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+    step_ms = rig.timed_steps(args.steps, flush_l2)
     total_ms = float(sum(step_ms))
     launches = batch.kernel_launches - launches0
+    episodes_timed = float(batch.read_episode_accum()[0]) - episodes_before
     # ---- free-running: K steps back to back (warm L2, launch gaps included)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(args.steps):
-        one_step(i)
+    for _ in range(args.steps):
+        rig.one_step()
     e1.record()
     torch.cuda.synchronize()
     free_ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
-    # ---- per-kernel durations for the roofline (events on the launch stream, L2 flushed)
+    # ---- per-kernel durations (whole batch in one launch each, events on the launch stream, L2 flushed)
     act_ms, obs_ms = [], []
     for i in range(min(args.steps, 50)):
-        act.copy_(act_ring[i % ring])
+        rig.act.copy_(rig.act_ring[i % rig.ring])
         flush_l2(i)
         torch.cuda.synchronize()
-        a_ms, o_ms = batch.profile_step(stream)
+        a_ms, o_ms = batch.profile_step(rig.stream)
         act_ms.append(a_ms); obs_ms.append(o_ms)
-    # ---- end to end through the host-buffer call: pinned H2D of actions, D2H of everything
-    hb = Batch(low, pool, N, device=local)
-    hb.use_internal_buffers()
-    hb.reset(seeds, maps)
-    # page-locked host buffers (what a host-side rollout worker would hold): the copy engines read/write them directly
+    # ---- end to end through the host-buffer call on the same (staggered) batch: page-locked H2D of the actions,
+    # the step, D2H of everything a rollout worker reads
     pin = lambda shape, dtype: torch.empty(shape, dtype=dtype, pin_memory=True).numpy()  # noqa: E731
-    h_act = pin((ring, N * A), torch.int32)
-    h_act[...] = np.random.RandomState(rank).randint(0, 5, size=(ring, N * A))
+    h_act = pin((rig.ring, N * A), torch.int32)
+    h_act[...] = np.random.RandomState(rank).randint(0, 5, size=(rig.ring, N * A))
     h_obs = pin((N * A, T, 3), torch.uint8); h_rew = pin((N * A,), torch.float32)
     h_term = pin((N * A,), torch.uint8); h_trunc = pin((N * A,), torch.uint8)
     e2e_steps = max(3, min(args.steps, 30))
 
     def e2e_run(changed_rows_only):
-        hb.set_host_export(changed_rows_only)
+        batch.set_host_export(changed_rows_only)
         for i in range(3):
-            hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
+            batch.step_host(h_act[i % rig.ring], h_obs, h_rew, h_term, h_trunc)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        b0 = hb.transfer_bytes()
+        b0 = batch.transfer_bytes()
         t0 = time.perf_counter()
         for i in range(e2e_steps):
-            hb.step_host(h_act[i % ring], h_obs, h_rew, h_term, h_trunc)
+            batch.step_host(h_act[i % rig.ring], h_obs, h_rew, h_term, h_trunc)
         torch.cuda.synchronize()
         secs = time.perf_counter() - t0
-        b1 = hb.transfer_bytes()
+        b1 = batch.transfer_bytes()
         return secs, (b1[0] - b0[0]) / e2e_steps, (b1[1] - b0[1]) / e2e_steps
 
-    e2e_full_s, _, full_d2h = e2e_run(False)   # every observation byte crosses the host link
+    e2e_full_s, _, full_d2h = e2e_run(False)   # every observation byte crosses the host link (mg_set_host_export 0)
     e2e_s, e2e_h2d, e2e_d2h = e2e_run(True)    # only the part of each row that changed (mg_set_host_export 1)
     # the export must leave the host buffer identical to the device observations
-    if not np.array_equal(h_obs, hb.read_obs().reshape(h_obs.shape)):
+    if not np.array_equal(h_obs, batch.read_obs().reshape(h_obs.shape)):
         raise SystemExit("bench: host observation buffer differs from the device buffer after the changed-rows export")
+    link = host_link_ceiling(torch, dist, dev, world)
     # ---- the only collective of the env path: episode stats (a few KB) over NCCL
     acc = torch.from_numpy(batch.read_episode_accum()).to(dev)
     t = torch.tensor([total_ms, free_ms, e2e_s, e2e_full_s], dtype=torch.float64, device=dev)
+    per_rank = torch.zeros(world, dtype=torch.float64, device=dev)
+    per_rank[rank] = total_ms / args.steps
+    ep = torch.tensor([episodes_timed], dtype=torch.float64, device=dev)
     reduce_episode_accumulators(acc)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(per_rank, op=dist.ReduceOp.SUM)
+        dist.all_reduce(ep, op=dist.ReduceOp.SUM)
     total_ms, free_ms, e2e_s, e2e_full_s = (float(x) for x in t.cpu())
+    peak, peak_kind = peaks()
+    rig.close()
+    others = None
+    if not args.no_other_configs:
+        others = other_configs(torch, dist, dev, rank, world, flush_l2, peak)
+        others["rollout_arena"] = rollout_config(torch, dist, dev, rank, world, peak)
     if rank == 0:
         units = world * N * A * args.steps
         value = units / (total_ms / 1000.0)
-        peak, peak_kind = peaks()
         obs_mean_ms = float(np.mean(obs_ms)); act_mean_ms = float(np.mean(act_ms))
-        achieved = ALG_BYTES_OBS * N * A / (obs_mean_ms / 1000.0) / 1e9
+        achieved = value / world * ALG_BYTES_STEP / 1e9
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, kind, secs = cpu_throughput(1, 16, 9000)
-            cpu = {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": kind,
-                   "sample": f"16 arena envs x 24 agents x 9000 steps on one host core ({secs:.1f} s)"}
+            arm = CpuArm(1, 8)
+            arm.sample(100)
+            v, secs = arm.sample(12000)
+            arm.close()
+            cpu = {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": arm.kind, "cpu": cpu_info(),
+                   "sample": f"8 arena envs x 24 agents x 12000 steps on one host core, envs pre-rolled to staggered episode phases ({secs:.1f} s)"}
+        traffic = ncu_traffic() if N == ENVS_PER_GPU else None
+        e2e_value = world * N * A * e2e_steps / e2e_s
+        e2e_full_value = world * N * A * e2e_steps / e2e_full_s
+        d2h_rate = e2e_d2h * e2e_steps / e2e_s / 1e9  # GB/s this rank moved in changed-rows mode
+        full_rate = full_d2h * e2e_steps / e2e_full_s / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
             "config": {"workload": workload_name(N, A, T),
                        "envs_per_gpu": N, "agents_per_env": A, "l2": "flushed between timed steps (256 MiB fill" + (", then 256 MiB streamed read)" if args.flush == "write+read" else ")"),
-                       "parallelism": f"env shards x{world}, no data-path collective"},
+                       "parallelism": f"env shards x{world}, no data-path collective",
+                       "steady_state": {"preroll_steps": 0 if args.no_stagger else max_steps, "preroll_s": preroll_s,
+                                        "episode_step_min": int(steps_now.min()), "episode_step_median": int(np.median(steps_now)),
+                                        "episode_step_max": int(steps_now.max())}},
             "clocks": clocks,
-            "e2e": {"value": world * N * A * e2e_steps / e2e_s, "unit": "agent-steps/s",
+            "per_rank_ms": [float(x) for x in per_rank.cpu()],
+            "step_ms": {"min": float(np.min(step_ms)), "median": float(np.median(step_ms)), "p90": float(np.percentile(step_ms, 90)), "max": float(np.max(step_ms))},
+            "e2e": {"value": e2e_value, "unit": "agent-steps/s",
                     "h2d_bytes_per_step": int(e2e_h2d), "d2h_bytes_per_step": int(e2e_d2h),
-                    "host_export": "page-locked caller buffers; observations: changed row prefixes written by a kernel (mg_set_host_export 1), "
-                                   "host buffer checked equal to the device buffer after the run",
-                    "full_rows": {"value": world * N * A * e2e_steps / e2e_full_s, "d2h_bytes_per_step": int(full_d2h),
-                                  "note": "same call with every observation byte copied (mg_set_host_export 0)"}},
+                    "mode": "changed_rows: mg_step_host with page-locked caller buffers and mg_set_host_export 1 (what GpuMettaGridVecEnv(host=True) "
+                            "uses): observations as changed row pieces written by a kernel; host buffer checked equal to the device buffer after the run",
+                    "modes": {"changed_rows": {"value": e2e_value, "d2h_bytes_per_step": int(e2e_d2h), "d2h_gbs_per_rank": d2h_rate},
+                              "full_rows": {"value": e2e_full_value, "d2h_bytes_per_step": int(full_d2h), "d2h_gbs_per_rank": full_rate,
+                                            "note": "same call with every observation byte copied (mg_set_host_export 0, the C-ABI default)"}},
+                    "host_link": link,
+                    "host_link_frac": {"changed_rows": d2h_rate * world / link["d2h_10MB_gbs_all_ranks"], "full_rows": full_rate * world / link["d2h_60MB_gbs_all_ranks"]}},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "mg_obs_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": NCU_OBS_TRAFFIC_BYTES if N == ENVS_PER_GPU else None,
-                         "traffic_source": "profiles/r01k_ncu_full_summary.txt (ncu --set full, one launch over 4096 envs: dram__bytes_read.sum + dram__bytes_write.sum)",
-                         "peak_source": peak_kind,
-                         "kernel_ms": obs_mean_ms, "alg_bytes_per_launch": ALG_BYTES_OBS * N * A,
-                         "step_kernel_ms": act_mean_ms, "whole_step_frac": (ALG_BYTES_OBS + ALG_BYTES_ACT) * N * A / ((obs_mean_ms + act_mean_ms) / 1000.0) / 1e9 / peak},
+            "roofline": {"bound": "hbm", "kernel": "whole step: mg_step_kernel + mg_obs_kernel in overlapped slices", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "alg_bytes_per_agent_step": ALG_BYTES_STEP,
+                         "formula": "value per GPU x 948 B / peak (SURVEY.md 8d)", "peak_source": peak_kind,
+                         "traffic": (traffic or {}).get("whole_step_bytes"), "traffic_source": (traffic or {}).get("source"),
+                         "per_kernel": {
+                             "mg_step_kernel": {"ms": act_mean_ms, "alg_bytes_per_launch": ALG_BYTES_ACT * N * A,
+                                                "achieved": ALG_BYTES_ACT * N * A / (act_mean_ms / 1000.0) / 1e9,
+                                                "frac": ALG_BYTES_ACT * N * A / (act_mean_ms / 1000.0) / 1e9 / peak,
+                                                "traffic": (traffic or {}).get("mg_step_kernel_bytes")},
+                             "mg_obs_kernel": {"ms": obs_mean_ms, "alg_bytes_per_launch": ALG_BYTES_OBS * N * A,
+                                               "achieved": ALG_BYTES_OBS * N * A / (obs_mean_ms / 1000.0) / 1e9,
+                                               "frac": ALG_BYTES_OBS * N * A / (obs_mean_ms / 1000.0) / 1e9 / peak,
+                                               "traffic": (traffic or {}).get("mg_obs_kernel_bytes")},
+                             "note": "each kernel alone over the whole batch (mg_profile_step), L2 flushed; inside a step they run as slices that overlap"}},
             "free_running": {"value": world * N * A * args.steps / (free_ms / 1000.0), "unit": "agent-steps/s", "l2": "warm"},
             "cpu_baseline": cpu,
-            "episodes_finished": float(acc[0]),
+            "episodes_finished": float(ep),
+            "episodes_finished_since_start": float(acc[0]),
+            "other_configs": others,
         }
         print(json.dumps(line))
-    hb.close()
-    batch.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -361,6 +606,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--no-stagger", action="store_true", help="skip the pre-roll: time the first steps of fresh episodes (tuning only)")
     ap.add_argument("--flush", default="write+read", choices=["write", "write+read"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -82,6 +82,15 @@ int mg_profile_step(void* handle, void* cuda_stream, float* out_ms_host);
 /* MettaGrid::_compute_observations (mettagrid_c.cpp:557-563) alone. */
 int mg_compute_observations(void* handle, void* cuda_stream);
 
+/* What the policy's first op computes from the observations, handed over by the observation pass instead
+ * (replaces the per-batch `coords == 255 -> argmax -> any -> max` of ObsShimTokens.forward,
+ * agent/src/metta/agent/components/obs_shim.py:181-196). All three are optional caller-owned DEVICE
+ * buffers (NULL = not produced), filled by every observation pass from then on:
+ *   row_lengths i32[N*A]   tokens in the row = index of the first 0xFF location byte (T if the row is full)
+ *   max_flip    i32[1]     max of row_lengths over all rows (after a masked mg_reset: an upper bound)
+ *   obs_mask    u8[N*A][T] 1 where the slot is padding: the shim's `obs_mask`; slice [:, :max_flip]. */
+int mg_set_obs_aux(void* handle, void* row_lengths_dev, void* max_flip_dev, void* obs_mask_dev);
+
 /* auto_reset: 1 = MettaGridPufferEnv semantics (default), 0 = bare MettaGrid. map_stride: which pool
  * map an env moves to on auto-reset ((index + stride) mod pool size). */
 int mg_set_options(void* handle, int32_t auto_reset, int32_t map_stride);
@@ -115,7 +124,11 @@ int mg_set_inventory(void* handle, int32_t env, int32_t agent, const int32_t* it
  * error; every call on a GPU shares that array, which keeps the last call's contents (nothing in it
  * needs clearing), so calls that overlap on the GPU race and must be serialised by the caller; the
  * first call on each device looks up the array's device address (cudaGetSymbolAddress) and should
- * be made before any stream capture begins. Asynchronous on `cuda_stream`. */
+ * be made before any stream capture begins. Asynchronous on `cuda_stream`.
+ * Ordering is the caller's job: the peek reads grid, agent and token records, so it has to run after
+ * the preceding mg_step has finished and before the next one starts (same stream, or an event between
+ * the two); on an unordered stream it would see a half-stepped state. Host calls on one handle must not
+ * overlap either (the handle is not thread-safe); the peek itself writes nothing into the handle. */
 int mg_peek_observations_noalloc(void* handle, void* obs_out_dev, void* cuda_stream);
 
 int64_t mg_kernel_launches(void* handle); /* kernels launched through this handle so far */

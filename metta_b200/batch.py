@@ -134,6 +134,11 @@ class Batch:
     def use_internal_buffers(self) -> None:
         self._check(self._c.mg_set_buffers(self._h, None, None, None, None, None))
 
+    def set_obs_aux(self, row_lengths: int = 0, max_flip: int = 0, obs_mask: int = 0) -> None:
+        """Device addresses (0 = off) of i32[N*A] row lengths, an i32 maximum of them and a u8[N*A][T] padding
+        mask that every observation pass fills: what ObsShimTokens.forward recomputes per batch."""
+        self._check(self._c.mg_set_obs_aux(self._h, row_lengths or None, max_flip or None, obs_mask or None))
+
     def reset(self, seeds, map_idx, mask=None) -> None:
         seeds = np.ascontiguousarray(seeds, dtype=np.uint32)
         map_idx = np.ascontiguousarray(map_idx, dtype=np.int32)

@@ -78,7 +78,13 @@ struct MgEnvs {
   cudaGraph_t graph;
   cudaGraphExec_t graph_exec;
   uint8_t* d_mask;
+  uint32_t* d_seeds;   // mg_reset: seeds and map indices of the envs being reset (patched into EnvRec on the device)
+  int32_t* d_map_idx;
   int32_t* d_tmp;  // small scratch for set_inventory
+  // library-owned caller buffers (mg_set_buffers with all NULLs), kept so that a later all-NULL call rebinds them
+  uint8_t *own_obs, *own_term, *own_trunc;
+  float* own_rew;
+  int32_t* own_act;
   // mg_step_host with page-locked buffers, export mode 1: only the part of each row that changed
   int host_export_mode;
   const void* host_obs_last;      // the host buffer whose contents d_prev_counts describes (nullptr = none)
@@ -105,6 +111,16 @@ static int dev_alloc(MgEnvs* e, T** out, size_t count, bool zero = true) {
   if (zero) CUDA_TRY(cudaMemset(p, 0, bytes));
   e->allocs.push_back(p);
   *out = reinterpret_cast<T*>(p);
+  return MG_OK;
+}
+
+// Queue mode only: did an observation CTA give up waiting for the step kernel? (checked after a sync)
+static int check_queue_error(MgEnvs* e, const char* who) {
+  if (e->step_mode != 1 || e->b.qctl == nullptr) return MG_OK;
+  MgQueueCtl ctl;
+  CUDA_TRY(cudaMemcpy(&ctl, e->b.qctl, sizeof(ctl), cudaMemcpyDeviceToHost));
+  if (ctl.error != 0)
+    return fail(MG_ERR_CUDA, std::string(who) + ": an observation CTA gave up waiting for the step kernel (queue mode); results are incomplete");
   return MG_OK;
 }
 
@@ -322,6 +338,8 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &b.action_success, N * A));
   TRY(dev_alloc(e, &b.episode_accum, (size_t)(2 + b.S + b.GS)));
   TRY(dev_alloc(e, &e->d_mask, N));
+  TRY(dev_alloc(e, &e->d_seeds, N));
+  TRY(dev_alloc(e, &e->d_map_idx, N));
   TRY(dev_alloc(e, &e->d_tmp, (size_t)4 * MG_RES_STRIDE));
   CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   TRY(dev_alloc(e, &e->d_prev_counts, N * A));
@@ -433,17 +451,17 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
   MgBatch& b = e->b;
   const size_t NA = (size_t)b.num_envs * b.A;
   if (!obs && !terminals && !truncations && !rewards && !actions) {
-    if (!e->owns_buffers) {
+    if (!e->owns_buffers) {  // allocated once; every later all-NULL call binds the same buffers again
       int rc;
-      int32_t* act;
-      TRY(dev_alloc(e, &b.obs, NA * b.T * 3 + 16));
-      TRY(dev_alloc(e, &b.terminals, NA));
-      TRY(dev_alloc(e, &b.truncations, NA));
-      TRY(dev_alloc(e, &b.rewards, NA));
-      TRY(dev_alloc(e, &act, NA));
-      b.actions = act;
+      TRY(dev_alloc(e, &e->own_obs, NA * b.T * 3 + 16));
+      TRY(dev_alloc(e, &e->own_term, NA));
+      TRY(dev_alloc(e, &e->own_trunc, NA));
+      TRY(dev_alloc(e, &e->own_rew, NA));
+      TRY(dev_alloc(e, &e->own_act, NA));
       e->owns_buffers = true;
     }
+    b.obs = e->own_obs; b.terminals = e->own_term; b.truncations = e->own_trunc;
+    b.rewards = e->own_rew; b.actions = e->own_act;
   } else {
     if (!obs || !terminals || !truncations || !rewards || !actions)
       return fail(MG_ERR_ARG, "mg_set_buffers: all five buffers are required");
@@ -455,7 +473,7 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
   return MG_OK;
 }
 
-static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask) {
+static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask, bool count = true) {
   const dim3 grid((unsigned)(b.env_end - b.env_begin), (unsigned)((b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
   const int slot = (b.T * 3 + 16 + 15) & ~15;
   const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
@@ -465,12 +483,25 @@ static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const u
   else if (cpl_t == 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   else if (cpl_t == 4) { MG_LAUNCH(mg_obs_kernel<4>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   else { MG_LAUNCH(mg_obs_kernel<8>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
-  e->launches++;
+  if (count) e->launches++;
   CUDA_TRY(cudaGetLastError());
   return MG_OK;
 }
 
-static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) { return launch_obs_slice(e, e->b, s, mask); }
+// The running maximum of the row lengths starts at zero for every full observation pass (a masked pass
+// keeps the old value: it stays an upper bound).
+static int begin_obs_pass(MgEnvs* e, cudaStream_t s) {
+  if (e->b.max_flip != nullptr) CUDA_TRY(cudaMemsetAsync(e->b.max_flip, 0, sizeof(int32_t), s));
+  return MG_OK;
+}
+
+static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
+  if (mask == nullptr) {
+    const int rc = begin_obs_pass(e, s);
+    if (rc != MG_OK) return rc;
+  }
+  return launch_obs_slice(e, e->b, s, mask);
+}
 
 static int launch_step_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
   const int grid = (b.env_end - b.env_begin + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
@@ -507,6 +538,7 @@ static int launch_export(MgEnvs* e, const MgBatch& b, cudaStream_t s, const MgHo
 static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* ht = nullptr) {
   const int n = e->b.num_envs, per = (n + e->chunks - 1) / e->chunks;
   int rc;
+  if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
   CUDA_TRY(cudaEventRecord(e->ev_fork, s));
   for (int c = 0; c < e->chunks; c++) {
     MgBatch slice = e->b;
@@ -545,6 +577,7 @@ static int launch_obs_queue(MgEnvs* e, const MgBatch& b, cudaStream_t s, int cta
 static int enqueue_queue_step(MgEnvs* e, cudaStream_t s) {
   const MgBatch& b = e->b;
   int rc;
+  if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
   MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
@@ -578,23 +611,23 @@ int mg_reset(void* h, const uint32_t* seeds, const int32_t* map_idx, const uint8
   CUDA_TRY(cudaSetDevice(e->device));
   MgBatch& b = e->b;
   const size_t N = (size_t)b.num_envs;
-  std::vector<EnvRec> recs(N);
-  CUDA_TRY(cudaMemcpy(recs.data(), b.env, N * sizeof(EnvRec), cudaMemcpyDeviceToHost));
   for (size_t i = 0; i < N; i++) {
     if (mask && !mask[i]) continue;
     if (map_idx[i] < 0 || map_idx[i] >= b.num_maps) return fail(MG_ERR_ARG, "mg_reset: map index out of range");
-    recs[i].seed = seeds[i];
-    recs[i].map_idx = map_idx[i];
-    recs[i].early_reset_step = 0;
   }
-  CUDA_TRY(cudaMemcpy(b.env, recs.data(), N * sizeof(EnvRec), cudaMemcpyHostToDevice));
+  // A step may still be in flight on a non-blocking stream (mg_step is asynchronous): wait for it, then
+  // hand seeds and map indices to the reset kernel, which patches the records of the envs it resets on the
+  // device. Records of unmasked envs are never rewritten from the host.
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaMemcpy(e->d_seeds, seeds, N * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(e->d_map_idx, map_idx, N * sizeof(int32_t), cudaMemcpyHostToDevice));
   const uint8_t* d_mask = nullptr;
   if (mask) {
     CUDA_TRY(cudaMemcpy(e->d_mask, mask, N, cudaMemcpyHostToDevice));
     d_mask = e->d_mask;
   }
   const int grid = (b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
-  MG_LAUNCH(mg_reset_kernel, grid, MG_STEP_WARPS * 32, 0, (cudaStream_t)0, b, d_mask);
+  MG_LAUNCH(mg_reset_kernel, grid, MG_STEP_WARPS * 32, 0, (cudaStream_t)0, b, d_mask, (const uint32_t*)e->d_seeds, (const int32_t*)e->d_map_idx);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   int rc;
@@ -625,6 +658,7 @@ int mg_step(void* h, void* stream) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e) return fail(MG_ERR_ARG, "mg_step: null handle");
   if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_step: maps or buffers missing");
+  CUDA_TRY(cudaSetDevice(e->device));
   cudaStream_t s = (cudaStream_t)stream;
   if (e->chunks <= 1 && e->step_mode != 1) {
     int rc = launch_step_slice(e, e->b, s);
@@ -650,6 +684,7 @@ int mg_profile_step(void* h, void* stream, float* out_ms) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e || !out_ms) return fail(MG_ERR_ARG, "mg_profile_step: bad arguments");
   if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_profile_step: maps or buffers missing");
+  CUDA_TRY(cudaSetDevice(e->device));
   MgBatch& b = e->b;
   cudaStream_t s = (cudaStream_t)stream;
   cudaEvent_t ev[3];
@@ -671,6 +706,7 @@ int mg_profile_step(void* h, void* stream, float* out_ms) {
 int mg_compute_observations(void* h, void* stream) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_compute_observations: buffers missing");
+  CUDA_TRY(cudaSetDevice(e->device));
   return launch_obs(e, (cudaStream_t)stream, nullptr);
 }
 
@@ -773,7 +809,7 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
     memcpy(terminals, st + off_term, NA);
     memcpy(truncations, st + off_trunc, NA);
   }
-  return MG_OK;
+  return check_queue_error(e, "mg_step_host");
 }
 
 // How mg_step_host delivers observations into a page-locked caller buffer. 0 (default): the whole
@@ -800,6 +836,21 @@ int mg_transfer_bytes(void* h, uint64_t* h2d, uint64_t* d2h) {
   if (!e || !h2d || !d2h) return fail(MG_ERR_ARG, "mg_transfer_bytes: bad arguments");
   *h2d = e->h2d_total;
   *d2h = e->d2h_total + (e->h_export_bytes ? *e->h_export_bytes : 0ull);
+  return MG_OK;
+}
+
+// Optional side outputs of every observation pass, in caller-owned device memory (any of them may be null):
+// row_lengths i32 [N*A], max_flip i32 [1], obs_mask u8 [N*A][T]. See include/mettagrid_b200.h.
+int mg_set_obs_aux(void* h, void* row_lengths, void* max_flip, void* obs_mask) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_set_obs_aux: null handle");
+  if ((reinterpret_cast<uintptr_t>(row_lengths) | reinterpret_cast<uintptr_t>(max_flip)) & 3)
+    return fail(MG_ERR_ARG, "mg_set_obs_aux: row_lengths and max_flip must be 4-byte aligned");
+  if (reinterpret_cast<uintptr_t>(obs_mask) & 7) return fail(MG_ERR_ARG, "mg_set_obs_aux: obs_mask must be 8-byte aligned");
+  e->b.row_len = reinterpret_cast<int32_t*>(row_lengths);
+  e->b.max_flip = reinterpret_cast<int32_t*>(max_flip);
+  e->b.obs_mask = reinterpret_cast<uint8_t*>(obs_mask);
+  mark_graphs_dirty(e);
   return MG_OK;
 }
 
@@ -875,6 +926,10 @@ int mg_read(void* h, int32_t what, void* host_out, int64_t nbytes) {
   if (!p) return fail(MG_ERR_ARG, "mg_read: unknown or unbound state array");
   if ((size_t)nbytes != bytes) return fail(MG_ERR_ARG, "mg_read: size mismatch, expected " + std::to_string(bytes));
   CUDA_TRY(cudaDeviceSynchronize());
+  {
+    const int qrc = check_queue_error(e, "mg_read");
+    if (qrc != MG_OK) return qrc;
+  }
   if (what == MG_ST_GAME_STATS) {  // pending token counts of the last observation pass
     const int grid = (e->b.num_envs + MG_STEP_WARPS - 1) / MG_STEP_WARPS;
     MG_LAUNCH(mg_fold_kernel, grid, MG_STEP_WARPS * 32, 0, (cudaStream_t)0, e->b);
@@ -941,12 +996,7 @@ int mg_sync(void* h) {
   if (!e) return fail(MG_ERR_ARG, "mg_sync: null handle");
   CUDA_TRY(cudaSetDevice(e->device));
   CUDA_TRY(cudaDeviceSynchronize());
-  if (e->b.qctl != nullptr) {
-    MgQueueCtl ctl;
-    CUDA_TRY(cudaMemcpy(&ctl, e->b.qctl, sizeof(ctl), cudaMemcpyDeviceToHost));
-    if (ctl.error != 0) return fail(MG_ERR_CUDA, "mg_sync: an observation CTA gave up waiting for the step kernel (queue mode); results are incomplete");
-  }
-  return MG_OK;
+  return check_queue_error(e, "mg_sync");
 }
 
 }  // extern "C"
@@ -1002,8 +1052,9 @@ extern "C" int mg_peek_observations_noalloc(void* h, void* obs_out_dev, void* st
   MgBatch view = b;              // same state, other destinations
   view.obs = reinterpret_cast<uint8_t*>(obs_out_dev);
   view.tok_counts = scratch;
+  view.row_len = nullptr; view.max_flip = nullptr; view.obs_mask = nullptr;  // the bound side outputs stay as they are
   cudaStream_t s = (cudaStream_t)stream;
-  const int rc_launch = launch_obs_slice(e, view, s, nullptr);
+  const int rc_launch = launch_obs_slice(e, view, s, nullptr, false);  // the handle itself is not written to: no launch count
   if (rc_launch != MG_OK) return rc_launch;
   return MG_OK;
 }

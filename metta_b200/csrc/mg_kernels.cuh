@@ -359,12 +359,15 @@ MG_DEVICE MG_NOINLINE void accumulate_episode_warp(const MgBatch& b, int env, in
     if (gstats[s] != 0.0f) atomicAdd(&b.episode_accum[2 + b.S + s], (double)gstats[s]);
 }
 
-MG_GLOBAL void mg_reset_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
+MG_GLOBAL void mg_reset_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask, const uint32_t* seeds, const int32_t* map_idx) {
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * MG_STEP_WARPS + (threadIdx.x >> 5);
   if (env >= b.num_envs) return;
   if (mask != nullptr && !mask[env]) return;
   EnvRec er = b.env[env];
+  er.seed = seeds[env];
+  er.map_idx = map_idx[env];
+  er.early_reset_step = 0u;
   reset_env_warp(b, env, lane, er);
   for (int ai = lane; ai < b.A; ai += 32) {  // _init_buffers, mettagrid_c.cpp:264-289
     const size_t g = (size_t)env * b.A + ai;
@@ -747,6 +750,7 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
   }
   if (lane == 0) {
     sm.ordered_mask = ordered_mask;
+    sm.er.spare[0] += A <= 32 ? (uint32_t)__popc(ordered_mask) : (uint32_t)A;  // agents that went through the ordered pass, since mg_create (tests read it)
     if (fast_shuffle && ordered_mask != 0u) std_shuffle_apply(sm.order, A, draws);
   }
   __syncwarp();
@@ -1023,10 +1027,27 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
     for (int i = lane + 64; i < n16; i += 32) d[i] = s[i];
   }
   if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
+  const int written = attempted < b.T ? attempted : b.T;
   if (lane == 0) {
     uint16_t* tc = b.tok_counts + (size_t)g * 2;
-    tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
+    tc[0] = (uint16_t)written;
     tc[1] = (uint16_t)attempted;
+    if (b.row_len != nullptr) b.row_len[g] = written;
+    // the running maximum only moves a few times per pass: look before bumping it, so that nearly
+    // all rows do without an atomic on the one shared word
+    if (b.max_flip != nullptr && written > MG_LD_L2(b.max_flip)) atomicMax(b.max_flip, written);
+  }
+  if (b.obs_mask != nullptr) {  // 8 slots per lane and round; a row of T bytes starts 8-byte aligned when T % 8 == 0
+    uint8_t* m = b.obs_mask + (size_t)g * b.T;
+    if ((b.T & 7) == 0) {
+      for (int j0 = lane * 8; j0 < b.T; j0 += 256) {
+        const int k = written - j0;  // slots of this group that hold tokens
+        const unsigned long long v = k <= 0 ? 0x0101010101010101ull : (k >= 8 ? 0ull : (0x0101010101010101ull << (8 * k)));
+        *reinterpret_cast<unsigned long long*>(m + j0) = v;
+      }
+    } else {
+      for (int j = lane; j < b.T; j += 32) m[j] = j >= written ? 1 : 0;
+    }
   }
 }
 

@@ -163,6 +163,11 @@ struct MgBatch {
   uint8_t* truncations;        // [N*A]
   float* rewards;              // [N*A]
   const int32_t* actions;      // [N*A]
+  // optional, caller-owned (mg_set_obs_aux): what the policy's first op would otherwise recompute from
+  // the observations (agent/src/metta/agent/components/obs_shim.py:181-196)
+  int32_t* row_len;            // [N*A] tokens written per row = index of the first 0xFF location byte (T if none)
+  int32_t* max_flip;           // [1]   max of row_len over the rows of the last full observation pass
+  uint8_t* obs_mask;           // [N*A][T] 1 where the token slot is padding (location byte 0xFF)
 };
 
 #endif  // MG_STATE_H_

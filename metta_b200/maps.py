@@ -157,3 +157,17 @@ def random_maps(lowered: LoweredConfig, num_maps: int, height: int, width: int, 
         cells[rng.permutation(inner_h * inner_w)[: len(fill)]] = rng.permutation(fill)
         out[m, border : height - border, border : width - border] = cells.reshape(inner_h, inner_w)
     return out
+
+
+def arena_mapgen_pool(lowered: LoweredConfig, num_maps: int | None = None) -> np.ndarray:
+    """The reference's own arena maps (MapGen, builder/envs.py:57-75, map_builder.seed = 1000 + i) as cell
+    codes [M,62,62]. The builders are out of scope; 256 of their grids were generated in the build container
+    (tests/golden/make_golden.py arena_pool) and are shipped as data."""
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "arena_mapgen_pool.npz")
+    data = np.load(path)
+    names = [str(x) for x in data["names"]]
+    table = np.array([0 if n in EMPTY_NAMES else lowered.cell_codes[n] for n in names], dtype=np.uint8)
+    codes = table[data["cells"]]
+    return codes if num_maps is None else codes[:num_maps]

@@ -57,6 +57,7 @@ class GpuMettaGridVecEnv:
         device: int | str = 0,
         host: bool = False,
         map_stride: int = 0,
+        obs_mask: bool = False,
     ):
         import torch
 
@@ -101,11 +102,25 @@ class GpuMettaGridVecEnv:
             self.observations.data_ptr(), self.terminals.data_ptr(), self.truncations.data_ptr(),
             self.rewards.data_ptr(), self.actions.data_ptr(),
         )
+        # what the policy's first op would recompute from the observations (obs_shim.py:181-196): tokens per
+        # row, their maximum and, on request, the padding mask, written by the observation kernel
+        self.row_lengths = torch.zeros(NA, dtype=torch.int32, device=dev)
+        self.max_flip = torch.zeros((), dtype=torch.int32, device=dev)
+        self.obs_mask = torch.ones((NA, T), dtype=torch.bool, device=dev) if obs_mask else None
+        self._want_obs_mask = obs_mask
+        self.batch.set_obs_aux(self.row_lengths.data_ptr(), self.max_flip.data_ptr(),
+                               self.obs_mask.data_ptr() if obs_mask else 0)
         if host:
-            self._h_obs = np.full((NA, T, 3), 255, dtype=np.uint8)
-            self._h_rew = np.zeros(NA, dtype=np.float32)
-            self._h_term = np.zeros(NA, dtype=np.bool_)
-            self._h_trunc = np.zeros(NA, dtype=np.bool_)
+            # page-locked arrays: the copy engines and the export kernel reach them directly, and since this
+            # object is the only writer of them, only the parts of the rows that changed cross the host link
+            pin = lambda shape, dtype: torch.zeros(shape, dtype=dtype, pin_memory=True).numpy()  # noqa: E731
+            self._h_obs = pin((NA, T, 3), torch.uint8)
+            self._h_obs[...] = 255
+            self._h_rew = pin((NA,), torch.float32)
+            self._h_term = pin((NA,), torch.uint8).view(np.bool_)
+            self._h_trunc = pin((NA,), torch.uint8).view(np.bool_)
+            self._h_act = pin((NA,), torch.int32)
+            self.batch.set_host_export(True)
         self._seed = seed
         self._map_stride = map_stride
         self._pending = None
@@ -138,6 +153,7 @@ class GpuMettaGridVecEnv:
         self._seeds[:] = seeds
         if self.host:
             self._download()
+            self.batch.set_host_export(True)  # the host arrays were just rewritten here: next step copies everything once
 
     def reset(self, seed: Optional[int] = None):
         self.async_reset(seed)
@@ -155,8 +171,8 @@ class GpuMettaGridVecEnv:
             limit = np.minimum(limit, self._max_steps)
         self._done = self._steps >= limit
         if self.host:
-            a = np.ascontiguousarray(np.asarray(actions).reshape(-1), dtype=np.int32)
-            self.batch.step_host(a, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
+            self._h_act[...] = np.asarray(actions).reshape(-1)
+            self.batch.step_host(self._h_act, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
             return
         if isinstance(actions, np.ndarray):
             actions = torch.from_numpy(np.ascontiguousarray(actions.reshape(-1), dtype=np.int32))
@@ -268,7 +284,7 @@ class GpuMettaGridVecEnv:
             map_codes = self.pool.codes
         self.batch.close()
         self.__init__(cfg, self.num_envs, maps=maps, map_codes=map_codes, seed=self._seed, device=self.device, host=self.host,
-                      map_stride=self._map_stride)
+                      map_stride=self._map_stride, obs_mask=self._want_obs_mask)
 
     def get_episode_rewards(self):
         """f32 [num_envs, agents_per_env] (MettaGrid::get_episode_rewards; CurriculumEnv takes its mean)."""

@@ -45,6 +45,8 @@ def lib() -> ctypes.CDLL:
         for name in ("mgo_agent_state", "mgo_assembler_state", "mgo_chest_state"):
             getattr(l, name).argtypes = [vp, i32, vp]
         l.mgo_set_inventory.argtypes = [vp, i32, vp, vp, i32]
+        l.mgo_get_rng.argtypes = [vp, vp]
+        l.mgo_set_rng.argtypes = [vp, vp]
         _lib = l
     return _lib
 
@@ -136,6 +138,17 @@ class OracleEnv:
         items = np.asarray([p[0] for p in pairs], dtype=np.int32)
         amounts = np.asarray([p[1] for p in pairs], dtype=np.int32)
         lib().mgo_set_inventory(self._h, agent, items.ctypes.data, amounts.ctypes.data, len(items))
+
+    def get_rng(self) -> np.ndarray:
+        """The env generator: 624 state words followed by the position (std::mt19937 _M_x, _M_p). Test hook."""
+        out = np.zeros(625, dtype=np.uint32)
+        lib().mgo_get_rng(self._h, out.ctypes.data)
+        return out
+
+    def set_rng(self, state625: np.ndarray) -> None:
+        s = np.ascontiguousarray(state625, dtype=np.uint32)
+        assert s.shape == (625,)
+        lib().mgo_set_rng(self._h, s.ctypes.data)
 
     def close(self) -> None:
         if self._h:

@@ -134,12 +134,37 @@ def cogames_clipper_config():
     print("cogames_repair_config", grid.shape, "clip_period", cfg.game.clipper.clip_period if cfg.game.clipper else None)
 
 
+def arena_mapgen_pool(n=256):
+    """BASELINE configs[1] asks for arena maps from the reference's MapGen (builder/envs.py:57-75,
+    map_builder.seed = 1000 + env index). The builders are out of scope; their output is
+    committed: `names` (the cell names that occur) and `cells` u8 [n][62][62] indexing into it."""
+    from mettagrid.builder.envs import make_arena
+
+    grids = []
+    for i in range(n):
+        ref_cfg = make_arena(24)
+        ref_cfg.game.map_builder.seed = 1000 + i
+        grids.append(ref_cfg.game.map_builder.create().build_for_num_agents(24).grid)
+    names = sorted({str(x) for g in grids for x in np.unique(g)})
+    cells = np.zeros((n,) + grids[0].shape, np.uint8)
+    for i, g in enumerate(grids):
+        for k, name in enumerate(names):
+            cells[i][g == name] = k
+    np.savez_compressed(os.path.join(HERE, "arena_mapgen_pool.npz"), names=np.array(names), cells=cells)
+    occ = {name: float((cells == k).mean()) for k, name in enumerate(names)}
+    print("arena_mapgen_pool", cells.shape, {k: round(v, 4) for k, v in occ.items()})
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "clipper":
         cogames_clipper_config()
     elif len(sys.argv) > 1 and sys.argv[1] == "cogames":
         cogames()
+    elif len(sys.argv) > 1 and sys.argv[1] == "arena_pool":
+        arena_mapgen_pool()
     else:
         main()
         cogames()
         cogames_clipper_config()
+        arena_mapgen_pool()
+

@@ -180,4 +180,80 @@ def clipped_start() -> tuple[MettaGridConfig, np.ndarray]:
     return MettaGridConfig(game=game), ascii_map(rows, legend)
 
 
-SCENARIOS = {"kitchen_sink": kitchen_sink, "tiny_truncating": tiny_truncating, "clipped_start": clipped_start}
+def _crowded(num_agents: int, rows: list[str]) -> tuple[MettaGridConfig, np.ndarray]:
+    """kitchen_sink's rules in a room where nearly every action meets another agent: the processing
+    order of the reference (std::shuffle per step) decides most outcomes. Loot can take the `gear`
+    item that raises the cargo limit, moves consume nothing (agents never run dry and stop), attacks
+    freeze for a few steps so that swaps with frozen agents happen all the time."""
+    cfg, _ = kitchen_sink()
+    game = cfg.game.model_dump()
+    game["num_agents"] = num_agents
+    teams = [i % 2 for i in range(num_agents)]
+    proto = game["agents"][0]
+    game["agents"] = []
+    for t in teams:
+        a = {k: v for k, v in proto.items()}
+        a["team_id"] = t
+        a["tags"] = ["agent", f"team{t}"]
+        a["freeze_duration"] = 3
+        game["agents"].append(a)
+    game["actions"]["move"]["consumed_resources"] = {}
+    game["actions"]["attack"]["consumed_resources"] = {}
+    game["actions"]["attack"]["success"]["loot"] = ["heart", "carbon", "gear"]
+    game["actions"]["attack"]["success"]["freeze"] = 2
+    game["inventory_regen_interval"] = 2
+    legend = {"#": "wall", ".": "empty", "B": "block", "E": "extractor", "F": "forge", "C": "chest", "a": "agent.team_0", "b": "agent.team_1"}
+    return MettaGridConfig(game=game), ascii_map(rows, legend)
+
+
+def _populate(rows: list[str], num_agents: int, seed: int) -> list[str]:
+    """Scatter `num_agents` agents (teams alternating) over the free cells of an object-only room, reproducibly."""
+    cells = [(r, c) for r, row in enumerate(rows) for c, ch in enumerate(row) if ch == "."]
+    pick = np.random.RandomState(seed).permutation(len(cells))[:num_agents]
+    out = [list(row) for row in rows]
+    for k, idx in enumerate(sorted(pick)):
+        r, c = cells[idx]
+        out[r][c] = "ab"[k % 2]
+    return ["".join(row) for row in out]
+
+
+def dense_conflict() -> tuple[MettaGridConfig, np.ndarray]:
+    """28 agents in an 8x7 room with two forges (chest search distance 2, a multi-vibe protocol with
+    min_agents 2), an extractor and two chests."""
+    rows = [
+        "##########",
+        "#........#",
+        "#..F...C.#",
+        "#........#",
+        "#...E..F.#",
+        "#.C......#",
+        "#....B...#",
+        "#........#",
+        "##########",
+    ]
+    return _crowded(28, _populate(rows, 28, seed=1))
+
+
+def crowd_48() -> tuple[MettaGridConfig, np.ndarray]:
+    """48 agents (more than a warp has lanes: the step kernel's 64-agent instantiation) in a 12x12 room."""
+    rows = [
+        "##############",
+        "#............#",
+        "#..F......C..#",
+        "#............#",
+        "#....E.......#",
+        "#............#",
+        "#......F.....#",
+        "#.C..........#",
+        "#............#",
+        "#.....E....B.#",
+        "#............#",
+        "#..C.....F...#",
+        "#............#",
+        "##############",
+    ]
+    return _crowded(48, _populate(rows, 48, seed=2))
+
+
+SCENARIOS = {"kitchen_sink": kitchen_sink, "tiny_truncating": tiny_truncating, "clipped_start": clipped_start,
+             "dense_conflict": dense_conflict, "crowd_48": crowd_48}

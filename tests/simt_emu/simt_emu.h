@@ -148,6 +148,7 @@ static inline unsigned __match_any_sync(unsigned, int v) {
   return m;
 }
 static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
+static inline int atomicMax(int* p, int v) { int o = *p; if (v > o) *p = v; return o; }
 static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
 static inline long long clock64() { return 0; }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
@@ -170,6 +171,7 @@ static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMallocHost(void** p, size_t n) { return cudaMalloc(p, n); }
 static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMemset(void* p, int v, size_t n) { memset(p, v, n); return 0; }
+static inline cudaError_t cudaMemsetAsync(void* p, int v, size_t n, void*) { memset(p, v, n); return 0; }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, int) { memcpy(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, int, cudaStream_t) { memcpy(d, s, n); return 0; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, int) { *s = nullptr; return 0; }

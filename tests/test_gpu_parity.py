@@ -278,3 +278,133 @@ def test_changed_rows_export_follows_resets(chunks, lib, monkeypatch):
         episodes_seen += int(trunc.any() or term.any())
     assert episodes_seen >= 2
     b.close()
+
+
+@pytest.mark.parametrize("name,n,steps", [("dense_conflict", 64, 2000), ("crowd_48", 32, 600)])
+def test_crowded_rooms_vs_oracle(name, n, steps, lib):
+    """Where the reference's shuffled processing order decides most outcomes: 28 agents in an 8x7 room
+    (attack, transfer, swaps with frozen agents, shared assembler neighbourhoods, chests in reach of an
+    assembler, loot that removes a limit modifier), and 48 agents (the 64-agent instantiation of the
+    step kernel). The oracle is pinned against the compiled reference on the same scenarios
+    (tests/test_oracle_vs_reference.py::test_crowded_rooms_many_seeds)."""
+    cfg, grid = SCENARIOS[name]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=n, seeds=np.arange(n) + 300, cuda=True)
+    ls.compare_outputs()
+    rng = np.random.RandomState(17)
+    for s in range(steps):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=41, step=s))
+        if s % 50 == 49:
+            ls.compare_state()
+    ordered = ls.batch.read_env()["spare"][:, 0].sum() / float(n * ls.A * steps)
+    st = ls.batch.read_agent_stats().sum(axis=(0, 1))
+    assert st[L.MG_AS_SWAP] > 0 and st[L.MG_AS_TRANSFER_COUNT] > 0 and st[L.MG_AS_ATTACK_HIT : L.MG_AS_ATTACK_HIT + 8].sum() > 0
+    assert ordered > 0.6, f"only {ordered:.2f} of the agents went through the ordered pass"
+    print(f"{name}: {ordered:.3f} of all agent-steps went through the ordered pass")
+    ls.close()
+
+
+def test_shuffle_with_a_rejected_word(lib):
+    """Lemire's method in std::shuffle rejects about one word in 1e7 (bits/uniform_int_dist.h:257-330); the
+    kernel then leaves its draw-per-lane path for the serial loop. Forced here by zeroing the state word of
+    the second draw (a zero word tempers to zero, and 0 * 12 mod 2^32 < 2^32 mod 12) in both generators."""
+    cfg, grid = SCENARIOS["dense_conflict"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    n = 9
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=n, seeds=np.arange(n) + 900, cuda=True)
+    rng = np.random.RandomState(23)
+    for s in range(40):
+        if s % 4 == 1:
+            state = ls.batch.read_rng()
+            idx = ls.batch.read_env()["rng_idx"].astype(np.int64)
+            for i, o in enumerate(ls.checkers):
+                mine = o.get_rng()
+                assert int(mine[624]) == int(idx[i]) and np.array_equal(mine[:624], state[i]), "generators differ before the test"
+                if idx[i] + 2 >= 624:
+                    continue
+                state[i, idx[i] + 1] = 0
+                mine[idx[i] + 1] = 0
+                o.set_rng(mine)
+            before = idx.copy()
+            ls.batch._write(10, state)
+            ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+            after = ls.batch.read_env()["rng_idx"].astype(np.int64)
+            for i, o in enumerate(ls.checkers):
+                assert int(o.get_rng()[624]) == int(after[i])
+                if before[i] + 2 < 624 and after[i] > before[i]:
+                    assert after[i] - before[i] >= ls.A // 2 + 1, "the rejected word was not replaced by another draw"
+        else:
+            ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+    ls.compare_state()
+    ls.close()
+
+
+def test_reset_while_a_step_is_in_flight_and_partial_reset(lib):
+    """mg_reset right behind an asynchronous mg_step on a non-blocking stream (it must wait for the step),
+    with a mask: unmasked envs keep running their episode."""
+    import torch
+
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 24
+    ls = Lockstep(cfg, arena_maps(low, 4, seed=4), num_envs=n, seeds=np.arange(n) + 11, cuda=True)
+    rng = np.random.RandomState(6)
+    side = torch.cuda.Stream()
+    for s in range(12):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    a = rng.randint(0, 5, size=(n, 24)).astype(np.int32)
+    ls.buf.set_actions(a.reshape(-1))
+    torch.cuda.synchronize()
+    ls.batch.step(side.cuda_stream)  # in flight on a side stream
+    mask = (np.arange(n) % 3 == 0).astype(np.uint8)
+    new_seeds = ls.seeds.copy()
+    new_seeds[mask.astype(bool)] += 1000
+    ls.batch.reset(new_seeds, ls.map_of_env.astype(np.int32), mask)
+    ls.step_no += 1
+    for i, ck in enumerate(ls.checkers):
+        ck.step(a[i])
+        if mask[i]:
+            ls.seeds[i] = new_seeds[i]
+            ls.checkers[i] = ls._make_checker(i)
+    ls.compare_outputs()
+    for s in range(10):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.compare_state()
+    ls.close()
+
+
+def test_handle_on_a_device_that_is_not_current(lib):
+    """Every entry point makes its handle's device current itself: a batch on cuda:1 steps correctly while
+    cuda:0 is the caller's current device (needs two GPUs)."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU")
+    cfg, grid = SCENARIOS["kitchen_sink"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    from oracle.oracle import OracleEnv
+
+    A, T = cfg.game.num_agents, cfg.game.obs.num_tokens
+    torch.cuda.set_device(0)
+    b = Batch(low, build_pool(low, codes), 2, device=1)
+    obs = torch.zeros((2 * A, T, 3), dtype=torch.uint8, device="cuda:1")
+    term = torch.zeros(2 * A, dtype=torch.uint8, device="cuda:1")
+    trunc = torch.zeros_like(term)
+    rew = torch.zeros(2 * A, dtype=torch.float32, device="cuda:1")
+    act = torch.zeros(2 * A, dtype=torch.int32, device="cuda:1")
+    b.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act.data_ptr())
+    b.reset(np.array([5, 6], np.uint32), np.zeros(2, np.int32))
+    orcs = [OracleEnv(low.words, codes, 5 + i) for i in range(2)]
+    rng = np.random.RandomState(2)
+    for s in range(20):
+        a = random_actions(rng, cfg, low, 2 * A)
+        act.copy_(torch.from_numpy(a))
+        torch.cuda.synchronize(1)
+        torch.cuda.set_device(0)
+        b.step(0)
+        b.sync()
+        for i, o in enumerate(orcs):
+            o.step(a[i * A : (i + 1) * A])
+            assert np.array_equal(obs[i * A : (i + 1) * A].cpu().numpy(), o.observations), f"step {s} env {i}"
+    b.close()

@@ -146,3 +146,55 @@ def test_properties_and_config_swap():
     assert torch.equal(obs, ref_obs)
     env.close()
     ref.close()
+
+
+def test_obs_aux_matches_the_shim_expression_at_full_size():
+    """(f3) row_lengths, max_flip and obs_mask written by the observation kernel equal what
+    ObsShimTokens.forward computes per batch (obs_shim.py:181-196), on 4096 x 24 arena rows."""
+    import torch
+
+    from metta_b200.builders import make_arena
+    from metta_b200.maps import arena_mapgen_pool
+    from metta_b200.vecenv import GpuMettaGridVecEnv
+
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 4096
+    env = GpuMettaGridVecEnv(cfg, n, map_codes=arena_mapgen_pool(low, 64), seed=42, obs_mask=True)
+    env.collect_infos = False
+    obs, _ = env.reset()
+    g = torch.Generator().manual_seed(0)
+    M = obs.shape[1]
+    for step in range(12):
+        pad = obs[..., 0] == 255
+        flip = pad.int().argmax(dim=1)
+        want = torch.where(pad.any(dim=1), flip, torch.full_like(flip, M))
+        assert torch.equal(env.row_lengths.long(), want.long()), f"step {step}: row_lengths"
+        assert int(env.max_flip) == int(want.max()), f"step {step}: max_flip"
+        assert torch.equal(env.obs_mask, pad), f"step {step}: obs_mask"
+        a = torch.randint(0, 5, (n * 24,), generator=g, dtype=torch.int32).cuda()
+        obs, *_ = env.step(a)
+    env.close()
+
+
+def test_host_mode_uses_page_locked_arrays_and_matches_device_mode():
+    """GpuMettaGridVecEnv(host=True) hands out page-locked numpy arrays filled through the changed-rows
+    export; they must equal the device tensors of a twin env stepped with the same actions."""
+    import torch
+
+    cfg, low, codes, dev_env = _make("kitchen_sink", 40)
+    _, _, _, host_env = _make("kitchen_sink", 40, host=True)
+    A = cfg.game.num_agents
+    o_d, _ = dev_env.reset(seed=5)
+    o_h, _ = host_env.reset(seed=5)
+    assert isinstance(o_h, np.ndarray) and torch.from_numpy(o_h).is_pinned()
+    assert np.array_equal(o_h, o_d.cpu().numpy())
+    rng = np.random.RandomState(9)
+    for step in range(40):
+        a = random_actions(rng, cfg, low, 40 * A)
+        o_d, r_d, d_d, t_d, _ = dev_env.step(a)
+        o_h, r_h, d_h, t_h, _ = host_env.step(a)
+        assert np.array_equal(o_h, o_d.cpu().numpy()), f"step {step}: observations"
+        assert np.array_equal(r_h, r_d.cpu().numpy()) and np.array_equal(d_h, d_d.cpu().numpy()) and np.array_equal(t_h, t_d.cpu().numpy())
+    dev_env.close()
+    host_env.close()

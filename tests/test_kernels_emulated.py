@@ -89,3 +89,48 @@ def test_emulated_chunked_launch(emu_lib, monkeypatch):
     for s in range(14):
         ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
     ls.close()
+
+
+def test_emulated_obs_aux(emu_lib):
+    """mg_set_obs_aux: row lengths, their maximum and the padding mask equal what the policy's first op
+    computes from the observations (agent/src/metta/agent/components/obs_shim.py:181-196)."""
+    cfg, grid = SCENARIOS["kitchen_sink"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=3, seeds=[3, 4, 5], clib=emu_lib)
+    NA, T = ls.N * ls.A, ls.T
+    row_len = np.full(NA, -1, np.int32)
+    max_flip = np.full(1, -1, np.int32)
+    mask = np.full((NA, T), 7, np.uint8)
+    ls.batch.set_obs_aux(row_len.ctypes.data, max_flip.ctypes.data, mask.ctypes.data)
+    rng = np.random.RandomState(5)
+    for s in range(30):
+        ls.step(random_actions(rng, cfg, ls.lowered, NA))
+        obs = ls.buf.obs
+        pad = obs[:, :, 0] == 255
+        expect = np.where(pad.any(1), pad.argmax(1), T)
+        assert np.array_equal(row_len, expect)
+        assert max_flip[0] == expect.max()
+        assert np.array_equal(mask.astype(bool), pad)
+    ls.close()
+
+
+@pytest.mark.parametrize("name,envs,steps", [("dense_conflict", 3, 150), ("crowd_48", 2, 60)])
+def test_emulated_crowded_rooms(name, envs, steps, emu_lib):
+    """The order-independence classifier where conflicts dominate (and, with 48 agents, the 64-agent
+    instantiation of the step kernel whose agents all take the ordered pass)."""
+    cfg, grid = SCENARIOS[name]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=envs, seeds=np.arange(envs) + 70, clib=emu_lib)
+    ls.compare_outputs()
+    rng = np.random.RandomState(12)
+    for s in range(steps):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=23, step=s))
+        if s % 50 == 49:
+            ls.compare_state()
+    ls.compare_state()
+    ordered = ls.batch.read_env()["spare"][:, 0].sum() / float(envs * ls.A * steps)
+    st = ls.batch.read_agent_stats().sum(axis=(0, 1))
+    from metta_b200.layout import L
+    assert st[L.MG_AS_SWAP] > 0 and st[L.MG_AS_TRANSFER_COUNT] > 0 and st[L.MG_AS_ATTACK_HIT : L.MG_AS_ATTACK_HIT + 8].sum() > 0
+    assert ordered > 0.6, f"only {ordered:.2f} of the agents went through the ordered pass"
+    ls.close()

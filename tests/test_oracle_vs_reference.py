@@ -101,3 +101,16 @@ def test_bridge_equals_reference_lowering(product_lib):
         own.step(a)
         bridged.step(a)
         assert np.array_equal(own.observations, bridged.observations) and np.array_equal(own.rewards, bridged.rewards)
+
+
+@needs_ref
+@pytest.mark.parametrize("name,seeds,steps", [("dense_conflict", 64, 2000), ("crowd_48", 12, 1500)])
+def test_crowded_rooms_many_seeds(name, seeds, steps, product_lib):
+    """Rooms where nearly every action meets another agent (attack, transfer, swap with frozen agents,
+    shared assembler neighbourhoods, chests within reach of an assembler, loot that removes a limit
+    modifier): the oracle against the compiled reference on many seeds, every byte of every step."""
+    cfg, grid = SCENARIOS[name]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    for seed in range(300, 300 + seeds):
+        lockstep(cfg, codes, low, seed, steps, invalid_every=41)

@@ -1,5 +1,5 @@
 #!/bin/bash
-# usage: tools_bench_variants.sh name ... ; runs bench.py against build_variants/lib_<name>.so and prints the key numbers
+# usage: tools/bench_variants.sh name ... ; runs bench.py against build_variants/lib_<name>.so and prints the key numbers
 for v in "$@"; do
   if [ "$v" = default ]; then python bench.py --no-cpu-baseline > gpurun_out/bench_$v.log 2>&1; else MG_LIB_PATH=build_variants/lib_$v.so python bench.py --no-cpu-baseline > gpurun_out/bench_$v.log 2>&1; fi
   python - "$v" <<'PY'

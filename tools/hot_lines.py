@@ -1,5 +1,5 @@
 """Per-source-line instruction and stall-sample totals from an ncu report (cuda,sass source view).
-usage: python tools_hot_lines.py report.ncu-rep [warps_per_launch] [samples]"""
+usage: python tools/hot_lines.py report.ncu-rep [warps_per_launch] [samples]"""
 import csv, subprocess, sys
 rep = sys.argv[1]
 div = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0

@@ -1,4 +1,4 @@
-"""Key metrics of the first kernel in an ncu report. usage: python tools_ncu_summary.py report.ncu-rep"""
+"""Key metrics of the first kernel in an ncu report. usage: python tools/ncu_summary.py report.ncu-rep"""
 import csv, subprocess, sys
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
