@@ -75,6 +75,7 @@ struct MgEnvs {
   int sm_count;
   int q_early, q_late;  // observation CTAs per SM beside / behind the step kernel in queue mode
   bool graph_dirty;
+  long long graph_launches, hgraph_launches;  // kernels per replay of the two graphs
   cudaGraph_t graph;
   cudaGraphExec_t graph_exec;
   uint8_t* d_mask;
@@ -116,7 +117,7 @@ static int dev_alloc(MgEnvs* e, T** out, size_t count, bool zero = true) {
 
 // Queue mode only: did an observation CTA give up waiting for the step kernel? (checked after a sync)
 static int check_queue_error(MgEnvs* e, const char* who) {
-  if (e->step_mode != 1 || e->b.qctl == nullptr) return MG_OK;
+  if (e->step_mode == 0 || e->b.qctl == nullptr) return MG_OK;
   MgQueueCtl ctl;
   CUDA_TRY(cudaMemcpy(&ctl, e->b.qctl, sizeof(ctl), cudaMemcpyDeviceToHost));
   if (ctl.error != 0)
@@ -190,7 +191,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   b.max_chest = cfg[MGC_MAX_CHESTS] > 0 ? cfg[MGC_MAX_CHESTS] : 1;
   b.has_clipper = (cfg + cfg[MGC_OFF_CLIPPER])[MG_CLIP_ENABLED];
   b.obs_cells = cfg[MGC_OBS_H] * cfg[MGC_OBS_W];
-  b.grid_stride = ((b.H * b.W + 7) / 8) * 8;
+  b.grid_stride = ((b.H * b.W + 63) / 64) * 64;  // whole 128-byte lines per env (see mg_fused_kernel)
   b.auto_reset = 1;
   b.map_stride = 0;
   b.env_begin = 0;
@@ -313,6 +314,10 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
     const int stride = 1 << b.rec_shift;
     const int base_agent = ncell, base_asm = ncell + b.A, base_chest = ncell + b.A + b.max_asm;
     b.rec_slots = base_chest + b.max_chest;
+    {  // pad so that an env's records end on a 128-byte line
+      const int per_line = 128 >> b.rec_shift;
+      if (per_line > 1) b.rec_slots = ((b.rec_slots + per_line - 1) / per_line) * per_line;
+    }
     if (b.rec_slots > 0xFFFF) return fail(MG_ERR_ARG, "mg_create: too many objects per env for the token record index");
     b.rec_kind_base_lo = (uint32_t)0 | ((uint32_t)base_agent << 16);   // grid kinds 0 static, 1 agent
     b.rec_kind_base_hi = (uint32_t)base_asm | ((uint32_t)base_chest << 16);  // 2 assembler, 3 chest
@@ -362,7 +367,8 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   if (e->chunks < 1) e->chunks = 1;
   if (e->chunks > MG_MAX_CHUNKS) e->chunks = MG_MAX_CHUNKS;
   e->step_mode = MG_DEFAULT_STEP_MODE;
-  if (const char* env_mode = getenv("MG_STEP_MODE")) e->step_mode = strcmp(env_mode, "queue") == 0 ? 1 : 0;  // tuning knob
+  if (const char* env_mode = getenv("MG_STEP_MODE"))  // tuning knob: "sliced", "queue", "fused"
+    e->step_mode = strcmp(env_mode, "queue") == 0 ? 1 : (strcmp(env_mode, "fused") == 0 ? 2 : 0);
   e->q_early = MG_QUEUE_OBS_CTAS_EARLY;
   e->q_late = MG_QUEUE_OBS_CTAS_LATE;
   if (const char* v = getenv("MG_QUEUE_EARLY")) e->q_early = atoi(v);
@@ -600,6 +606,57 @@ static int enqueue_queue_step(MgEnvs* e, cudaStream_t s) {
 }
 #endif
 
+#ifndef MG_SIMT_EMU
+}  // extern "C" (templates below)
+// Fused mode: one persistent kernel steps the envs and encodes their observations (mg_fused_kernel).
+template <int MAXA, int CPL>
+static int launch_fused_t(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
+  const int slot = (b.T * 3 + 16 + 15) & ~15;
+  size_t warp_bytes = sizeof(StepSmem<MAXA>);
+  if ((size_t)(slot + MG_OBS_DESC_BYTES(CPL)) > warp_bytes) warp_bytes = (size_t)(slot + MG_OBS_DESC_BYTES(CPL));
+  warp_bytes = (warp_bytes + 127) & ~(size_t)127;
+  const size_t smem = warp_bytes * MG_FUSED_WARPS;
+  static bool configured = false;  // per instantiation
+  static int per_sm = 0;
+  if (!configured) {
+    CUDA_TRY(cudaFuncSetAttribute(mg_fused_kernel<MAXA, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mg_fused_kernel<MAXA, CPL>, MG_FUSED_WARPS * 32, smem));
+  if (per_sm < 1) return fail(MG_ERR_CUDA, "fused step kernel does not fit an SM");
+  const int n = b.env_end - b.env_begin;
+  const int tasks = n * ((b.A + MG_FUSED_ROWS - 1) / MG_FUSED_ROWS);
+  int grid = e->sm_count * per_sm;
+  const int useful = ((n > tasks ? n : tasks) + MG_FUSED_WARPS - 1) / MG_FUSED_WARPS;
+  if (grid > useful) grid = useful;
+  MG_LAUNCH((mg_fused_kernel<MAXA, CPL>), grid, MG_FUSED_WARPS * 32, smem, s, b, (int)warp_bytes);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return MG_OK;
+}
+
+static bool fused_supported(const MgBatch& b) {
+  const int cpl = (b.obs_cells + 31) / 32;
+  return b.A <= 32 ? (cpl <= 4) : (cpl <= 4);
+}
+
+static int enqueue_fused_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* ht) {
+  const MgBatch& b = e->b;
+  int rc;
+  if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
+  MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  const int cpl = (b.obs_cells + 31) / 32;
+  if (b.A <= 32) rc = cpl <= 2 ? launch_fused_t<32, 2>(e, b, s) : launch_fused_t<32, 4>(e, b, s);
+  else rc = launch_fused_t<MG_MAX_AGENTS, 4>(e, b, s);
+  if (rc != MG_OK) return rc;
+  if (ht != nullptr && (rc = launch_export(e, b, s, *ht, b.env_begin * b.A, b.env_end * b.A)) != MG_OK) return rc;
+  return MG_OK;
+}
+extern "C" {
+#endif
+
 // Start episodes: seeds u32 [N], map index i32 [N], optional mask u8 [N] (host pointers; null mask = all).
 // Writes the initial observation and clears rewards/terminals/truncations of the reset envs
 // (MettaGrid ctor + set_buffers/_init_buffers, mettagrid_c.cpp:46-155,264-289).
@@ -644,8 +701,12 @@ static int capture_step_graph(MgEnvs* e, const MgHostTargets* ht, cudaGraph_t* g
   if (*graph) { cudaGraphDestroy(*graph); *graph = nullptr; }
   const long long before = e->launches;
   CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
-  int rc = (e->step_mode == 1 && ht == nullptr) ? enqueue_queue_step(e, e->capture_stream) : enqueue_chunked_step(e, e->capture_stream, ht);
+  int rc;
+  if (e->step_mode == 2 && fused_supported(e->b)) rc = enqueue_fused_step(e, e->capture_stream, ht);
+  else if (e->step_mode == 1 && ht == nullptr) rc = enqueue_queue_step(e, e->capture_stream);
+  else rc = enqueue_chunked_step(e, e->capture_stream, ht);
   cudaError_t end = cudaStreamEndCapture(e->capture_stream, graph);
+  (ht != nullptr ? e->hgraph_launches : e->graph_launches) = e->launches - before;  // kernels one replay of this graph launches
   e->launches = before;
   if (rc != MG_OK) return rc;
   if (end != cudaSuccess) return fail(MG_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(end));
@@ -660,7 +721,7 @@ int mg_step(void* h, void* stream) {
   if (!e->maps_loaded || !e->buffers_bound) return fail(MG_ERR_STATE, "mg_step: maps or buffers missing");
   CUDA_TRY(cudaSetDevice(e->device));
   cudaStream_t s = (cudaStream_t)stream;
-  if (e->chunks <= 1 && e->step_mode != 1) {
+  if (e->chunks <= 1 && e->step_mode == 0) {
     int rc = launch_step_slice(e, e->b, s);
     return rc != MG_OK ? rc : launch_obs(e, s, nullptr);
   }
@@ -673,7 +734,7 @@ int mg_step(void* h, void* stream) {
     e->graph_dirty = false;
   }
   CUDA_TRY(cudaGraphLaunch(e->graph_exec, s));
-  e->launches += e->step_mode == 1 ? 2 + (e->q_early > 0) + (e->q_late > 0) : 2LL * e->chunks;
+  e->launches += e->graph_launches;
   return MG_OK;
 #endif
 }
@@ -772,7 +833,7 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
     }
   }
   if (sparse) {
-    if (e->chunks <= 1) {
+    if (e->chunks <= 1 && e->step_mode == 0) {
       TRY(launch_step_slice(e, b, s));
       TRY(launch_obs(e, s, nullptr));
       TRY(launch_export(e, b, s, ht, 0, (int)NA));
@@ -783,7 +844,7 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
         e->hgraph_dirty = false;
       }
       CUDA_TRY(cudaGraphLaunch(e->hgraph_exec, s));
-      e->launches += 3LL * e->chunks;
+      e->launches += e->hgraph_launches;
     }
     CUDA_TRY(cudaMemcpyAsync(e->h_export_bytes, e->d_export_bytes, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

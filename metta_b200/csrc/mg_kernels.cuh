@@ -982,6 +982,7 @@ MG_GLOBAL void mg_queue_begin_kernel(MgQueueCtl* ctl) {
     ctl->epoch += 1u;
     ctl->tail = 0u;
     ctl->head = 0u;
+    ctl->env_next = 0u;
   }
 }
 #endif  // !MG_SIMT_EMU
@@ -1010,7 +1011,7 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
     for (int i = lane + 64; i < n16; i += 32) p[i] = ff;
   }
   __syncwarp();
-  const uint32_t current_step = b.env[env].current_step;
+  const uint32_t current_step = MG_LD_L2(&b.env[env].current_step);  // two env records share a cache line: read past L1 (fused kernel)
   const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step);
   __syncwarp();
   // store: bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
@@ -1104,6 +1105,86 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_queue
     __syncthreads();
     if (env < 0) return;
     if (ai < b.A) obs_row_warp<CPL>(b, env, ai, lane, warp_smem);
+  }
+}
+#endif  // !MG_SIMT_EMU
+
+#ifndef MG_SIMT_EMU
+// ---------------------------------------------------------------- one kernel for the whole step
+// mg_fused_kernel: a persistent grid in which every warp first steps envs (claimed one at a time from a
+// counter) and then, once no env is left to claim, encodes observation rows of envs whose step has
+// finished (tasks of MG_FUSED_ROWS rows, handed out in the order the envs were published). Why: the step
+// of an env is one dependent chain (tens of microseconds, with a long tail where assemblers are used) that
+// leaves the issue slots idle, while the observation pass is issue-bound. As two kernels per slice, every
+// slice's observation pass waited for the slowest env of the slice and the tail of every launch ran on a
+// half-empty GPU; here the encoding of finished envs fills the issue slots under the chains of the slow
+// ones, and only the last env's own rows are left over at the end.
+// Hand-over: the stepping warp makes its writes visible (__threadfence) and publishes epoch << 32 | env
+// into the queue; a consumer polls the entry, fences, and reads the env's state. State that a consumer
+// reads lives in cache lines owned by one env (grid and token-record strides are padded to 128 bytes; the
+// one exception, EnvRec::current_step, is read at L2), so a line cached while encoding one env never holds
+// another env's pre-step bytes.
+#ifndef MG_FUSED_WARPS
+#define MG_FUSED_WARPS 4
+#endif
+#ifndef MG_FUSED_MIN_CTAS
+#define MG_FUSED_MIN_CTAS 6
+#endif
+#ifndef MG_FUSED_ROWS
+#define MG_FUSED_ROWS 4
+#endif
+template <int MAXA, int CPL>
+MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_FUSED_WARPS * 32, MG_FUSED_MIN_CTAS) mg_fused_kernel(const MG_GRID_CONSTANT MgBatch b, int warp_bytes) {
+  MG_DYN_SMEM(dyn);
+  const int lane = threadIdx.x & 31;
+  unsigned char* mine = dyn + (size_t)(threadIdx.x >> 5) * warp_bytes;  // [StepSmem] while stepping, [row image | descriptors] while encoding
+  StepSmem<MAXA>& sm = *reinterpret_cast<StepSmem<MAXA>*>(mine);
+  MgQueueCtl* ctl = b.qctl;
+  const uint32_t n_envs = (uint32_t)(b.env_end - b.env_begin);
+  const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&ctl->epoch);
+  for (;;) {  // ---- stepping
+    uint32_t k = 0;
+    if (lane == 0) k = atomicAdd(&ctl->env_next, 1u);
+    k = __shfl_sync(MG_FULL_MASK, k, 0);
+    if (k >= n_envs) break;
+    const int env = b.env_begin + (int)k;
+    step_env_warp<MAXA>(b, sm, env, lane);
+    __threadfence();  // every lane's writes, then the entry
+    __syncwarp();
+    if (lane == 0) {
+      const uint32_t pos = atomicAdd(&ctl->tail, 1u);
+      *reinterpret_cast<volatile unsigned long long*>(b.queue + pos) = ((unsigned long long)epoch << 32) | (unsigned long long)(uint32_t)env;
+    }
+    __syncwarp();
+  }
+  // ---- encoding
+  const uint32_t per_env = (uint32_t)((b.A + MG_FUSED_ROWS - 1) / MG_FUSED_ROWS);
+  const uint32_t total = n_envs * per_env;
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(&ctl->head, 1u);
+    t = __shfl_sync(MG_FULL_MASK, t, 0);
+    if (t >= total) break;
+    int env = -1;
+    if (lane == 0) {
+      const volatile unsigned long long* entry = b.queue + t / per_env;
+      const long long t0 = clock64();
+      for (;;) {
+        const unsigned long long v = *entry;
+        if ((uint32_t)(v >> 32) == epoch) { env = (int)(uint32_t)v; break; }
+        if (clock64() - t0 > MG_QUEUE_WAIT_CYCLES) { atomicExch(&ctl->error, 1u); break; }
+        MG_NANOSLEEP(100);
+      }
+    }
+    env = __shfl_sync(MG_FULL_MASK, env, 0);
+    if (env < 0) break;
+    __threadfence();
+    const int a0 = (int)(t % per_env) * MG_FUSED_ROWS;
+#pragma unroll 1
+    for (int ai = a0; ai < a0 + MG_FUSED_ROWS && ai < b.A; ai++) {
+      obs_row_warp<CPL>(b, env, ai, lane, mine);
+      __syncwarp();
+    }
   }
 }
 #endif  // !MG_SIMT_EMU

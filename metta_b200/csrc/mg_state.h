@@ -100,6 +100,8 @@ struct MgQueueCtl {
   uint32_t tail;   // entries published so far
   uint32_t head;   // observation tasks handed out so far
   uint32_t error;  // set if a consumer gave up waiting (never in a healthy run)
+  uint32_t env_next;  // fused kernel: envs handed out so far
+  uint32_t pad[3];
 };
 
 // Everything a kernel needs, passed by value.

@@ -408,3 +408,28 @@ def test_handle_on_a_device_that_is_not_current(lib):
             o.step(a[i * A : (i + 1) * A])
             assert np.array_equal(obs[i * A : (i + 1) * A].cpu().numpy(), o.observations), f"step {s} env {i}"
     b.close()
+
+
+@pytest.mark.parametrize("name,n,steps", [("arena", 40, 60), ("kitchen_sink", 33, 200), ("crowd_48", 9, 120), ("dense_conflict", 70, 300)])
+def test_fused_mode_matches_oracle(name, n, steps, lib, monkeypatch):
+    """MG_STEP_MODE=fused: one persistent kernel whose warps step envs and then encode the observations of
+    finished envs. Same results as the sliced launch, for the 32- and 64-agent instantiations and both
+    window sizes, with episode ends inside the run."""
+    monkeypatch.setenv("MG_STEP_MODE", "fused")
+    if name == "arena":
+        cfg = make_arena(24, max_steps=25)
+        cfg.game.episode_truncates = True
+        low = lower_game_config(cfg.game, 62, 62)
+        codes = arena_maps(low, 4, seed=6)
+    else:
+        cfg, grid = SCENARIOS[name]()
+        low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+        codes = names_to_codes(low, grid)
+    ls = Lockstep(cfg, codes, num_envs=n, seeds=np.arange(n) + 70, cuda=True)
+    ls.compare_outputs()
+    rng = np.random.RandomState(9)
+    for s in range(steps):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=37, step=s))
+    ls.compare_state()
+    ls.batch.sync()
+    ls.close()

@@ -3,12 +3,12 @@ sys.path.insert(0, os.getcwd())
 from metta_b200.batch import Batch
 from metta_b200.builders import make_arena
 from metta_b200.lowering import lower_game_config
-from metta_b200.maps import arena_maps, build_pool
+from metta_b200.maps import arena_mapgen_pool, build_pool
 N=int(sys.argv[1]) if len(sys.argv)>1 else 4096
 FLUSH=(sys.argv[2]=='flush') if len(sys.argv)>2 else True
 A,T=24,200
 cfg=make_arena(A); low=lower_game_config(cfg.game,62,62)
-pool=build_pool(low, arena_maps(low,256,seed=1234))
+pool=build_pool(low, arena_mapgen_pool(low))
 b=Batch(low,pool,N)
 dev='cuda'
 obs=torch.zeros((N*A,T,3),dtype=torch.uint8,device=dev); term=torch.zeros(N*A,dtype=torch.uint8,device=dev); trunc=torch.zeros_like(term); rew=torch.zeros(N*A,dtype=torch.float32,device=dev)
@@ -17,6 +17,13 @@ b.set_buffers(obs.data_ptr(),term.data_ptr(),trunc.data_ptr(),rew.data_ptr(),act
 b.reset((np.arange(N)+42).astype(np.uint32),(np.arange(N)%256).astype(np.int32))
 flush=torch.empty(256*1024*1024,dtype=torch.uint8,device=dev)
 STEPS=int(sys.argv[3]) if len(sys.argv)>3 else 20
+if len(sys.argv)>4 and sys.argv[4]=='stagger':  # the bench's steady state: envs at staggered episode phases
+    g=np.arange(N,dtype=np.int64)
+    b.set_early_reset((1+(g*6181)%9999).astype(np.uint32))
+    ring=torch.randint(0,5,(16,N*A),dtype=torch.int32).to(dev)
+    for s in range(10000):
+        act.copy_(ring[s%16]); b.step()
+    torch.cuda.synchronize()
 for s in range(STEPS):
     act.copy_(torch.randint(0,5,(N*A,),dtype=torch.int32))
     if FLUSH: flush.fill_(s)
