@@ -255,6 +255,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &b.hot_stats, N * A * (size_t)MG_HOT_STATS));
   TRY(dev_alloc(e, &b.game_stats, N * (size_t)b.GS));
   TRY(dev_alloc(e, &b.rng, N * MT_N));
+  TRY(dev_alloc(e, &b.rng_seeded, N * MT_N, false));
   if (b.has_clipper) TRY(dev_alloc(e, &b.clip_rng, N * MT_N));
   {
     // static token templates (see mg_obs.cuh): cells, then protocols, then agent groups

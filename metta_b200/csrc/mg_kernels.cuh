@@ -168,24 +168,48 @@ MG_DEVICE MG_NOINLINE void write_all_asm_tokens_warp(const MgBatch& b, int env, 
 
 // One observation pass that only counts tokens (nothing is written): the reference runs such
 // passes on buffers nobody reads (see reset_env_warp), but their token counts stay in the stats.
-MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step) {
+MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step, int folds) {
   __syncwarp();
-  for (int ai = 0; ai < b.A; ai++) {
-    const int attempted = obs_count_agent_warp(b, env, ai, lane, current_step);
-    if (lane == 0) {
-      uint16_t* tc = b.tok_counts + ((size_t)env * b.A + ai) * 2;
-      tc[0] = (uint16_t)(attempted < b.T ? attempted : b.T);
-      tc[1] = (uint16_t)attempted;
+  uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
+  if (b.obs_cells <= 128) {  // four agents' loads in flight at a time
+    for (int ai = 0; ai < b.A; ai += 4) {
+      int totals[4];
+      const int n = b.A - ai < 4 ? b.A - ai : 4;
+      obs_count_group_warp<4, 4>(b, env, ai, n, lane, current_step, totals);
+      if (lane < n) {
+        const int attempted = lane == 0 ? totals[0] : (lane == 1 ? totals[1] : (lane == 2 ? totals[2] : totals[3]));
+        tc[(ai + lane) * 2] = (uint16_t)(attempted < b.T ? attempted : b.T);
+        tc[(ai + lane) * 2 + 1] = (uint16_t)attempted;
+      }
+    }
+  } else {
+    for (int ai = 0; ai < b.A; ai++) {
+      const int attempted = obs_count_agent_warp(b, env, ai, lane, current_step);
+      if (lane == 0) {
+        tc[ai * 2] = (uint16_t)(attempted < b.T ? attempted : b.T);
+        tc[ai * 2 + 1] = (uint16_t)attempted;
+      }
     }
   }
   __syncwarp();
-  fold_token_stats_warp(b, env, lane);
+  // `folds` identical passes (the reference runs the pass again on an unchanged state): counted that many times
+  for (int k = 0; k < folds; k++) {
+    uint32_t keep[(MG_MAX_AGENTS + 31) / 32];
+    for (int i = lane, q = 0; i < b.A; i += 32, q++) keep[q] = *reinterpret_cast<const uint32_t*>(tc + i * 2);
+    fold_token_stats_warp(b, env, lane);
+    if (k + 1 < folds) {
+      for (int i = lane, q = 0; i < b.A; i += 32, q++) *reinterpret_cast<uint32_t*>(tc + i * 2) = keep[q];
+      __syncwarp();
+    }
+  }
 }
 
 // ---------------------------------------------------------------- reset
 // MettaGrid::MettaGrid + _init_grid + Clipper ctor (mettagrid_c.cpp:46-245, clipper.hpp:35-91),
 // from a map that the host already split into per-kind object tables (metta_b200/maps.py).
-MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er) {
+// `seeded_cached`: the env's seed is the one its cached generator state was made from (auto-reset).
+// `folds`: how many times the closing observation count is added to the token stats (see the end).
+MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er, bool seeded_cached, int folds) {
   const int32_t* cfg = b.cfg;
   const int map = er.map_idx;
   // grid: 16-byte copies (grid_stride is a multiple of 8 cells)
@@ -201,8 +225,17 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   er.rng_idx = MT_N;
   er.clip_rng_idx = MT_N;
   float* astats = b.agent_stats + (size_t)env * b.A * b.S;
-  for (int i = lane; i < b.A * b.S; i += 32) astats[i] = 0.0f;
-  for (int i = lane; i < b.A * MG_HOT_STATS; i += 32) b.hot_stats[(size_t)env * b.A * MG_HOT_STATS + i] = 0.0f;
+  {
+    const uint4 zero = {0u, 0u, 0u, 0u};
+    const size_t n = (size_t)b.A * b.S;  // the env's slice starts 16-byte aligned when A * S is a multiple of 4
+    if ((n & 3) == 0 && (reinterpret_cast<uintptr_t>(astats) & 15) == 0) {
+      for (int i = lane; i < (int)(n >> 2); i += 32) reinterpret_cast<uint4*>(astats)[i] = zero;
+    } else {
+      for (int i = lane; i < (int)n; i += 32) astats[i] = 0.0f;
+    }
+    uint4* hot = reinterpret_cast<uint4*>(b.hot_stats + (size_t)env * b.A * MG_HOT_STATS);
+    for (int i = lane; i < b.A * MG_HOT_STATS / 4; i += 32) hot[i] = zero;
+  }
   float* gstats = b.game_stats + (size_t)env * b.GS;
   for (int i = lane; i < b.GS; i += 32) gstats[i] = 0.0f;
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
@@ -260,7 +293,17 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
     chests[i] = c;
   }
   uint32_t* mt = b.rng + (size_t)env * MT_N;
-  if (lane == 0) mt_seed_serial(mt, er.seed);  // mettagrid_c.cpp:57
+  {  // std::mt19937(seed), mettagrid_c.cpp:57: 623 dependent steps on one lane, or a copy of the state made last time
+    uint4* cache = reinterpret_cast<uint4*>(b.rng_seeded + (size_t)env * MT_N);
+    uint4* st = reinterpret_cast<uint4*>(mt);
+    if (seeded_cached) {
+      for (int i = lane; i < MT_N / 4; i += 32) st[i] = cache[i];
+    } else {
+      if (lane == 0) mt_seed_serial(mt, er.seed);
+      __syncwarp();
+      for (int i = lane; i < MT_N / 4; i += 32) cache[i] = st[i];
+    }
+  }
   __syncwarp();
   EnvCtx e = make_ctx(b, env, agents, er);
   // initial inventories bypass the limits but still report through on_inventory_change
@@ -299,8 +342,9 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   // is kept. Both passes add to tokens_written/dropped/free_space, so the first is counted here.
   update_protocol_cache_warp(b, e, lane);
   write_all_asm_tokens_warp(b, env, lane, er.n_asm, 0u);
-  count_observation_pass_warp(b, env, lane, 0u);
-  if (b.has_clipper) {
+  count_observation_pass_warp(b, env, lane, 0u, folds);
+  if (!b.has_clipper) return;  // nothing below changes what observers see
+  {
     uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
     for (int i = lane; i < MT_N; i += 32) cmt[i] = mt[i];  // the clipper keeps its own copy of the rng
     const int32_t* cc = cfg + cfg[MGC_OFF_CLIPPER];
@@ -368,7 +412,7 @@ MG_GLOBAL void mg_reset_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* 
   er.seed = seeds[env];
   er.map_idx = map_idx[env];
   er.early_reset_step = 0u;
-  reset_env_warp(b, env, lane, er);
+  reset_env_warp(b, env, lane, er, false, 1);
   for (int ai = lane; ai < b.A; ai += 32) {  // _init_buffers, mettagrid_c.cpp:264-289
     const size_t g = (size_t)env * b.A + ai;
     b.rewards[g] = 0.0f;
@@ -558,15 +602,26 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       if (any) {
         const int total = lane == 0 ? w : (lane == 1 ? d : f);
         const bool exact = gs3 + (float)total < 16777216.0f;  // see fold_token_stats_warp
+        float folded = MG_FADD(gs3, (float)total);
         if (__ballot_sync(MG_FULL_MASK, lane < 3 && !exact) != 0u) {
-          fold_token_stats_warp(b, env, lane);
-        } else {
-          if (lane < 3) gs[MG_GS_TOKENS_WRITTEN + lane] = MG_FADD(gs3, (float)total);
+          // a total beyond 2^24 (tokens_free_space gets there after ~4600 arena steps): the reference's float
+          // additions round agent by agent, so they are replayed in its order, from the counts in registers
+          folded = gs3;
+          for (int ai = 0; ai < A; ai++) {
+            uint32_t pair = 0u;
 #pragma unroll
-          for (int k = 0; k < NA; k++) {
-            const int ai = lane + 32 * k;
-            if (ai < A) tc[ai * 2 + 1] = 0xFFFF;
+            for (int k = 0; k < NA; k++)
+              if ((ai >> 5) == k) pair = __shfl_sync(MG_FULL_MASK, tc_v[k], ai & 31);
+            const int written = (int)(pair & 0xFFFFu), attempted = (int)(pair >> 16);
+            if (attempted == 0xFFFF) continue;
+            folded = MG_FADD(folded, (float)(lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written)));
           }
+        }
+        if (lane < 3) gs[MG_GS_TOKENS_WRITTEN + lane] = folded;
+#pragma unroll
+        for (int k = 0; k < NA; k++) {
+          const int ai = lane + 32 * k;
+          if (ai < A) tc[ai * 2 + 1] = 0xFFFF;
         }
       }
     }
@@ -577,10 +632,11 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       __syncwarp();
       if (b.num_maps > 0) er.map_idx = (er.map_idx + b.map_stride) % b.num_maps;
       er.episodes += 1;
-      reset_env_warp(b, env, lane, er);
+      // set_buffers of the new Simulation: the initial observation nobody sees is still counted. Without a
+      // clipper it equals the constructor's own pass, which is then simply counted twice.
+      reset_env_warp(b, env, lane, er, true, b.has_clipper ? 1 : 2);
       __syncwarp();
-      // set_buffers of the new Simulation: the initial observation nobody sees is still counted
-      count_observation_pass_warp(b, env, lane, 0u);
+      if (b.has_clipper) count_observation_pass_warp(b, env, lane, 0u, 1);
       fresh = true;
       continue;  // load the new episode's state
     }

@@ -185,6 +185,55 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
   return pos_base;
 }
 
+// Count-only pass for U consecutive agents at once: the loads of all of them (position, grid cells, record
+// headers) are issued together, so that the pass costs about two memory round trips per group of agents
+// instead of per agent (an env's reset runs it for every agent of the env on one warp).
+template <int CPL, int U>
+MG_DEVICE inline void obs_count_group_warp(const MgBatch& b, int env, int ai0, int n, int lane, uint32_t current_step, int* totals) {
+  const int32_t* cfg = b.cfg;
+  const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
+  const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
+  const uint8_t* ebase = b.etok + (((size_t)env * b.rec_slots) << b.rec_shift);
+  const uint64_t kind_base = (uint64_t)b.rec_kind_base_lo | ((uint64_t)b.rec_kind_base_hi << 32);
+  const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);
+  uint32_t pos[U];
+  int n_global[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    const int ai = ai0 + (u < n ? u : 0);
+    pos[u] = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
+    n_global[u] = b.gtok[((size_t)env * b.A + ai) * MG_GTOK_STRIDE];
+  }
+  uint32_t g[U][CPL];
+#pragma unroll
+  for (int u = 0; u < U; u++)
+#pragma unroll
+    for (int j = 0; j < CPL; j++) {
+      const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
+      const uint32_t r = (pos[u] & 0xFFFFu) - (uint32_t)hr + (loc >> 4), c = (pos[u] >> 16) - (uint32_t)wr + (loc & 0xFu);
+      g[u][j] = (u < n && loc != 0xFFu && r < (uint32_t)b.H && c < (uint32_t)b.W) ? grid[r * (uint32_t)b.W + c] : 0u;
+    }
+  uint2 h[U][CPL];
+#pragma unroll
+  for (int u = 0; u < U; u++)
+#pragma unroll
+    for (int j = 0; j < CPL; j++) {
+      h[u][j].x = h[u][j].y = 0u;
+      if (g[u][j] != 0u) {
+        const uint32_t slot = ((uint32_t)(kind_base >> (MG_GRID_KIND(g[u][j]) * 16u)) & 0xFFFFu) + MG_GRID_INDEX(g[u][j]);
+        h[u][j] = *reinterpret_cast<const uint2*>(ebase + ((size_t)slot << b.rec_shift));
+      }
+    }
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    int mine = 0;
+#pragma unroll
+    for (int j = 0; j < CPL; j++)
+      if (g[u][j] != 0u) mine += (int)(h[u][j].x & 0xFFu) + (h[u][j].y > current_step ? 1 : 0);  // + the cooldown_remaining token while it is > 0
+    totals[u] = n_global[u] + MG_WARP_SUM(mine);
+  }
+}
+
 // Count-only pass used by the reset path (any window size).
 MG_DEVICE inline int obs_count_agent_warp(const MgBatch& b, int env, int ai, int lane, uint32_t current_step) {
   const int cpl = (b.obs_cells + 31) >> 5;

@@ -40,6 +40,7 @@
 #endif
 #define MG_LD_L2(p) __ldcg(p) /* read at L2: for words other lanes may have bumped with atomics */
 #define MG_NANOSLEEP(ns) __nanosleep(ns)
+#define MG_WARP_SUM(v) ((int)__reduce_add_sync(0xFFFFFFFFu, (int)(v))) /* one redux.sync instead of five shuffle rounds */
 #define MG_ROLLED _Pragma("unroll 1")
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif

@@ -150,6 +150,7 @@ struct MgBatch {
   float* game_stats;           // [N][GS]
   uint32_t* rng;               // [N][624]
   uint32_t* clip_rng;          // [N][624] (only with a clipper)
+  uint32_t* rng_seeded;        // [N][624] the generator right after std::mt19937(seed): an auto-reset (same seed) copies it instead of re-seeding
   uint8_t* etok;               // [N][rec_slots][1 << rec_shift] token records (see above)
   uint8_t* gtok;               // [N][A][MG_GTOK_STRIDE]: byte 0 = n, then n (location, feature, value) triples: the global tokens of an agent
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel

@@ -255,5 +255,54 @@ def crowd_48() -> tuple[MettaGridConfig, np.ndarray]:
     return _crowded(48, _populate(rows, 48, seed=2))
 
 
+def clipper_spread() -> tuple[MettaGridConfig, np.ndarray]:
+    """A clipper that actually picks: 14 trackable assemblers spread over a 17x21 map, clip_period 6, one
+    assembler starting clipped (so infection weights exist from step 0), cheap unclipping protocols and agents
+    holding the items for them (random walkers unclip now and then, which moves assemblers between the
+    clipper's border / unclipped sets): Clipper::pick_assembler_to_clip, clip_assembler, on_unclip_assembler
+    (systems/clipper.hpp:140-238)."""
+    game = {
+        "resource_names": ["energy", "carbon", "decoder", "modulator", "heart"],
+        "num_agents": 6,
+        "max_steps": 0,
+        "obs": {"width": 11, "height": 11, "num_tokens": 100},
+        "agent": {"inventory": {"default_limit": 200, "initial": {"decoder": 60, "modulator": 60, "energy": 20}}, "rewards": {"inventory": {"heart": 1.0}}},
+        "actions": {"noop": {}, "move": {}, "change_vibe": {"vibes": _vibes(["default", "gear"])}},
+        "clipper": {
+            "unclipping_protocols": [
+                {"input_resources": {"decoder": 1}, "cooldown": 1},
+                {"input_resources": {"modulator": 1}, "cooldown": 2},
+                {"input_resources": {"energy": 1}, "cooldown": 1},
+            ],
+            "clip_period": 6,
+            "scaled_cutoff_distance": 2,
+        },
+        "objects": {
+            "wall": {"pydantic_type": "wall", "name": "wall"},
+            "mine": {"pydantic_type": "assembler", "name": "mine", "protocols": [{"output_resources": {"carbon": 1}, "cooldown": 3}]},
+            "seed": {"pydantic_type": "assembler", "name": "seed", "start_clipped": True,
+                     "protocols": [{"output_resources": {"energy": 1}, "cooldown": 2}]},
+            "altar": {"pydantic_type": "assembler", "name": "altar", "clip_immune": True,
+                      "protocols": [{"input_resources": {"carbon": 1}, "output_resources": {"heart": 1}, "cooldown": 1}]},
+        },
+    }
+    legend = {"#": "wall", ".": "empty", "M": "mine", "S": "seed", "A": "altar", "@": "agent.agent"}
+    rows = [
+        "#####################",
+        "#.M....@...M......M.#",
+        "#...................#",
+        "#....M.....@....M...#",
+        "#.@.......S.........#",
+        "#...M..........M....#",
+        "#.........A.....@...#",
+        "#..M......M.........#",
+        "#.....@........M....#",
+        "#...........M.......#",
+        "#.M.......@......M..#",
+        "#####################",
+    ]
+    return MettaGridConfig(game=game), ascii_map(rows, legend)
+
+
 SCENARIOS = {"kitchen_sink": kitchen_sink, "tiny_truncating": tiny_truncating, "clipped_start": clipped_start,
-             "dense_conflict": dense_conflict, "crowd_48": crowd_48}
+             "dense_conflict": dense_conflict, "crowd_48": crowd_48, "clipper_spread": clipper_spread}

@@ -148,6 +148,8 @@ static inline unsigned __match_any_sync(unsigned, int v) {
   return m;
 }
 static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
+static inline int emu_warp_sum(int v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o); return v; }
+#define MG_WARP_SUM(v) emu_warp_sum((int)(v))
 static inline int atomicMax(int* p, int v) { int o = *p; if (v > o) *p = v; return o; }
 static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
 static inline long long clock64() { return 0; }

@@ -433,3 +433,19 @@ def test_fused_mode_matches_oracle(name, n, steps, lib, monkeypatch):
     ls.compare_state()
     ls.batch.sync()
     ls.close()
+
+
+def test_token_stats_beyond_2_pow_24(lib):
+    """tokens_free_space passes 2^24 after ~4700 arena steps; from there the reference's float additions
+    round agent by agent (mettagrid_c.cpp:552-554) and the kernel replays them in that order."""
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    n = 3
+    ls = Lockstep(cfg, arena_maps(low, 3, seed=12), num_envs=n, seeds=np.arange(n) + 61, cuda=True)
+    rng = np.random.RandomState(14)
+    for s in range(5600):
+        ls.step(rng.randint(0, 5, size=n * 24), compare=(s % 400 == 0))
+    ls.compare_outputs()
+    ls.compare_state()
+    assert ls.batch.read_game_stats()[:, L.MG_GS_TOKENS_FREE_SPACE].min() > 2.0**24
+    ls.close()
