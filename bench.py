@@ -265,20 +265,35 @@ class Rig:
         self.term = torch.zeros(NA, dtype=torch.uint8, device=dev)
         self.trunc = torch.zeros(NA, dtype=torch.uint8, device=dev)
         self.rew = torch.zeros(NA, dtype=torch.float32, device=dev)
-        g = torch.Generator().manual_seed(gen_seed)
-        self.ring = 16
-        self.act_ring = torch.randint(0, n_actions, (self.ring, NA), generator=g, dtype=torch.int32).to(dev)
-        self.act = self.act_ring[0].clone()  # the bound action buffer, refreshed from the ring every step (device copy)
+        # actions: uniformly random and never repeated (a short cycle of pre-generated actions would give every
+        # agent a fixed net drift per cycle and pile the agents up against the walls over a long run)
+        self.n_actions = n_actions
+        self.gen = torch.Generator(device=dev).manual_seed(1234 + gen_seed)
+        self.act = torch.zeros(NA, dtype=torch.int32, device=dev)  # the bound action buffer
+        self.queue = []  # pre-generated action tensors for timed regions (the policy's output, resident in HBM)
         self.batch.set_buffers(self.obs.data_ptr(), self.term.data_ptr(), self.trunc.data_ptr(), self.rew.data_ptr(), self.act.data_ptr())
         self.batch.reset(seeds, maps)
         self.stream = torch.cuda.current_stream(dev).cuda_stream
         self.flush_mode = flush_mode
-        self.i = 0
+
+    def fresh_actions(self, out=None):
+        torch = self.torch
+        a = torch.randint(0, self.n_actions, (self.N * self.A,), generator=self.gen, dtype=torch.int32, device=self.dev)
+        if out is None:
+            return a
+        out.copy_(a, non_blocking=True)
+        return out
+
+    def prepare(self, k: int):
+        """Pre-generate the actions of the next k steps."""
+        self.queue = [self.fresh_actions() for _ in range(k)]
 
     def one_step(self):
-        self.act.copy_(self.act_ring[self.i % self.ring], non_blocking=True)  # what a policy's sampling kernel would write
+        if self.queue:
+            self.act.copy_(self.queue.pop(), non_blocking=True)  # what a policy's sampling kernel would write
+        else:
+            self.fresh_actions(self.act)
         self.batch.step(self.stream)
-        self.i += 1
 
     def stagger(self, max_steps: int, first_global_env: int):
         """Cut every env's first episode at its own offset and roll the batch forward by one episode length."""
@@ -292,6 +307,7 @@ class Rig:
         torch = self.torch
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(k)]
         ends = [torch.cuda.Event(enable_timing=True) for _ in range(k)]
+        self.prepare(k)
         torch.cuda.synchronize()
         for i in range(k):
             flush(i)
@@ -468,6 +484,8 @@ def run_ours(args):
     episodes_timed = float(batch.read_episode_accum()[0]) - episodes_before
     # ---- free-running: K steps back to back (warm L2, launch gaps included)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rig.prepare(args.steps)
+    torch.cuda.synchronize()
     e0.record()
     for _ in range(args.steps):
         rig.one_step()
@@ -478,7 +496,7 @@ def run_ours(args):
     # ---- per-kernel durations (whole batch in one launch each, events on the launch stream, L2 flushed)
     act_ms, obs_ms = [], []
     for i in range(min(args.steps, 50)):
-        rig.act.copy_(rig.act_ring[i % rig.ring])
+        rig.fresh_actions(rig.act)
         flush_l2(i)
         torch.cuda.synchronize()
         a_ms, o_ms = batch.profile_step(rig.stream)
@@ -486,23 +504,23 @@ def run_ours(args):
     # ---- end to end through the host-buffer call on the same (staggered) batch: page-locked H2D of the actions,
     # the step, D2H of everything a rollout worker reads
     pin = lambda shape, dtype: torch.empty(shape, dtype=dtype, pin_memory=True).numpy()  # noqa: E731
-    h_act = pin((rig.ring, N * A), torch.int32)
-    h_act[...] = np.random.RandomState(rank).randint(0, 5, size=(rig.ring, N * A))
+    e2e_steps = max(3, min(args.steps, 30))
+    h_act = pin((2 * (e2e_steps + 3), N * A), torch.int32)  # one fresh row of actions per e2e step
+    h_act[...] = np.random.RandomState(rank).randint(0, 5, size=h_act.shape)
     h_obs = pin((N * A, T, 3), torch.uint8); h_rew = pin((N * A,), torch.float32)
     h_term = pin((N * A,), torch.uint8); h_trunc = pin((N * A,), torch.uint8)
-    e2e_steps = max(3, min(args.steps, 30))
-
     def e2e_run(changed_rows_only):
         batch.set_host_export(changed_rows_only)
+        base = (e2e_steps + 3) if changed_rows_only else 0
         for i in range(3):
-            batch.step_host(h_act[i % rig.ring], h_obs, h_rew, h_term, h_trunc)
+            batch.step_host(h_act[base + i], h_obs, h_rew, h_term, h_trunc)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         b0 = batch.transfer_bytes()
         t0 = time.perf_counter()
         for i in range(e2e_steps):
-            batch.step_host(h_act[i % rig.ring], h_obs, h_rew, h_term, h_trunc)
+            batch.step_host(h_act[base + 3 + i], h_obs, h_rew, h_term, h_trunc)
         torch.cuda.synchronize()
         secs = time.perf_counter() - t0
         b1 = batch.transfer_bytes()

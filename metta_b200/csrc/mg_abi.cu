@@ -442,6 +442,12 @@ int mg_load_maps(void* h, int32_t num_maps, const uint16_t* grids, const int32_t
   CUDA_TRY(cudaMemcpy(d_as, asms, M * b.max_asm * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(d_nc, n_chest, M * sizeof(int32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(d_ch, chests, M * b.max_chest * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  {  // first-observation token counts per map: computed by the first env that starts an episode on the map
+    uint16_t* d_t0; uint32_t* d_t0v;
+    TRY(dev_alloc(e, &d_t0, M * b.A));
+    TRY(dev_alloc(e, &d_t0v, M));
+    b.pool_tok0 = d_t0; b.pool_tok0_valid = d_t0v;
+  }
   b.pool_grid = d_grid; b.pool_agents = d_ag; b.pool_n_asm = d_na; b.pool_asm = d_as; b.pool_n_chest = d_nc; b.pool_chest = d_ch;
   b.num_maps = num_maps;
   e->maps_loaded = true;
@@ -502,12 +508,15 @@ static int begin_obs_pass(MgEnvs* e, cudaStream_t s) {
   return MG_OK;
 }
 
-static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask) {
+static int launch_obs(MgEnvs* e, cudaStream_t s, const uint8_t* mask, bool after_step = false) {
   if (mask == nullptr) {
     const int rc = begin_obs_pass(e, s);
     if (rc != MG_OK) return rc;
   }
-  return launch_obs_slice(e, e->b, s, mask);
+  if (!after_step) return launch_obs_slice(e, e->b, s, mask);
+  MgBatch b = e->b;
+  b.after_step = 1;
+  return launch_obs_slice(e, b, s, mask);
 }
 
 static int launch_step_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
@@ -555,6 +564,7 @@ static int enqueue_chunked_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* 
     cudaStream_t cs = e->chunk_stream[c];
     CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_fork, 0));
     if ((rc = launch_step_slice(e, slice, cs)) != MG_OK) return rc;
+    slice.after_step = 1;
     if ((rc = launch_obs_slice(e, slice, cs, nullptr)) != MG_OK) return rc;
     if (ht != nullptr && (rc = launch_export(e, slice, cs, *ht, slice.env_begin * slice.A, slice.env_end * slice.A)) != MG_OK) return rc;
     CUDA_TRY(cudaEventRecord(e->ev_join[c], cs));
@@ -582,7 +592,8 @@ static int launch_obs_queue(MgEnvs* e, const MgBatch& b, cudaStream_t s, int cta
 // Queue mode: [begin] -> { step kernel (one env per CTA) -> late observation CTAs } beside { early
 // observation CTAs }, joined back into `s`. Observation tasks are handed out in the order envs finish.
 static int enqueue_queue_step(MgEnvs* e, cudaStream_t s) {
-  const MgBatch& b = e->b;
+  MgBatch b = e->b;
+  b.after_step = 1;
   int rc;
   if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
   MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
@@ -642,7 +653,8 @@ static bool fused_supported(const MgBatch& b) {
 }
 
 static int enqueue_fused_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* ht) {
-  const MgBatch& b = e->b;
+  MgBatch b = e->b;
+  b.after_step = 1;
   int rc;
   if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
   MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
@@ -724,7 +736,7 @@ int mg_step(void* h, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   if (e->chunks <= 1 && e->step_mode == 0) {
     int rc = launch_step_slice(e, e->b, s);
-    return rc != MG_OK ? rc : launch_obs(e, s, nullptr);
+    return rc != MG_OK ? rc : launch_obs(e, s, nullptr, true);
   }
 #ifdef MG_SIMT_EMU
   return enqueue_chunked_step(e, s);
@@ -755,7 +767,7 @@ int mg_profile_step(void* h, void* stream, float* out_ms) {
   CUDA_TRY(cudaEventRecord(ev[0], s));
   TRY(launch_step_slice(e, b, s));
   CUDA_TRY(cudaEventRecord(ev[1], s));
-  TRY(launch_obs(e, s, nullptr));
+  TRY(launch_obs(e, s, nullptr, true));
   CUDA_TRY(cudaEventRecord(ev[2], s));
   CUDA_TRY(cudaEventSynchronize(ev[2]));
   CUDA_TRY(cudaEventElapsedTime(&out_ms[0], ev[0], ev[1]));
@@ -836,7 +848,7 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   if (sparse) {
     if (e->chunks <= 1 && e->step_mode == 0) {
       TRY(launch_step_slice(e, b, s));
-      TRY(launch_obs(e, s, nullptr));
+      TRY(launch_obs(e, s, nullptr, true));
       TRY(launch_export(e, b, s, ht, 0, (int)NA));
     } else {
       if (e->hgraph_dirty || memcmp(&ht, &e->hgraph_targets, sizeof(ht)) != 0) {
@@ -1000,6 +1012,11 @@ int mg_read(void* h, int32_t what, void* host_out, int64_t nbytes) {
     CUDA_TRY(cudaDeviceSynchronize());
   }
   CUDA_TRY(cudaMemcpy(host_out, p, bytes, cudaMemcpyDeviceToHost));
+  if (what == MG_ST_EPISODE_ACCUM) {  // kept as 48.16 fixed point on the device, handed out as doubles
+    long long* raw = reinterpret_cast<long long*>(host_out);
+    double* out = reinterpret_cast<double*>(host_out);
+    for (size_t i = 0; i < bytes / sizeof(double); i++) out[i] = (double)raw[i] / 65536.0;
+  }
   if (what == MG_ST_AGENT_STATS) {  // slots 0..MG_HOT_STATS-1 of every agent live in an array of their own
     const size_t NA = (size_t)e->b.num_envs * e->b.A;
     std::vector<float> hot(NA * MG_HOT_STATS);

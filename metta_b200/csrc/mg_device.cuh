@@ -140,8 +140,8 @@ MG_DEVICE inline void on_inventory_change(EnvCtx& e, const InvView& v, int item,
     AgentRec* a = &e.ag[v.owner_idx];
     a->pad0 = 1;  // token record is stale
     int amount = a->amt[item];
-    if (delta > 0) MG_RED_ADD(&st[MG_AS_GAINED + item], (float)delta);
-    else MG_RED_ADD(&st[MG_AS_LOST + item], (float)(-delta));
+    if (delta > 0) MG_STAT_BUMP(&st[MG_AS_GAINED + item], (float)delta);
+    else MG_STAT_BUMP(&st[MG_AS_LOST + item], (float)(-delta));
     st[MG_AS_AMOUNT + item] = (float)amount;
     const int32_t* grp = e.cfg + e.cfg[MGC_OFF_GROUPS] + a->group * MG_GRP_WORDS;
     if (grp[MG_GRP_DIVERSITY + item]) {
@@ -776,24 +776,31 @@ MG_DEVICE MG_NOINLINE bool try_transfer(EnvCtx& e, int actor, uint16_t target_ce
   return true;
 }
 
+// Results of action_begin. MG_ACT_USE_PENDING: the action came down to using assembler *asm_out and the caller
+// asked to run that use itself (with the whole warp, assembler_use_warp); nothing of the use has happened yet.
+#define MG_ACT_FAIL 0
+#define MG_ACT_OK 1
+#define MG_ACT_USE_PENDING 2
+#define MG_ACT_FROZEN 3 /* counted and done: no motion bookkeeping, no success/failure stats (action_handler.hpp:100-110) */
+
 // Move::_handle_action, move.hpp:74-141
-MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
+MG_DEVICE inline int handle_move(EnvCtx& e, int actor, int arg, bool defer_use, int* asm_out) {
   AgentRec* ac = &e.ag[actor];
   // orientation.hpp:28-48: N,S,W,E,NW,NE,SW,SE packed as 2-bit (delta+1) fields
   int dr = (int)((0xA058u >> (2 * arg)) & 3u) - 1;   // -1,+1,0,0,-1,-1,+1,+1
   int dc = (int)((0x8885u >> (2 * arg)) & 3u) - 1;   //  0, 0,-1,+1,-1,+1,-1,+1
   int tr = (int)ac->r + dr, tc = (int)ac->c + dc;
-  if (tr < 0 || tc < 0 || tr >= e.H || tc >= e.W) return false;  // u16 wrap + is_valid_location
+  if (tr < 0 || tc < 0 || tr >= e.H || tc >= e.W) return MG_ACT_FAIL;  // u16 wrap + is_valid_location
   uint16_t target = grid_at(e, tr, tc);
   int handler = e.cfg[e.cfg[MGC_OFF_VIBES] + ac->vibe * MG_VIBE_WORDS + MG_VIBE_HANDLER];
-  if (handler == MG_HANDLER_ATTACK && try_attack(e, actor, target)) return true;
-  if (handler == MG_HANDLER_TRANSFER && try_transfer(e, actor, target)) return true;
+  if (handler == MG_HANDLER_ATTACK && try_attack(e, actor, target)) return MG_ACT_OK;
+  if (handler == MG_HANDLER_TRANSFER && try_transfer(e, actor, target)) return MG_ACT_OK;
   if (target == 0) {  // Grid::move_object, core/grid.hpp:70-83
     e.grid[tr * e.W + tc] = (uint16_t)(0x4000 | actor);
     e.grid[(int)ac->r * e.W + (int)ac->c] = 0;
     ac->r = (uint16_t)tr;
     ac->c = (uint16_t)tc;
-    return true;
+    return MG_ACT_OK;
   }
   int kind = MG_GRID_KIND(target), idx = MG_GRID_INDEX(target);
   if (kind == MG_GK_AGENT) {
@@ -806,36 +813,42 @@ MG_DEVICE inline bool handle_move(EnvCtx& e, int actor, int arg) {
       ac->r = (uint16_t)tr;
       ac->c = (uint16_t)tc;
       *agent_stat(e, actor, MG_AS_SWAP) += 1.0f;
-      return true;
+      return MG_ACT_OK;
     }
-    return false;  // Agent::onUse, agent.cpp:179-185
+    return MG_ACT_FAIL;  // Agent::onUse, agent.cpp:179-185
   }
-  if (kind == MG_GK_ASM) return assembler_on_use(e, idx, actor);
-  if (kind == MG_GK_CHEST) return chest_on_use(e, idx, actor);
-  return false;  // walls are not Usable
+  if (kind == MG_GK_ASM) {
+    if (defer_use) { *asm_out = idx; return MG_ACT_USE_PENDING; }
+    return assembler_on_use(e, idx, actor) ? MG_ACT_OK : MG_ACT_FAIL;
+  }
+  if (kind == MG_GK_CHEST) return chest_on_use(e, idx, actor) ? MG_ACT_OK : MG_ACT_FAIL;
+  return MG_ACT_FAIL;  // walls are not Usable
 }
 
-// ActionHandler::handle_action, action_handler.hpp:99-153
-MG_DEVICE MG_NOINLINE bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
+// ActionHandler::handle_action, action_handler.hpp:99-153, in two halves around the handler's own work, so
+// that an assembler use can be run by the whole warp in between (assembler_use_warp).
+MG_DEVICE MG_NOINLINE int action_begin(EnvCtx& e, int actor, int kind, int arg, bool defer_use, int* asm_out) {
   AgentRec* ac = &e.ag[actor];
   if (ac->frozen != 0) {
     *agent_stat(e, actor, MG_AS_FROZEN_TICKS) += 1.0f;
     if (ac->frozen > 0) { ac->frozen -= 1; ac->pad0 = 1; }
-    return false;
+    return MG_ACT_FROZEN;
   }
   const int32_t* res = e.cfg + e.cfg[MGC_OFF_ACTION_RES] + kind * MG_ACTRES_WORDS;
-  bool has = true;
   MG_ROLLED
   for (uint32_t m = e.req_mask[kind]; m != 0u; m &= m - 1u) {
     const int i = __ffs((int)m) - 1;
-    if ((int)ac->amt[i] < (res[MG_ACTRES_REQUIRED + i] & 0xFFFF)) { has = false; break; }
+    if ((int)ac->amt[i] < (res[MG_ACTRES_REQUIRED + i] & 0xFFFF)) return MG_ACT_FAIL;
   }
-  bool success = false;
-  if (has) {
-    if (kind == MG_ACTION_NOOP) success = true;
-    else if (kind == MG_ACTION_MOVE) success = handle_move(e, actor, arg);
-    else { ac->vibe = (uint8_t)arg; ac->pad0 = 1; success = true; }  // change_vibe.hpp:48-51
-  }
+  if (kind == MG_ACTION_NOOP) return MG_ACT_OK;
+  if (kind == MG_ACTION_MOVE) return handle_move(e, actor, arg, defer_use, asm_out);
+  ac->vibe = (uint8_t)arg;  // change_vibe.hpp:48-51
+  ac->pad0 = 1;
+  return MG_ACT_OK;
+}
+
+MG_DEVICE MG_NOINLINE void action_end(EnvCtx& e, int actor, int kind, bool success) {
+  AgentRec* ac = &e.ag[actor];
   if (ac->r == ac->prev_r && ac->c == ac->prev_c) {
     ac->steps_without_motion += 1;
     float* mx = agent_stat(e, actor, MG_AS_MAX_STEPS_WITHOUT_MOTION);
@@ -848,6 +861,7 @@ MG_DEVICE MG_NOINLINE bool handle_action(EnvCtx& e, int actor, int kind, int arg
   if (success) {
     *agent_stat(e, actor, MG_AS_ACTION_SUCCESS + kind) += 1.0f;
     if (e.con_mask[kind] != 0u) {
+      const int32_t* res = e.cfg + e.cfg[MGC_OFF_ACTION_RES] + kind * MG_ACTRES_WORDS;
       InvView ai = agent_inv(e, actor);
       MG_ROLLED
       for (uint32_t m = e.con_mask[kind]; m != 0u; m &= m - 1u) {
@@ -859,7 +873,144 @@ MG_DEVICE MG_NOINLINE bool handle_action(EnvCtx& e, int actor, int kind, int arg
     *agent_stat(e, actor, MG_AS_ACTION_FAILED + kind) += 1.0f;
     *agent_stat(e, actor, MG_AS_ACTION_FAILED_ANY) += 1.0f;
   }
-  return success;
+}
+
+// ---------------------------------------------------------------- assembler use by the whole warp
+// Inventory::update (inventory.cpp:37-85) for an agent, all 32 lanes with the same arguments: the limit's
+// member sum and its modifier bonus are one warp sum each (a lane per resource) instead of two loops.
+MG_DEVICE inline int inv_update_warp(EnvCtx& e, int actor, int item, int attempted_delta, int lane) {
+  InvView v = agent_inv(e, actor);
+  const int initial = v.amt[item];
+  int max = 65535;
+  const int limit = v.invcfg[MG_INVCFG_ITEM_LIMIT + item];
+  if (limit >= 0) {
+    const uint32_t members = (uint32_t)v.masks[limit], mods = (uint32_t)v.masks[MG_MAX_LIMITS + limit];
+    const int mine = lane < MG_MAX_RESOURCES ? (int)v.amt[lane] : 0;
+    const int used = MG_WARP_SUM(((members >> lane) & 1u) ? mine : 0) & 0xFFFF;
+    int effective = v.invcfg[MG_INVCFG_LIMIT_BASE + limit];
+    if (mods != 0u) effective += MG_WARP_SUM(((mods >> lane) & 1u) ? mine * v.invcfg[MG_INVCFG_LIMIT_MOD + limit * RS + lane] : 0);
+    effective = effective < 0 ? 0 : (effective > 65535 ? 65535 : effective);
+    int others = used - initial;
+    others = others < 0 ? 0 : others;
+    max = effective - others;
+    max = max < 0 ? 0 : max;
+  }
+  const int want = initial + attempted_delta;
+  const int clamped = want < 0 ? 0 : (want > max ? max : want);
+  const int delta = clamped - initial;
+  __syncwarp();  // every lane has read the amounts before lane 0 changes them
+  if (lane == 0) {
+    if (clamped == 0) {
+      if (initial > 0) order_erase(v.order, item);
+    } else if (initial == 0) {
+      order_push_front(v.order, item);
+    }
+    v.amt[item] = (uint16_t)clamped;
+    if (delta != 0) on_inventory_change(e, v, item, delta);
+    if (delta < 0 && v.invcfg[MG_INVCFG_IS_MODIFIER + item]) inv_enforce_all_limits(e, v, 0);
+  }
+  __syncwarp();
+  return delta;
+}
+
+// Assembler::onUse (assembler.hpp:455-526) called by all 32 lanes with the same arguments. The common case
+// -- the actor is the only agent around the assembler, which is neither clipped, nor cooling down, nor
+// searching chests -- runs here with a lane per ring cell / per protocol item; everything else is handed
+// to assembler_on_use on lane 0, unchanged. `alone`: the caller knows that no other agent stands next to
+// the assembler (step_phase_decide, rule 3).
+MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor, bool alone, int lane) {
+#ifdef MG_TIMING
+  const long long tk0 = clock64();
+#endif
+  AsmRec* a = &e.asms[asm_idx];
+  const int32_t* t = asm_type_cfg(e.cfg, a->cell);
+  const uint32_t max_uses = (uint32_t)t[MG_ASM_MAX_USES];
+  if (max_uses > 0 && a->uses_count >= max_uses) return false;
+  const uint32_t remaining = a->cooldown_end <= e.current_step ? 0u : a->cooldown_end - e.current_step;
+  const bool partial = t[MG_ASM_ALLOW_PARTIAL] != 0;
+  if (remaining > 0 && !partial) return false;
+  bool simple = remaining == 0 && (a->flags & MG_ASMF_CLIPPED) == 0 && t[MG_ASM_CHEST_DISTANCE] <= 0;
+  if (simple && !alone) {  // who stands in the ring? One cell per lane.
+    bool agent_here = false;
+    if (lane < 8) {
+      const int rr = (int)a->r + (int)((0xA940u >> (2 * lane)) & 3u) - 1, cc = (int)a->c + (int)((0x9224u >> (2 * lane)) & 3u) - 1;
+      if (rr >= 0 && cc >= 0 && rr < e.H && cc < e.W) agent_here = MG_GRID_KIND(grid_at(e, rr, cc)) == MG_GK_AGENT;
+    }
+    simple = __popc(__ballot_sync(MG_FULL_MASK, agent_here)) == 1;
+  }
+  int pi = -1;
+  const int32_t* p = nullptr;
+  if (simple) {
+    pi = asm_protocol_for(e, a, (uint64_t)e.ag[actor].vibe, 1);
+    if (pi < 0) return false;
+    p = proto_cfg(e.cfg, pi);
+  }
+  if (!simple) {  // the general case, as before
+    int ok = 0;
+    __syncwarp();  // every lane has read the assembler's record before lane 0 changes it
+    if (lane == 0) ok = assembler_on_use(e, asm_idx, actor) ? 1 : 0;
+    return __shfl_sync(MG_FULL_MASK, ok, 0) != 0;
+  }
+  // one inventory pays (the actor) and, with a single agent around, the same one receives
+  // (get_output_inventories :198-223: the actor unless vibing participants claim the slots, and the only
+  // candidate is the actor)
+  const int32_t* lin = p + MG_PROTO_INPUTS;
+  const int32_t* lout = p + MG_PROTO_OUTPUTS;
+  const int n_in = lin[MG_LIST_N], n_out = lout[MG_LIST_N];
+  const AgentRec* ac = &e.ag[actor];
+  int my_item = 0, my_amount = 0;  // lanes [0, n_in): inputs; lanes [16, 16 + n_out): outputs
+  if (lane < n_in) { my_item = lin[MG_LIST_ITEM(lane)]; my_amount = (int)(uint16_t)lin[MG_LIST_VAL(lane)]; }
+  if (lane >= 16 && lane - 16 < n_out) { my_item = lout[MG_LIST_ITEM(lane - 16)]; my_amount = (int)(uint16_t)lout[MG_LIST_VAL(lane - 16)]; }
+  const bool short_of = lane < n_in && (int)ac->amt[my_item] < my_amount;  // can_afford_protocol :124-137
+  if (__ballot_sync(MG_FULL_MASK, short_of) != 0u) return false;
+  const bool gives = lane >= 16 && lane - 16 < n_out && my_amount > 0;
+  const uint32_t giving = __ballot_sync(MG_FULL_MASK, gives);
+  if (giving != 0u) {  // can_receive_output :143-171: room for at least one unit of some output
+    InvView v = agent_inv(e, actor);
+    const bool room = gives && inv_free_space(v, my_item) >= 1;
+    if (__ballot_sync(MG_FULL_MASK, room) == 0u) return false;
+  }
+#ifdef MG_TIMING
+  const long long tk1 = clock64();
+#endif
+  for (int i = 0; i < n_in; i++) {  // consume_resources_for_protocol :228-234
+    const int item = __shfl_sync(MG_FULL_MASK, my_item, i), amount = __shfl_sync(MG_FULL_MASK, my_amount, i);
+    inv_update_warp(e, actor, item, -amount, lane);
+  }
+  for (int i = 0; i < n_out; i++) {  // give_output_for_protocol :174-184
+    const int item = __shfl_sync(MG_FULL_MASK, my_item, 16 + i), amount = __shfl_sync(MG_FULL_MASK, my_amount, 16 + i);
+    const int distributed = inv_update_warp(e, actor, item, amount, lane);
+    if (distributed > 0 && lane == 0) MG_RED_ADD(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
+  }
+#ifdef MG_TIMING
+  const long long tk2 = clock64();
+#endif
+  if (lane == 0) {
+    a->cooldown_duration = (uint32_t)(uint16_t)p[MG_PROTO_COOLDOWN];
+    a->cooldown_end = e.current_step + a->cooldown_duration;
+    a->uses_count++;
+  }
+  __syncwarp();
+  if (e.asm_records_on_use) write_asm_tokens_warp(*e.batch, a, e.current_step, token_record(*e.batch, e.env, MG_GK_ASM, (uint32_t)asm_idx), lane);
+#ifdef MG_TIMING
+  if (lane == 0 && e.batch->dbg != nullptr) {  // set-up and checks | (unused) | consume and give | record
+    uint32_t* d = e.batch->dbg + (size_t)e.env * 16 + 12;
+    const long long tk3 = clock64();
+    atomicAdd(d + 0, (uint32_t)(tk1 - tk0));
+    atomicAdd(d + 2, (uint32_t)(tk2 - tk1));
+    atomicAdd(d + 3, (uint32_t)(tk3 - tk2));
+  }
+#endif
+  return true;
+}
+
+// The whole of handle_action on one lane (paths that never hand an assembler use to the warp).
+MG_DEVICE inline bool handle_action(EnvCtx& e, int actor, int kind, int arg) {
+  int unused = -1;
+  const int code = action_begin(e, actor, kind, arg, false, &unused);
+  if (code == MG_ACT_FROZEN) return false;
+  action_end(e, actor, kind, code == MG_ACT_OK);
+  return code == MG_ACT_OK;
 }
 
 // inventory regeneration for one agent, mettagrid_c.cpp:625-640
@@ -899,7 +1050,7 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
       v = (float)a->amt[as - MG_AS_AMOUNT];
     } else if (as >= 0) {
       const float* sp = agent_stat(e, ai, as);
-      v = as < MG_HOT_STATS ? *sp : MG_LDCG(sp);
+      v = as < MG_HOT_STATS ? *sp : MG_LD_L2(sp);  // some of these slots are bumped with reductions (at L2)
     }
     v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LD_L2(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));

@@ -15,6 +15,8 @@
 #include "mg_obs.cuh"
 #include "mg_rng.cuh"
 
+#include <math.h>
+
 // -DMG_TIMING: per-env cycle counts of the step kernel's phases in EnvRec::spare (tuning builds only)
 #ifdef MG_TIMING
 #define MG_TICK(i) do { const long long now__ = clock64(); tick_acc[i] += (uint32_t)(now__ - tick_last); tick_last = now__; } while (0)
@@ -56,6 +58,31 @@ struct StepSmem {
   EnvRec er;
   EnvCtx ctx;  // warp-uniform; lives here so that passing it to out-of-line functions costs no stack traffic
 };
+
+// n 16-byte words from src to dst by one warp, eight loads in flight per lane (a plain copy loop waits for
+// every load before it issues the next).
+MG_DEVICE inline void copy16_warp(uint4* dst, const uint4* src, int n, int lane) {
+  for (int i0 = 0; i0 < n; i0 += 32 * 8) {
+    uint4 w[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int i = i0 + lane + 32 * k;
+      if (i < n) w[k] = src[i];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int i = i0 + lane + 32 * k;
+      if (i < n) dst[i] = w[k];
+    }
+  }
+}
+
+// Ask for a whole range at once (one request per 128-byte line, spread over the lanes): what follows reads it
+// in dependent steps, and would otherwise pay an HBM round trip for each of them.
+MG_DEVICE inline void prefetch_range_warp(const void* p, size_t bytes, int lane) {
+  const char* c = reinterpret_cast<const char*>(p);
+  for (size_t off = (size_t)lane * 128; off < bytes; off += 32 * 128) MG_PREFETCH_TO_L2(c + off);
+}
 
 // An EnvRec moves as four 16-byte words, not field by field.
 MG_DEVICE inline void copy_env_rec(EnvRec* dst, const EnvRec* src) {
@@ -168,10 +195,20 @@ MG_DEVICE MG_NOINLINE void write_all_asm_tokens_warp(const MgBatch& b, int env, 
 
 // One observation pass that only counts tokens (nothing is written): the reference runs such
 // passes on buffers nobody reads (see reset_env_warp), but their token counts stay in the stats.
-MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step, int folds) {
+// `map`: >= 0 when the pass looks at the untouched start of an episode on that pool map and nothing but the
+// map decides what the agents see (no clipper): the counts are then kept per map and reused.
+MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env, int lane, uint32_t current_step, int folds, int map) {
   __syncwarp();
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
-  if (b.obs_cells <= 128) {  // four agents' loads in flight at a time
+  const bool cacheable = map >= 0 && b.pool_tok0 != nullptr;
+  if (cacheable && *reinterpret_cast<volatile uint32_t*>(&b.pool_tok0_valid[map]) != 0u) {
+    __threadfence();
+    for (int ai = lane; ai < b.A; ai += 32) {
+      const int attempted = MG_LD_L2(&b.pool_tok0[(size_t)map * b.A + ai]);
+      tc[ai * 2] = (uint16_t)(attempted < b.T ? attempted : b.T);
+      tc[ai * 2 + 1] = (uint16_t)attempted;
+    }
+  } else if (b.obs_cells <= 128) {  // four agents' loads in flight at a time
     for (int ai = 0; ai < b.A; ai += 4) {
       int totals[4];
       const int n = b.A - ai < 4 ? b.A - ai : 4;
@@ -192,6 +229,13 @@ MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env
     }
   }
   __syncwarp();
+  if (cacheable && *reinterpret_cast<volatile uint32_t*>(&b.pool_tok0_valid[map]) == 0u) {
+    // several envs may get here for the same map at once: they all write the same values
+    for (int ai = lane; ai < b.A; ai += 32) b.pool_tok0[(size_t)map * b.A + ai] = tc[ai * 2 + 1];
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile uint32_t*>(&b.pool_tok0_valid[map]) = 1u;
+  }
   // `folds` identical passes (the reference runs the pass again on an unchanged state): counted that many times
   for (int k = 0; k < folds; k++) {
     uint32_t keep[(MG_MAX_AGENTS + 31) / 32];
@@ -210,14 +254,14 @@ MG_DEVICE MG_NOINLINE void count_observation_pass_warp(const MgBatch& b, int env
 // `seeded_cached`: the env's seed is the one its cached generator state was made from (auto-reset).
 // `folds`: how many times the closing observation count is added to the token stats (see the end).
 MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, EnvRec& er, bool seeded_cached, int folds) {
+#ifdef MG_TIMING
+  const long long rt_begin = clock64();
+#endif
   const int32_t* cfg = b.cfg;
   const int map = er.map_idx;
   // grid: 16-byte copies (grid_stride is a multiple of 8 cells)
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(b.pool_grid + (size_t)map * b.grid_stride);
-    uint4* dst = reinterpret_cast<uint4*>(b.grid + (size_t)env * b.grid_stride);
-    for (int i = lane; i < b.grid_stride / 8; i += 32) dst[i] = src[i];
-  }
+  copy16_warp(reinterpret_cast<uint4*>(b.grid + (size_t)env * b.grid_stride),
+              reinterpret_cast<const uint4*>(b.pool_grid + (size_t)map * b.grid_stride), b.grid_stride / 8, lane);
   er.current_step = 0;
   er.done = 0;
   er.n_asm = b.pool_n_asm[map];
@@ -297,11 +341,11 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
     uint4* cache = reinterpret_cast<uint4*>(b.rng_seeded + (size_t)env * MT_N);
     uint4* st = reinterpret_cast<uint4*>(mt);
     if (seeded_cached) {
-      for (int i = lane; i < MT_N / 4; i += 32) st[i] = cache[i];
+      copy16_warp(st, cache, MT_N / 4, lane);
     } else {
       if (lane == 0) mt_seed_serial(mt, er.seed);
       __syncwarp();
-      for (int i = lane; i < MT_N / 4; i += 32) cache[i] = st[i];
+      copy16_warp(cache, st, MT_N / 4, lane);
     }
   }
   __syncwarp();
@@ -327,8 +371,7 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   {  // token records: static objects from the per-config templates, then agents, chests, global tokens
     const uint4* src = reinterpret_cast<const uint4*>(b.static_rec);
     uint4* dst = reinterpret_cast<uint4*>(token_record(b, env, MG_GK_STATIC, 0u));
-    const int n16 = (cfg[MGC_NUM_CELLTYPES] << b.rec_shift) >> 4;
-    for (int i = lane; i < n16; i += 32) dst[i] = src[i];
+    copy16_warp(dst, src, (cfg[MGC_NUM_CELLTYPES] << b.rec_shift) >> 4, lane);
   }
   for (int ai = lane; ai < b.A; ai += 32) {
     write_agent_tokens(b, agents[ai], token_record(b, env, MG_GK_AGENT, (uint32_t)ai));
@@ -340,9 +383,22 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   // (_make_buffers -> set_buffers -> _init_buffers, mettagrid_c.cpp:139-140,247-262), BEFORE the
   // clipper exists; the caller's set_buffers (simulator.py:93-100) then runs the pass whose output
   // is kept. Both passes add to tokens_written/dropped/free_space, so the first is counted here.
+#ifdef MG_TIMING
+  const long long rt1 = clock64();
+#endif
   update_protocol_cache_warp(b, e, lane);
   write_all_asm_tokens_warp(b, env, lane, er.n_asm, 0u);
-  count_observation_pass_warp(b, env, lane, 0u, folds);
+#ifdef MG_TIMING
+  const long long rt2 = clock64();
+#endif
+  count_observation_pass_warp(b, env, lane, 0u, folds, b.has_clipper ? -1 : er.map_idx);
+#if defined(MG_TIMING) && !defined(MG_TIMING_ACC)
+  if (lane == 0 && b.dbg != nullptr) {  // reset: [13] up to the assembler records | [14] assembler records | [15] count pass
+    b.dbg[(size_t)env * 16 + 13] = (uint32_t)(rt1 - rt_begin);
+    b.dbg[(size_t)env * 16 + 14] = (uint32_t)(rt2 - rt1);
+    b.dbg[(size_t)env * 16 + 15] = (uint32_t)(clock64() - rt2);
+  }
+#endif
   if (!b.has_clipper) return;  // nothing below changes what observers see
   {
     uint32_t* cmt = b.clip_rng + (size_t)env * MT_N;
@@ -382,25 +438,48 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
   write_all_asm_tokens_warp(b, env, lane, er.n_asm, 0u);
 }
 
-// Sum a finished episode into the batch accumulators before its state is overwritten.
-MG_DEVICE MG_NOINLINE void accumulate_episode_warp(const MgBatch& b, int env, int lane) {
-  const AgentRec* agents = b.agents + (size_t)env * b.A;
-  const float* astats = b.agent_stats + (size_t)env * b.A * b.S;
-  const float* gstats = b.game_stats + (size_t)env * b.GS;
+// v as fixed point with 16 fraction bits, from 32-bit conversions only (|v| < 2^31)
+MG_DEVICE inline long long to_fixed16(float v) {
+  const float whole = floorf(v);
+  return (long long)(int)whole * 65536ll + (long long)(int)((v - whole) * 65536.0f + 0.5f);
+}
+MG_DEVICE inline void accum_add(long long* slot, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(slot), (unsigned long long)to_fixed16(v));
+}
+
+// An episode that has just ended is summed into the batch accumulators by the observation pass that follows
+// the step: the warp that encodes agent ai's row adds that agent's stat row and episode reward (and agent
+// 0's warp the env's game stats). Twenty-four warps share the work there, off the step's critical chain; the
+// state itself stays as it is until the next step starts the new episode.
+MG_DEVICE MG_NOINLINE void accumulate_agent_warp(const MgBatch& b, int env, int ai, int lane) {
+  const size_t g = (size_t)env * b.A + ai;
+  const float* row = b.agent_stats + g * b.S;
+  const float* hot = b.hot_stats + g * MG_HOT_STATS;
   if (lane == 0) {
-    double r = 0.0;
-    for (int ai = 0; ai < b.A; ai++) r += (double)agents[ai].episode_reward;
-    atomicAdd(&b.episode_accum[0], 1.0);
-    atomicAdd(&b.episode_accum[1], r);
+    const float r = b.agents[g].episode_reward;
+    if (r != 0.0f) accum_add(&b.episode_accum[1], r);
+    if (ai == 0) accum_add(&b.episode_accum[0], 1.0f);
   }
-  for (int s = lane; s < b.S; s += 32) {
-    double v = 0.0;
-    for (int ai = 0; ai < b.A; ai++)
-      v += (double)(s < MG_HOT_STATS ? b.hot_stats[((size_t)env * b.A + ai) * MG_HOT_STATS + s] : astats[(size_t)ai * b.S + s]);
-    if (v != 0.0) atomicAdd(&b.episode_accum[2 + s], v);
+  if (lane < MG_HOT_STATS) {
+    const float v = hot[lane];
+    if (v != 0.0f) accum_add(&b.episode_accum[2 + lane], v);
   }
-  for (int s = lane; s < b.GS; s += 32)
-    if (gstats[s] != 0.0f) atomicAdd(&b.episode_accum[2 + b.S + s], (double)gstats[s]);
+  for (int s0 = MG_HOT_STATS; s0 < b.S; s0 += 32 * 4) {  // four loads in flight per lane
+    float x[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) x[k] = s0 + lane + 32 * k < b.S ? row[s0 + lane + 32 * k] : 0.0f;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      if (x[k] != 0.0f) accum_add(&b.episode_accum[2 + s0 + lane + 32 * k], x[k]);
+  }
+  if (ai == 0) {
+    const float* gstats = b.game_stats + (size_t)env * b.GS;
+    for (int s = lane; s < b.GS; s += 32) {
+      // the token counts of this very pass are still pending (folded at the next step's start): add them here
+      float v = gstats[s];
+      if (v != 0.0f) accum_add(&b.episode_accum[2 + b.S + s], v);
+    }
+  }
 }
 
 MG_GLOBAL void mg_reset_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask, const uint32_t* seeds, const int32_t* map_idx) {
@@ -627,8 +706,15 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     }
     MG_SM_TICK(sm, 0);
     if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
-      __syncwarp();
-      accumulate_episode_warp(b, env, lane);
+      {  // everything the episode change will read, requested now
+        const int next_map = b.num_maps > 0 ? (er.map_idx + b.map_stride) % b.num_maps : er.map_idx;
+        prefetch_range_warp(b.pool_grid + (size_t)next_map * b.grid_stride, (size_t)b.grid_stride * sizeof(uint16_t), lane);
+        prefetch_range_warp(b.rng_seeded + (size_t)env * MT_N, MT_N * sizeof(uint32_t), lane);
+        prefetch_range_warp(b.pool_asm + (size_t)next_map * b.max_asm * 3, (size_t)b.max_asm * 3 * sizeof(int32_t), lane);
+        prefetch_range_warp(b.pool_agents + (size_t)next_map * A * 3, (size_t)A * 3 * sizeof(int32_t), lane);
+        if (lane == 0) { MG_PREFETCH_TO_L2(b.pool_n_asm + next_map); MG_PREFETCH_TO_L2(b.pool_n_chest + next_map); }
+        if (b.pool_tok0 != nullptr) prefetch_range_warp(b.pool_tok0 + (size_t)next_map * A, (size_t)A * sizeof(uint16_t), lane);
+      }
       __syncwarp();
       if (b.num_maps > 0) er.map_idx = (er.map_idx + b.map_stride) % b.num_maps;
       er.episodes += 1;
@@ -636,7 +722,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       // clipper it equals the constructor's own pass, which is then simply counted twice.
       reset_env_warp(b, env, lane, er, true, b.has_clipper ? 1 : 2);
       __syncwarp();
-      if (b.has_clipper) count_observation_pass_warp(b, env, lane, 0u, 1);
+      if (b.has_clipper) count_observation_pass_warp(b, env, lane, 0u, 1, -1);
       fresh = true;
       continue;  // load the new episode's state
     }
@@ -671,7 +757,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       const float* st = b.agent_stats + (abase + ai) * b.S;
       for (int i = 0; i < grp[MG_GRP_NUM_REWARDS]; i++) {
         const int slot = grp[MG_GRP_REWARDS + i * MG_RWD_WORDS + MG_RWD_AGENT_STAT];
-        if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) MG_PREFETCH_L2(st + slot);
+        if (slot >= MG_HOT_STATS && !(slot >= MG_AS_AMOUNT && slot < MG_AS_AMOUNT + MG_MAX_RESOURCES)) MG_PREFETCH_TO_L2(st + slot);
       }
     }
   }
@@ -776,23 +862,18 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
     if (uses_asm) {
       const AsmRec* ar = &e.asms[MG_GRID_INDEX(my_target)];
       if (b.has_clipper || asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE] > 0) ordered = true;  // (4)
-      for (int i = -1; i <= 1; i++)                                                         // (3) standing in the block
-        for (int j = -1; j <= 1; j++) {
-          const int rr = my_tr + i, cc = my_tc + j;
-          if ((i == 0 && j == 0) || rr < 0 || cc < 0 || rr >= b.H || cc >= b.W) continue;
-          const uint16_t g = e.grid[rr * b.W + cc];
-          if (MG_GRID_KIND(g) == MG_GK_AGENT && (int)MG_GRID_INDEX(g) != lane) {
-            ordered = true;
-            atomicOr(&sm.ordered_mask, 1u << MG_GRID_INDEX(g));
-          }
-        }
     }
+    // (3) every agent compares its own cell and the cell it moves into with the block of each user: no
+    // grid reads (agents stand where their records say)
+    const int my_r = lane < A ? (int)sm.ag[lane].r : -4, my_c = lane < A ? (int)sm.ag[lane].c : -4;
     uint32_t users = __ballot_sync(MG_FULL_MASK, uses_asm);
-    while (users != 0u) {                                                                   // (3) moving into the block
+    while (users != 0u) {
       const int u = __ffs((int)users) - 1;
       users &= users - 1u;
       const int br = __shfl_sync(MG_FULL_MASK, my_tr, u), bc = __shfl_sync(MG_FULL_MASK, my_tc, u);
-      const bool hit = moving && lane != u && my_tr >= br - 1 && my_tr <= br + 1 && my_tc >= bc - 1 && my_tc <= bc + 1;
+      const bool stands = lane != u && my_r >= br - 1 && my_r <= br + 1 && my_c >= bc - 1 && my_c <= bc + 1;
+      const bool enters = moving && lane != u && my_tr >= br - 1 && my_tr <= br + 1 && my_tc >= bc - 1 && my_tc <= bc + 1;
+      const bool hit = stands || enters;
       if (hit) ordered = true;
       if (__ballot_sync(MG_FULL_MASK, hit) != 0u && lane == u) ordered = true;
     }
@@ -826,12 +907,32 @@ MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, 
     if (lane == 0) e.concurrent = true;
     __syncwarp();
     const uint32_t intent = lane < A ? sm.intent[lane] : 0u;
+    const int kind = (int)((intent >> 8) & 0xFFu);
+    int code = MG_ACT_FROZEN, my_asm = -1;
     if (intent & 1u) {
-      const bool ok = handle_action(e, lane, (int)((intent >> 8) & 0xFFu), (int)(intent >> 16));
-      sm.success[lane] = ok ? 1 : 0;
-      if (ok) sm.executed[lane] = sm.action[lane];
+      code = action_begin(e, lane, kind, (int)(intent >> 16), true, &my_asm);
+      if (code == MG_ACT_OK || code == MG_ACT_FAIL) {
+        action_end(e, lane, kind, code == MG_ACT_OK);
+        sm.success[lane] = code == MG_ACT_OK ? 1 : 0;
+        if (code == MG_ACT_OK) sm.executed[lane] = sm.action[lane];
+      }
     }
     __syncwarp();
+    // assembler uses that came up in this pass: one after the other, each by the whole warp (they touch
+    // disjoint neighbourhoods, so their order does not matter)
+    uint32_t pending = __ballot_sync(MG_FULL_MASK, code == MG_ACT_USE_PENDING);
+    while (pending != 0u) {
+      const int who = __ffs((int)pending) - 1;
+      pending &= pending - 1u;
+      const int asm_idx = __shfl_sync(MG_FULL_MASK, my_asm, who);
+      const bool ok = assembler_use_warp(e, asm_idx, who, true, lane);
+      if (lane == who) {
+        action_end(e, who, MG_ACTION_MOVE, ok);
+        sm.success[who] = ok ? 1 : 0;
+        if (ok) sm.executed[who] = sm.action[who];
+      }
+      __syncwarp();
+    }
     if (lane == 0) e.concurrent = false;
     __syncwarp();
   }
@@ -848,14 +949,27 @@ MG_DEVICE MG_NOINLINE void step_phase_act(const MgBatch& b, StepSmem<MAXA>& sm, 
     n_ordered = __popc(picks);
     __syncwarp();
   }
-  if (lane == 0 && ordered_mask != 0u) {
+  if (ordered_mask != 0u) {
+    // every lane walks the list; lane 0 acts, and an assembler use is done by the whole warp
     for (int k = 0; k < n_ordered; k++) {
       const int ai = sm.order[k];
       const int a = sm.action[ai];
       if (a < 0 || a >= nact) continue;
-      const bool ok = handle_action(e, ai, acts[a * MG_ACT_WORDS + MG_ACT_KIND], acts[a * MG_ACT_WORDS + MG_ACT_ARG]);
-      sm.success[ai] = ok ? 1 : 0;
-      if (ok) sm.executed[ai] = a;
+      const int kind = acts[a * MG_ACT_WORDS + MG_ACT_KIND];
+      int code = MG_ACT_FROZEN, asm_idx = -1;
+      if (lane == 0) code = action_begin(e, ai, kind, acts[a * MG_ACT_WORDS + MG_ACT_ARG], true, &asm_idx);
+      code = __shfl_sync(MG_FULL_MASK, code, 0);
+      bool ok = code == MG_ACT_OK;
+      if (code == MG_ACT_USE_PENDING) {
+        asm_idx = __shfl_sync(MG_FULL_MASK, asm_idx, 0);
+        ok = assembler_use_warp(e, asm_idx, ai, false, lane);
+      }
+      if (lane == 0 && code != MG_ACT_FROZEN) {
+        action_end(e, ai, kind, ok);
+        sm.success[ai] = ok ? 1 : 0;
+        if (ok) sm.executed[ai] = a;
+      }
+      __syncwarp();
     }
   }
   __syncwarp();
@@ -884,6 +998,7 @@ MG_DEVICE MG_NOINLINE void step_phase_post(const MgBatch& b, StepSmem<MAXA>& sm,
   if (b.has_clipper) {
     uint32_t cidx = er.clip_rng_idx;
     clipper_step_warp(b, e, sm.scratch, cidx, lane);
+    __syncwarp();  // every lane has read the old position
     if (lane == 0) er.clip_rng_idx = cidx;
   }
 
@@ -892,6 +1007,7 @@ MG_DEVICE MG_NOINLINE void step_phase_post(const MgBatch& b, StepSmem<MAXA>& sm,
   // clipper), all assembler records are refreshed; otherwise assembler_on_use already did it
   if (cfg[MGC_HAS_VIBE_ASM]) write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);
 
+  __syncwarp();  // every lane has read the old position
   if (lane == 0) er.rng_idx = rs.idx;
   __syncwarp();
 }
@@ -1093,6 +1209,15 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
     // the running maximum only moves a few times per pass: look before bumping it, so that nearly
     // all rows do without an atomic on the one shared word
     if (b.max_flip != nullptr && written > MG_LD_L2(b.max_flip)) atomicMax(b.max_flip, written);
+  }
+  if (b.after_step && b.auto_reset) {
+    // EnvRec::done (byte 40) read at L2 like current_step; set by this step's finish phase when the episode ended
+    const uint32_t done_word = MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10);
+    if ((done_word & 0xFFu) != 0u) {
+      accumulate_agent_warp(b, env, ai, lane);
+      if (lane < 3)  // this pass's own token counts (folded into the game stats only when the next step starts)
+        accum_add(&b.episode_accum[2 + b.S + MG_GS_TOKENS_WRITTEN + lane], (float)(lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written)));
+    }
   }
   if (b.obs_mask != nullptr) {  // 8 slots per lane and round; a row of T bytes starts 8-byte aligned when T % 8 == 0
     uint8_t* m = b.obs_mask + (size_t)g * b.T;

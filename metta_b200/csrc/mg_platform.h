@@ -40,6 +40,10 @@
 #endif
 #define MG_LD_L2(p) __ldcg(p) /* read at L2: for words other lanes may have bumped with atomics */
 #define MG_NANOSLEEP(ns) __nanosleep(ns)
+// A counter in HBM that nothing on the step's critical path reads back through L1: bumped with a reduction
+// (no load, no stall on a cold line). Readers use MG_LD_L2.
+#define MG_STAT_BUMP(p, v) ((void)atomicAdd((p), (v)))
+#define MG_PREFETCH_TO_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #define MG_WARP_SUM(v) ((int)__reduce_add_sync(0xFFFFFFFFu, (int)(v))) /* one redux.sync instead of five shuffle rounds */
 #define MG_ROLLED _Pragma("unroll 1")
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */

@@ -23,22 +23,34 @@ MG_DEVICE inline void mt_seed_serial(uint32_t* mt, uint32_t seed) {
   }
 }
 
-// _M_gen_rand (bits/random.tcc:395-433) in chunks of 32 consecutive words: within a chunk every
-// lane reads old[i], old[i+1] and the word 397 ahead before anyone writes; across chunks the
-// order of the serial algorithm is kept, so word i+397 (mod 624) is old for i < 227 and already
-// regenerated for i >= 227, and word 623 sees the new word 0.
+// _M_gen_rand (bits/random.tcc:395-433), cooperatively: every lane reads old[i], old[i+1] and the word 397
+// ahead before anyone writes; the order of the serial algorithm is kept where it matters, so word i+397
+// (mod 624) is old for i < 227 and already regenerated for i >= 227, and word 623 sees the new word 0.
 MG_DEVICE MG_NOINLINE void mt_twist_warp(uint32_t* mt, int lane) {  // once per 624 words: kept out of line, out of the hot code
-  for (int s = 0; s < MT_N; s += 32) {
-    int i = s + lane;
-    uint32_t v = 0;
-    if (i < MT_N) {
-      int i1 = i + 1 == MT_N ? 0 : i + 1;
-      int im = i + MT_M >= MT_N ? i + MT_M - MT_N : i + MT_M;
-      uint32_t y = (mt[i] & 0x80000000u) | (mt[i1] & 0x7fffffffu);
-      v = mt[im] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  // Three spans instead of twenty chunks: [0,227) needs old words only, [227,454) the new words of the first
+  // span, [454,624) those of the second (and word 623 the new word 0). Within a span every lane first reads
+  // all its words (independent loads: one memory round trip per span), then the span is written.
+#pragma unroll 1
+  for (int span = 0; span < 3; span++) {
+    const int first = span * (MT_N - MT_M), last = span == 2 ? MT_N : first + (MT_N - MT_M);
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int i = first + lane + 32 * k;
+      v[k] = 0u;
+      if (i < last) {
+        const int i1 = i + 1 == MT_N ? 0 : i + 1;
+        const int im = i + MT_M >= MT_N ? i + MT_M - MT_N : i + MT_M;
+        const uint32_t y = (mt[i] & 0x80000000u) | (mt[i1] & 0x7fffffffu);
+        v[k] = mt[im] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+      }
     }
     __syncwarp();
-    if (i < MT_N) mt[i] = v;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int i = first + lane + 32 * k;
+      if (i < last) mt[i] = v[k];
+    }
     __syncwarp();
   }
 }

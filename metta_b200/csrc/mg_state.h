@@ -111,6 +111,7 @@ struct MgBatch {
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
+  int32_t after_step;          // this observation pass follows a step: envs whose episode just ended are summed into episode_accum here
   int32_t cfg_words;           // length of cfg in int32 words, including what mg_create appends to the blob
   // derived from the config once, on the host (mg_create):
   uint32_t req_mask[3], con_mask[3];  // per action kind: resources it requires / consumes (bit per item)
@@ -139,6 +140,8 @@ struct MgBatch {
   const int32_t* pool_asm;     // [M][max_asm][3]
   const int32_t* pool_n_chest; // [M]
   const int32_t* pool_chest;   // [M][max_chest][3]
+  uint16_t* pool_tok0;         // [M][A] token count of every agent's first observation on this map (filled on first use; without a clipper it depends on the map alone)
+  uint32_t* pool_tok0_valid;   // [M] 1 once pool_tok0[m] is complete
   // state
   EnvRec* env;
   uint16_t* grid;              // [N][H*W]
@@ -156,7 +159,8 @@ struct MgBatch {
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]
-  double* episode_accum;       // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce)
+  long long* episode_accum;    // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce), fixed point with 16 fraction bits:
+                               // integer atomics only (double arithmetic measured ~1000 cycles per instruction on this part); mg_read converts
   MgQueueCtl* qctl;            // queue control block and entries [N] (see above)
   unsigned long long* queue;
   uint32_t* dbg;               // [N][16] cycle counters of the step kernel's phases (builds with -DMG_TIMING only, else null)

@@ -157,6 +157,26 @@ MG_DEVICE inline void write_asm_tokens(const MgBatch& b, const AsmRec* a, uint32
   *reinterpret_cast<uint2*>(rec) = make_rec_header((uint32_t)n, v.cooldown_end);
 }
 
+// The same record written by the whole warp (all lanes with the same arguments): a token per lane.
+MG_DEVICE inline void write_asm_tokens_warp(const MgBatch& b, const AsmRec* a, uint32_t current_step, uint8_t* rec, int lane) {
+  AsmView v;
+  asm_view(b, b.cfg, a, current_step, v);
+  uint16_t* out = reinterpret_cast<uint16_t*>(rec + MG_REC_TOKENS);
+  const int cap = ((1 << b.rec_shift) - MG_REC_TOKENS) >> 1;
+  const int np = (int)(v.proto_ix & 0xFFu), nt = (int)(v.tail_ix & 0xFFu);
+  const int n = v.ndyn + np + nt;
+  const uint16_t* ps = b.tmpl_tok + (v.proto_ix >> 8);
+  const uint16_t* ts = b.tmpl_tok + (v.tail_ix >> 8);
+  for (int k = lane; k < n && k < cap; k += 32) {
+    uint16_t tok;
+    if (k < v.ndyn) tok = (uint16_t)(k == 0 ? v.dyn[0] : v.dyn[1]);
+    else if (k < v.ndyn + np) tok = MG_LDG(&ps[k - v.ndyn]);
+    else tok = MG_LDG(&ts[k - v.ndyn - np]);
+    out[k] = tok;
+  }
+  if (lane == 0) *reinterpret_cast<uint2*>(rec) = make_rec_header((uint32_t)n, v.cooldown_end);
+  __syncwarp();
+}
 
 // The tokens every agent gets at the centre of its window, then the compass token
 // (mettagrid_c.cpp:425-517), as (location, feature, value) triples ready to be copied.

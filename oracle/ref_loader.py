@@ -19,7 +19,8 @@ _mod = None
 
 
 def ref_so_path() -> str | None:
-    hits = sorted(glob.glob(os.path.join(_HERE, "_ref", "mettagrid_c*.so")))
+    # MG_REF_DIR=_ref_ordered selects the build with id-ordered clipper sets (oracle/build_ref_ordered.sh)
+    hits = sorted(glob.glob(os.path.join(_HERE, os.environ.get("MG_REF_DIR", "_ref"), "mettagrid_c*.so")))
     return hits[0] if hits else None
 
 

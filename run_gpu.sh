@@ -1,18 +1,15 @@
 #!/bin/bash
-# One GPU session: tests, benches of build variants, probes. Output under gpurun_out/.
 mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
 python -m pytest tests -m gpu -x -q > gpurun_out/gputests.log 2>&1; echo "gpu tests rc=$?" | tee gpurun_out/summary.txt
-tail -5 gpurun_out/gputests.log
+tail -4 gpurun_out/gputests.log
 B="python bench.py --no-cpu-baseline --no-other-configs"
 $B > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err
-for v in sw1c24 sw1c20 sw1c16 sw2c12 sw4c6; do
-  MG_LIB_PATH=build_variants/lib_$v.so $B > gpurun_out/bench_$v.json 2> gpurun_out/bench_$v.err
-done
-MG_CHUNKS=6 MG_LIB_PATH=build_variants/lib_sw1c24.so $B > gpurun_out/bench_sw1c24_ch6.json 2> gpurun_out/bench_sw1c24_ch6.err
-MG_CHUNKS=16 MG_LIB_PATH=build_variants/lib_sw1c24.so $B > gpurun_out/bench_sw1c24_ch16.json 2> gpurun_out/bench_sw1c24_ch16.err
+MG_CHUNKS=4 $B > gpurun_out/bench_default_ch4.json 2> gpurun_out/bench_default_ch4.err
+MG_CHUNKS=6 $B > gpurun_out/bench_default_ch6.json 2> gpurun_out/bench_default_ch6.err
+MG_CHUNKS=8 $B > gpurun_out/bench_default_ch8.json 2> gpurun_out/bench_default_ch8.err
 MG_STEP_MODE=fused $B > gpurun_out/bench_fused.json 2> gpurun_out/bench_fused.err
 MG_LIB_PATH=build_variants/lib_timing.so python tools/timing_probe.py 4096 flush 20 stagger > gpurun_out/timing_steady.txt 2>&1
-python tools/ordered_probe.py 1024 > gpurun_out/ordered_probe.txt 2>&1
+for i in 1 2; do MG_LIB_PATH=build_variants/lib_timing.so python tools/timing_probe.py 4096 flush $((20+i)) stagger 2>&1 | tail -1; done > gpurun_out/reset_steady.txt
 python - <<'PY' | tee -a gpurun_out/summary.txt
 import json,glob
 for f in sorted(glob.glob('gpurun_out/bench_*.json')):

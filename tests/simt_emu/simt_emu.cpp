@@ -1,10 +1,13 @@
 // Fiber scheduler of the SIMT emulator (see simt_emu.h). TEST INFRASTRUCTURE.
 #include "simt_emu.h"
+#include <stdio.h>
+#include <stdlib.h>
 
 emu_dim3 threadIdx, blockIdx, blockDim, gridDim;
 
 namespace simt_emu {
 static State g_state;
+void set_site(int site) { State& s = st(); if (s.cur >= 0 && s.cur < (int)s.fibers.size()) s.fibers[s.cur].site = site; }
 State& st() { return g_state; }
 static const size_t kStack = 512 * 1024;
 
@@ -35,6 +38,14 @@ void warp_barrier() {
   State& s = st();
   WarpState& w = s.warps[s.cur / 32];
   unsigned gen = w.gen;
+  const int g_site = s.fibers[s.cur].site;
+  if (w.arrived == 0) {
+    w.site = g_site;
+  } else if (w.site != g_site) {
+    fprintf(stderr, "simt_emu: lanes of one warp meet at different collectives: line %d vs line %d (lane %d, block %u)\n",
+            w.site % 100000, g_site % 100000, s.cur % 32, blockIdx.x);
+    abort();
+  }
   if (++w.arrived == w.alive) {
     w.arrived = 0;
     w.gen++;

@@ -31,6 +31,8 @@
 #define MG_PREFETCH_L2(p) ((void)(p))
 #define MG_RED_ADD(p, v) ((void)(*(p) += (v)))
 #define MG_LDCG(p) (*(p))
+#define MG_STAT_BUMP(p, v) ((void)(*(p) += (v)))
+#define MG_PREFETCH_TO_L2(p) ((void)(p))
 #define MG_LD_L2(p) (*(p))
 #define MG_NANOSLEEP(ns) ((void)0)
 #define MG_ROLLED
@@ -56,11 +58,13 @@ struct Fiber {
   ucontext_t ctx;
   char* stack;
   bool done;
+  int site;  // call site of the collective this lane is in (see MG_EMU_SITE)
 };
 struct WarpState {
   int arrived, alive;
   unsigned gen;
   uint64_t xchg[32];
+  int site, phase;  // call site of the first arrival at the barrier being filled; sub-barrier count within one collective
 };
 struct State {
   ucontext_t sched;
@@ -83,7 +87,7 @@ void block_barrier();
 
 extern emu_dim3 threadIdx, blockIdx, blockDim, gridDim;
 
-static inline void __syncwarp(unsigned = 0xFFFFFFFFu) { simt_emu::warp_barrier(); }
+static inline void emu__syncwarp(unsigned = 0xFFFFFFFFu) { simt_emu::warp_barrier(); }
 static inline void __syncthreads() { simt_emu::block_barrier(); }
 
 template <typename T>
@@ -102,26 +106,26 @@ static inline T emu_exchange(T v, int src_lane) {
 }
 // width: the warp is split into segments of `width` lanes (a power of two), as the hardware does
 template <typename T>
-static inline T __shfl_sync(unsigned, T v, int src, int width = 32) {
+static inline T emu__shfl_sync(unsigned, T v, int src, int width = 32) {
   int lane = (int)(threadIdx.x & 31);
   return emu_exchange(v, (lane & ~(width - 1)) | (src & (width - 1)));
 }
 template <typename T>
-static inline T __shfl_up_sync(unsigned, T v, unsigned d, int width = 32) {
+static inline T emu__shfl_up_sync(unsigned, T v, unsigned d, int width = 32) {
   int lane = (int)(threadIdx.x & 31), in_seg = lane & (width - 1);
   return emu_exchange(v, in_seg - (int)d >= 0 ? lane - (int)d : lane);
 }
 template <typename T>
-static inline T __shfl_down_sync(unsigned, T v, unsigned d, int width = 32) {
+static inline T emu__shfl_down_sync(unsigned, T v, unsigned d, int width = 32) {
   int lane = (int)(threadIdx.x & 31), in_seg = lane & (width - 1);
   return emu_exchange(v, in_seg + (int)d < width ? lane + (int)d : lane);
 }
 template <typename T>
-static inline T __shfl_xor_sync(unsigned, T v, int m, int width = 32) {
+static inline T emu__shfl_xor_sync(unsigned, T v, int m, int width = 32) {
   int lane = (int)(threadIdx.x & 31), target = lane ^ m;
   return emu_exchange(v, (target & ~(width - 1)) == (lane & ~(width - 1)) ? target : lane);
 }
-static inline unsigned __ballot_sync(unsigned, int pred) {
+static inline unsigned emu__ballot_sync(unsigned, int pred) {
   simt_emu::State& s = simt_emu::st();
   simt_emu::WarpState& w = s.warps[s.cur / 32];
   w.xchg[s.cur % 32] = pred ? 1 : 0;
@@ -134,7 +138,7 @@ static inline unsigned __ballot_sync(unsigned, int pred) {
   simt_emu::warp_barrier();
   return m;
 }
-static inline unsigned __match_any_sync(unsigned, int v) {
+static inline unsigned emu__match_any_sync(unsigned, int v) {
   simt_emu::State& s = simt_emu::st();
   simt_emu::WarpState& w = s.warps[s.cur / 32];
   w.xchg[s.cur % 32] = (uint64_t)(uint32_t)v;
@@ -148,11 +152,12 @@ static inline unsigned __match_any_sync(unsigned, int v) {
   return m;
 }
 static inline unsigned atomicOr(unsigned* p, unsigned v) { unsigned o = *p; *p |= v; return o; }
-static inline int emu_warp_sum(int v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o); return v; }
+static inline int emu_warp_sum(int v) { for (int o = 16; o > 0; o >>= 1) v += emu__shfl_xor_sync(0xFFFFFFFFu, v, o); return v; }
 #define MG_WARP_SUM(v) emu_warp_sum((int)(v))
 static inline int atomicMax(int* p, int v) { int o = *p; if (v > o) *p = v; return o; }
-static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
+static inline int emu__any_sync(unsigned m, int p) { return emu__ballot_sync(m, p) != 0; }
 static inline long long clock64() { return 0; }
+static inline void __threadfence() {}
 static inline int __ffs(int x) { return __builtin_ffs(x); }
 static inline int __ffsll(long long x) { return __builtin_ffsll(x); }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
@@ -202,5 +207,21 @@ static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, int) { 
 static inline cudaError_t cudaGraphExecDestroy(cudaGraphExec_t) { return 0; }
 static inline cudaError_t cudaGraphDestroy(cudaGraph_t) { return 0; }
 static inline cudaError_t cudaDeviceSetLimit(int, size_t) { return 0; }
+
+// Every collective records where it was called from; a barrier that completes with lanes arriving from
+// different call sites means the kernel's lanes took different numbers of collectives (a bug that real
+// hardware would turn into a hang or garbage): the emulator aborts with both sites.
+namespace simt_emu { void set_site(int site); }
+#define MG_EMU_SITE(call) (simt_emu::set_site(__COUNTER__ * 100000 + __LINE__), call)
+#define __syncwarp(...) MG_EMU_SITE(emu__syncwarp(__VA_ARGS__))
+#define __shfl_sync(...) MG_EMU_SITE(emu__shfl_sync(__VA_ARGS__))
+#define __shfl_up_sync(...) MG_EMU_SITE(emu__shfl_up_sync(__VA_ARGS__))
+#define __shfl_down_sync(...) MG_EMU_SITE(emu__shfl_down_sync(__VA_ARGS__))
+#define __shfl_xor_sync(...) MG_EMU_SITE(emu__shfl_xor_sync(__VA_ARGS__))
+#define __ballot_sync(...) MG_EMU_SITE(emu__ballot_sync(__VA_ARGS__))
+#define __match_any_sync(...) MG_EMU_SITE(emu__match_any_sync(__VA_ARGS__))
+#define __any_sync(...) MG_EMU_SITE(emu__any_sync(__VA_ARGS__))
+#undef MG_WARP_SUM
+#define MG_WARP_SUM(v) MG_EMU_SITE(emu_warp_sum((int)(v)))
 
 #endif  // SIMT_EMU_H_

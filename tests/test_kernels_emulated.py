@@ -134,3 +134,26 @@ def test_emulated_crowded_rooms(name, envs, steps, emu_lib):
     assert st[L.MG_AS_SWAP] > 0 and st[L.MG_AS_TRANSFER_COUNT] > 0 and st[L.MG_AS_ATTACK_HIT : L.MG_AS_ATTACK_HIT + 8].sum() > 0
     assert ordered > 0.6, f"only {ordered:.2f} of the agents went through the ordered pass"
     ls.close()
+
+
+def test_emulated_episode_accumulators(emu_lib):
+    """The finished-episode accumulators (what reduce_episode_stats all-reduces) equal the sums of the per-env
+    stats and episode rewards as they stood when the episodes ended."""
+    cfg, grid = SCENARIOS["tiny_truncating"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    n = 5
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=n, seeds=np.arange(n) + 3, clib=emu_lib)
+    rng = np.random.RandomState(4)
+    want = None
+    for s in range(1, 12):
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A))
+        if s in (5, 10):  # episodes end here (max_steps 5); the next step folds them into the accumulators
+            st = ls.batch.read_agent_stats().astype(np.float64).sum(axis=(0, 1))
+            gs = ls.batch.read_game_stats().astype(np.float64).sum(axis=0)
+            rw = ls.batch.read_episode_rewards().astype(np.float64).sum()
+            cur = np.concatenate([[float(n), rw], st, gs])
+            want = cur if want is None else want + cur
+    acc = ls.batch.read_episode_accum()
+    assert acc[0] == 2 * n
+    assert np.allclose(acc, want, rtol=0, atol=1e-3), np.argwhere(~np.isclose(acc, want, rtol=0, atol=1e-3))[:5].tolist()
+    ls.close()

@@ -13,14 +13,14 @@ b = Batch(low, build_pool(low, arena_mapgen_pool(low)), N)
 dev = 'cuda'
 obs = torch.zeros((N*A, T, 3), dtype=torch.uint8, device=dev); term = torch.zeros(N*A, dtype=torch.uint8, device=dev)
 trunc = torch.zeros_like(term); rew = torch.zeros(N*A, dtype=torch.float32, device=dev)
-ring = torch.randint(0, 5, (16, N*A), dtype=torch.int32).to(dev); act = ring[0].clone()
+act = torch.zeros(N*A, dtype=torch.int32, device=dev)
 rl = torch.zeros(N*A, dtype=torch.int32, device=dev)
 b.set_buffers(obs.data_ptr(), term.data_ptr(), trunc.data_ptr(), rew.data_ptr(), act.data_ptr())
 b.set_obs_aux(rl.data_ptr(), 0, 0)
 b.reset((np.arange(N)+42).astype(np.uint32), (np.arange(N) % 256).astype(np.int32))
 prev_o = 0; prev_u = 0
 for s in range(1, 10001):
-    act.copy_(ring[s % 16]); b.step()
+    act.copy_(torch.randint(0, 5, (N*A,), dtype=torch.int32, device=dev)); b.step()
     if s in (50, 200, 500, 1000, 2000, 3000, 5000, 7000, 9999):
         torch.cuda.synchronize()
         o = int(b.read_env()["spare"][:, 0].astype(np.int64).sum()); u = int(b.read_assemblers()["uses_count"].astype(np.int64).sum())

@@ -20,9 +20,8 @@ STEPS=int(sys.argv[3]) if len(sys.argv)>3 else 20
 if len(sys.argv)>4 and sys.argv[4]=='stagger':  # the bench's steady state: envs at staggered episode phases
     g=np.arange(N,dtype=np.int64)
     b.set_early_reset((1+(g*6181)%9999).astype(np.uint32))
-    ring=torch.randint(0,5,(16,N*A),dtype=torch.int32).to(dev)
     for s in range(10000):
-        act.copy_(ring[s%16]); b.step()
+        act.copy_(torch.randint(0,5,(N*A,),dtype=torch.int32,device=dev)); b.step()
     torch.cuda.synchronize()
 for s in range(STEPS):
     act.copy_(torch.randint(0,5,(N*A,),dtype=torch.int32))
@@ -51,3 +50,13 @@ su = sp[:,12:16]
 m = uses == 1
 if m.sum():
     print('one successful use: set-up+scans %.0f | checks %.0f | consume+give %.0f | record %.0f  (sum %.0f)' % (su[m,0].mean(), su[m,1].mean(), su[m,2].mean(), su[m,3].mean(), su[m].sum(1).mean()))
+
+print('per-phase means by number of successful uses in the step (cycles):')
+print('%-34s' % 'phase' + ''.join('%10s' % ('uses=%d' % k) for k in range(3)))
+for i,n in enumerate(names):
+    if not n: continue
+    print('%-34s' % n + ''.join('%10.0f' % (sp[uses==k, i].mean() if (uses==k).any() else float('nan')) for k in range(3)))
+m = sp[:,0] > 100000
+if m.any():
+    print('envs that started a new episode in this step: %d; load %.0f = accumulate %.0f | reset up to the assembler records %.0f | assembler records %.0f | count pass %.0f' % (
+        m.sum(), sp[m,0].mean(), sp[m,12].mean(), sp[m,13].mean(), sp[m,14].mean(), sp[m,15].mean()))
