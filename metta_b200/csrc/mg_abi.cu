@@ -361,8 +361,9 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<MG_MAX_AGENTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(sizeof(StepSmem<MG_MAX_AGENTS>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
 #endif
-  // slices of about 512 envs (128 CTAs of the step kernel, a little under one per SM)
-  e->chunks = (num_envs + 341) / 342;  // measured on B200, 4096 arena envs: 8 slices 703-708 M agent-steps/s, 12: 712-722, 14: 704-706
+  // slices of about 1024 envs: measured on B200, 4096 arena envs in the bench's steady state, 2 slices 701 M
+  // agent-steps/s, 3: 706, 4: 729-738, 6: 722, 8: 720, 12: 704
+  e->chunks = (num_envs + 1023) / 1024;
   if (e->chunks > 12) e->chunks = 12;
   if (const char* env_chunks = getenv("MG_CHUNKS")) e->chunks = atoi(env_chunks);  // tuning knob
   if (e->chunks < 1) e->chunks = 1;

@@ -604,10 +604,11 @@ MG_DEVICE MG_NOINLINE void clipper_step_warp(const MgBatch& b, EnvCtx& e, int32_
         }
         if (pick >= 0) {
           const uint32_t sel = uniform_below_warp(cs, lane, (uint32_t)cc[MG_CLIP_NUM_PROTOCOLS]);
+          __syncwarp();  // every lane has walked the records before lane 0 changes them
           if (lane == 0) clip_assembler(e, &e.asms[pick], sel);
-          __syncwarp();
         }
       }
+      __syncwarp();
     }
     clip_rng_idx = cs.idx;
   }
@@ -635,6 +636,19 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
   constexpr int NV = MAXA * 4 / 32;  // 16-byte loads per lane for records (and for hot stats)
   constexpr int NA = (MAXA + 31) / 32;
   const size_t abase = (size_t)env * A;
+#ifdef MG_PREFETCH_ENV
+  // The env's grid and assembler records are read later in dependent steps (target cells, then what stands
+  // there, then its neighbourhood), each of which would be an HBM round trip after the policy's forward pass
+  // has swept L2. Ask for all of it now (a few KB per env): the later reads, and the observation pass
+  // behind this kernel, find it in L2.
+  prefetch_range_warp(b.grid + (size_t)env * b.grid_stride, (size_t)b.H * b.W * sizeof(uint16_t), lane);
+#if MG_PREFETCH_ENV > 1
+  prefetch_range_warp(b.asms + (size_t)env * b.max_asm, (size_t)b.max_asm * sizeof(AsmRec), lane);
+#endif
+#if MG_PREFETCH_ENV > 2
+  prefetch_range_warp(b.etok + (((size_t)env * b.rec_slots) << b.rec_shift), (size_t)b.rec_slots << b.rec_shift, lane);
+#endif
+#endif
   for (bool fresh = false;;) {
     uint4 ag_v[NV], hot_v[NV];
     int32_t act_v[NA];
@@ -1166,40 +1180,64 @@ template <int CPL>
 MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* warp_smem) {
   const size_t g = (size_t)env * b.A + ai;  // global agent index
   const int row_bytes = b.T * 3;
-  const int slot = (row_bytes + 16 + 15) & ~15;  // room to mirror the row's misalignment
+  const int slot = (row_bytes + 16 + 15) & ~15;
   uint8_t* out = b.obs + (size_t)g * row_bytes;
+#ifdef MG_OBS_STORE16
   const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
-  uint8_t* base = warp_smem;  // 16-byte aligned: [row image | cell descriptors]
-  uint8_t* row = base + mis;                     // row and out are congruent mod 16
-  uint2* desc = reinterpret_cast<uint2*>(base + slot);
+#else
+  const int mis = 0;
+#endif
+  uint8_t* row = warp_smem + mis;  // warp_smem is 16-byte aligned: [row image | cell descriptors]
+  uint2* desc = reinterpret_cast<uint2*>(warp_smem + slot);
+  // read past L1 (two env records share a cache line, and the fused kernel encodes envs other SMs stepped):
+  // the step counter, and whether this step ended the episode (EnvRec::done, byte 40)
+  const uint32_t current_step = MG_LD_L2(&b.env[env].current_step);
+#ifndef MG_OBS_DONE_LATE
+  const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
+#endif
   {
     uint4 ff;
     ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
-    uint4* p = reinterpret_cast<uint4*>(base);
-    const int n16 = slot >> 4;  // 39 for 200 tokens: two rounds, spelled out; the loop is for longer rows
+    uint4* p = reinterpret_cast<uint4*>(warp_smem);
+    const int n16 = slot >> 4;  // 39 for 200 tokens
     if (lane < n16) p[lane] = ff;
     if (lane + 32 < n16) p[lane + 32] = ff;
 #pragma unroll 1
     for (int i = lane + 64; i < n16; i += 32) p[i] = ff;
   }
   __syncwarp();
-  const uint32_t current_step = MG_LD_L2(&b.env[env].current_step);  // two env records share a cache line: read past L1 (fused kernel)
   const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step);
   __syncwarp();
-  // store: bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
-  const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
-  const int n16 = (row_bytes - head) >> 4;
-  const int tail = head + (n16 << 4);
-  if (lane < head) out[lane] = row[lane];
-  {
+#ifdef MG_OBS_STORE16
+  {  // bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
+    const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
+    const int n16 = (row_bytes - head) >> 4;
+    const int tail = head + (n16 << 4);
+    if (lane < head) out[lane] = row[lane];
     const uint4* s = reinterpret_cast<const uint4*>(row + head);
     uint4* d = reinterpret_cast<uint4*>(out + head);
     if (lane < n16) d[lane] = s[lane];
     if (lane + 32 < n16) d[lane + 32] = s[lane + 32];
 #pragma unroll 1
     for (int i = lane + 64; i < n16; i += 32) d[i] = s[i];
+    if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
   }
-  if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
+#else
+  // store: rows are multiples of 8 bytes for every even token count, and then 8-byte aligned whenever the
+  // buffer is: 8-byte chunks, no head or tail
+  if ((row_bytes & 7) == 0 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0) {
+    const uint2* s2 = reinterpret_cast<const uint2*>(row);
+    uint2* d2 = reinterpret_cast<uint2*>(out);
+    const int n8 = row_bytes >> 3;
+#pragma unroll 3
+    for (int i = lane; i < n8; i += 32) d2[i] = s2[i];
+  } else {
+    for (int i = lane; i < row_bytes; i += 32) out[i] = row[i];
+  }
+#endif
+#ifdef MG_OBS_DONE_LATE
+  const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
+#endif
   const int written = attempted < b.T ? attempted : b.T;
   if (lane == 0) {
     uint16_t* tc = b.tok_counts + (size_t)g * 2;
@@ -1210,10 +1248,8 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
     // all rows do without an atomic on the one shared word
     if (b.max_flip != nullptr && written > MG_LD_L2(b.max_flip)) atomicMax(b.max_flip, written);
   }
-  if (b.after_step && b.auto_reset) {
-    // EnvRec::done (byte 40) read at L2 like current_step; set by this step's finish phase when the episode ended
-    const uint32_t done_word = MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10);
-    if ((done_word & 0xFFu) != 0u) {
+  {
+    if ((done_word & 0xFFu) != 0u) {  // the episode ended in this step: add it to the batch accumulators
       accumulate_agent_warp(b, env, ai, lane);
       if (lane < 3)  // this pass's own token counts (folded into the game stats only when the next step starts)
         accum_add(&b.episode_accum[2 + b.S + MG_GS_TOKENS_WRITTEN + lane], (float)(lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written)));

@@ -102,13 +102,29 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
   uint32_t cell[CPL];  // grid value | location << 16, 0 = nothing there
   const uint32_t lower = (1u << lane) - 1u;
   int rank = 0, n_obj = 0;
+#ifdef MG_OBS_NO_FASTGATHER
+  if (false) {
+#else
+  if (my_r >= hr && my_c >= wr && my_r + hr < b.H && my_c + wr < b.W) {
+#endif
+    // the whole window lies inside the map (always, where the map's border is at least as wide as the window's
+    // radius, as in the arena): one add per cell, no range tests
+    const uint16_t* corner = grid + (my_r - hr) * b.W + (my_c - wr);
 #pragma unroll
-  for (int j = 0; j < CPL; j++) {
-    const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
-    const uint32_t r = (uint32_t)(my_r - hr) + (loc >> 4), c = (uint32_t)(my_c - wr) + (loc & 0xFu);  // wraps below zero: fails the range test
-    uint32_t g = 0;
-    if (r < (uint32_t)b.H && c < (uint32_t)b.W && loc != 0xFFu) g = grid[r * (uint32_t)b.W + c];
-    cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
+    for (int j = 0; j < CPL; j++) {
+      const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
+      const uint32_t g = loc != 0xFFu ? (uint32_t)corner[(loc >> 4) * (uint32_t)b.W + (loc & 0xFu)] : 0u;
+      cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < CPL; j++) {
+      const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
+      const uint32_t r = (uint32_t)(my_r - hr) + (loc >> 4), c = (uint32_t)(my_c - wr) + (loc & 0xFu);  // wraps below zero: fails the range test
+      uint32_t g = 0;
+      if (r < (uint32_t)b.H && c < (uint32_t)b.W && loc != 0xFFu) g = grid[r * (uint32_t)b.W + c];
+      cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
+    }
   }
 #pragma unroll
   for (int j = 0; j < CPL; j++) {

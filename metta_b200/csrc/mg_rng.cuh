@@ -27,32 +27,49 @@ MG_DEVICE inline void mt_seed_serial(uint32_t* mt, uint32_t seed) {
 // ahead before anyone writes; the order of the serial algorithm is kept where it matters, so word i+397
 // (mod 624) is old for i < 227 and already regenerated for i >= 227, and word 623 sees the new word 0.
 MG_DEVICE MG_NOINLINE void mt_twist_warp(uint32_t* mt, int lane) {  // once per 624 words: kept out of line, out of the hot code
-  // Three spans instead of twenty chunks: [0,227) needs old words only, [227,454) the new words of the first
-  // span, [454,624) those of the second (and word 623 the new word 0). Within a span every lane first reads
-  // all its words (independent loads: one memory round trip per span), then the span is written.
-#pragma unroll 1
-  for (int span = 0; span < 3; span++) {
-    const int first = span * (MT_N - MT_M), last = span == 2 ? MT_N : first + (MT_N - MT_M);
-    uint32_t v[8];
+  // The whole state in registers: word i lives in x[i / 32] of lane i % 32 (twenty independent loads, one
+  // memory round trip). Word i needs word i+1 (the next lane) and word i+397 (old, thirteen lanes on and twelve
+  // registers up) for i < 227, or the regenerated word i-227 (three lanes back, seven registers down) after
+  // that; registers are regenerated in ascending order, so both are in the state the serial loop would see.
+  uint32_t x[20];
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-      const int i = first + lane + 32 * k;
-      v[k] = 0u;
-      if (i < last) {
-        const int i1 = i + 1 == MT_N ? 0 : i + 1;
-        const int im = i + MT_M >= MT_N ? i + MT_M - MT_N : i + MT_M;
-        const uint32_t y = (mt[i] & 0x80000000u) | (mt[i1] & 0x7fffffffu);
-        v[k] = mt[im] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
-      }
-    }
-    __syncwarp();
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      const int i = first + lane + 32 * k;
-      if (i < last) mt[i] = v[k];
-    }
-    __syncwarp();
+  for (int k = 0; k < 20; k++) {
+    const int i = lane + 32 * k;
+    x[k] = i < MT_N ? mt[i] : 0u;
   }
+#pragma unroll
+  for (int k = 0; k < 20; k++) {
+    uint32_t next = __shfl_down_sync(MG_FULL_MASK, x[k], 1);
+    if (k < 19) {
+      const uint32_t wrap = __shfl_sync(MG_FULL_MASK, x[k + 1], 0);
+      if (lane == 31) next = wrap;
+    } else {
+      const uint32_t first = __shfl_sync(MG_FULL_MASK, x[0], 0);  // word 623 pairs with the NEW word 0
+      if (lane == 15) next = first;
+    }
+    uint32_t far = 0u;
+    if (k <= 7) {  // old word i + 397
+      const uint32_t a = __shfl_sync(MG_FULL_MASK, x[k + 12], (lane + 13) & 31);
+      uint32_t b = 0u;
+      if (k + 13 < 20) b = __shfl_sync(MG_FULL_MASK, x[k + 13], (lane + 13) & 31);
+      far = lane + 13 < 32 ? a : b;
+    }
+    if (k >= 7) {  // new word i - 227
+      const uint32_t c = __shfl_sync(MG_FULL_MASK, x[k - 7], (lane - 3) & 31);
+      uint32_t d = 0u;
+      if (k >= 8) d = __shfl_sync(MG_FULL_MASK, x[k - 8], (lane + 29) & 31);
+      const uint32_t regenerated = lane >= 3 ? c : d;
+      if (k > 7 || lane >= 3) far = regenerated;
+    }
+    const uint32_t y = (x[k] & 0x80000000u) | (next & 0x7fffffffu);
+    x[k] = far ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  }
+#pragma unroll
+  for (int k = 0; k < 20; k++) {
+    const int i = lane + 32 * k;
+    if (i < MT_N) mt[i] = x[k];
+  }
+  __syncwarp();
 }
 
 // A warp's view of one env's generator. `buf` optionally holds the next untempered words

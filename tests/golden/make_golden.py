@@ -155,11 +155,34 @@ def arena_mapgen_pool(n=256):
     print("arena_mapgen_pool", cells.shape, {k: round(v, 4) for k, v in occ.items()})
 
 
+def clipper():
+    """Clipper picks (systems/clipper.hpp:140-238). Must run against the reference build whose clipper sets are
+    ordered by object id instead of heap address (oracle/build_ref_ordered.sh, MG_REF_DIR=_ref_ordered): the
+    stock build's pick order differs from process to process. Two fixtures: the clipper_spread scenario (about
+    400 clip and unclip events in 1500 steps) and a cogames mission with clip_period 50 on its own 110x110 map."""
+    assert os.environ.get("MG_REF_DIR") == "_ref_ordered", "run with MG_REF_DIR=_ref_ordered (see oracle/build_ref_ordered.sh)"
+    cfg, grid = SCENARIOS["clipper_spread"]()
+    run("clipper_spread", cfg, grid, 20, 1500)
+    sys.path.insert(0, "/root/reference/packages/cogames/src")
+    from cogames.cogs_vs_clips import missions as M
+    from mettagrid.config.mettagrid_c_config import convert_to_cpp_game_config
+
+    ref_cfg = M.HelloWorldOpenWorldMission.model_copy(update={"num_cogs": 8, "clip_period": 50}).make_env()
+    grid = ref_cfg.game.map_builder.create().build_for_num_agents(ref_cfg.game.num_agents).grid
+    c_cfg = convert_to_cpp_game_config(ref_cfg.game.model_dump())
+    dump = ref_cfg.model_dump()
+    dump["game"]["map_builder"] = None
+    cfg = MettaGridConfig.from_reference(dump)
+    run("cogames_clip_period", cfg, grid, 3, 700, c_cfg=c_cfg)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "clipper":
         cogames_clipper_config()
     elif len(sys.argv) > 1 and sys.argv[1] == "cogames":
         cogames()
+    elif len(sys.argv) > 1 and sys.argv[1] == "clipper_picks":
+        clipper()
     elif len(sys.argv) > 1 and sys.argv[1] == "arena_pool":
         arena_mapgen_pool()
     else:

@@ -100,7 +100,8 @@ def test_cogames_mission_8k_envs(lib):
 
 
 def test_cogames_clipper_mission_lockstep(lib):
-    """RepairMission (clipper with clip_period 50) on the GPU against the oracle, 48 envs x 300 steps."""
+    """RepairMission (clipper with clip_period 50) on the GPU against the oracle, 48 envs x 300 steps. (Which
+    assembler a clip picks is pinned against the reference by the clipper_spread / cogames_clip_period fixtures.)"""
     import json
     import os
 

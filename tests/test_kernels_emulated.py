@@ -157,3 +157,19 @@ def test_emulated_episode_accumulators(emu_lib):
     assert acc[0] == 2 * n
     assert np.allclose(acc, want, rtol=0, atol=1e-3), np.argwhere(~np.isclose(acc, want, rtol=0, atol=1e-3))[:5].tolist()
     ls.close()
+
+
+def test_emulated_clipper_picks_fixture(emu_lib):
+    """The kernels against the reference's own clipper code (fixture from the id-ordered reference build):
+    which assembler gets clipped, with which unclip protocol, and everything downstream, 400 steps."""
+    from golden_util import load
+
+    cfg, grid, d = load("clipper_spread")
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    ls = Lockstep(cfg, names_to_codes(low, grid), num_envs=1, seeds=[int(d["seed"])], clib=emu_lib)
+    assert np.array_equal(ls.buf.obs, d["obs"][0])
+    for s in range(400):
+        ls.step(d["actions"][s])
+        assert np.array_equal(ls.buf.obs, d["obs"][s + 1]), f"step {s}"
+        assert np.array_equal(ls.buf.rew, d["rewards"][s])
+    ls.close()

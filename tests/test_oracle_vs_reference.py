@@ -114,3 +114,43 @@ def test_crowded_rooms_many_seeds(name, seeds, steps, product_lib):
     codes = names_to_codes(low, grid)
     for seed in range(300, 300 + seeds):
         lockstep(cfg, codes, low, seed, steps, invalid_every=41)
+
+
+@needs_ref
+def test_arena_whole_episode(product_lib):
+    """A whole arena episode (10 000 steps, MapGen map): inventories at their limits, float stat totals
+    beyond 2^24, the generator regenerated 190 times."""
+    from metta_b200.maps import arena_mapgen_pool
+
+    cfg = make_arena(24)
+    low = lower_game_config(cfg.game, 62, 62)
+    codes = arena_mapgen_pool(low, 2)[1]
+    from oracle.ref_bridge import RefEnv
+
+    ref = RefEnv(cfg.game, codes_to_names(low, codes), 43)
+    orc = OracleEnv(low.words, codes, 43)
+    rng = np.random.RandomState(1)
+    for s in range(10000):
+        a = rng.randint(0, 5, size=24).astype(np.int32)
+        ref.step(a)
+        orc.step(a)
+        assert np.array_equal(ref.observations, orc.observations) and np.array_equal(ref.rewards, orc.rewards), f"step {s}"
+    assert ref.truncations.all() or ref.terminals.all()
+    assert np.array_equal(ref.terminals, orc.terminals) and np.array_equal(ref.truncations, orc.truncations)
+    assert np.array_equal(ref.episode_rewards(), orc.episode_rewards())
+
+
+@needs_ref
+@pytest.mark.skipif(not os.path.isdir(os.path.join(os.path.dirname(ref_loader.__file__), "_ref_ordered")), reason="oracle/_ref_ordered not built")
+def test_clipper_picks_against_the_id_ordered_reference_build(product_lib):
+    """Clipper::pick_assembler_to_clip walks std::set<Assembler*> in heap-address order (clipper.hpp:207-229),
+    which no two processes share. oracle/build_ref_ordered.sh builds the same reference sources with those
+    sets ordered by object id (a force-included comparator, nothing else changed); against that build the
+    oracle must agree on every clip: several seeds, about 400 clip/unclip events each."""
+    import subprocess
+    import sys
+
+    script = os.path.join(os.path.dirname(os.path.abspath(__file__)), "clipper_ordered_check.py")
+    env = dict(os.environ, MG_REF_DIR="_ref_ordered")
+    out = subprocess.run([sys.executable, script], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
