@@ -104,10 +104,17 @@ int mg_set_early_reset(void* handle, const uint32_t* steps_host);
  * `what` selects a raw array (record layouts: metta_b200/csrc/mg_state.h):
  * 0 env scalars, 1 grid, 2 agents, 3 assemblers, 4 chests, 5 agent stats, 6 game stats,
  * 7 last executed action, 8 action success, 9 finished-episode accumulators, 10 rng state,
- * 11 observations, 12 rewards, 13 terminals, 14 truncations, 15 actions. */
+ * 11 observations, 12 rewards, 13 terminals, 14 truncations, 15 actions, 17 out-of-range action ids per agent
+ * (i32 [N][A][MG_INVALID_WORDS], the record behind the action.invalid_index.<id> stats), 18 token records (what
+ * every object currently shows to observers, i.e. its obs_features(): byte 0 = n, then n u16 feature | value << 8
+ * from byte 8; layout from mg_token_record_layout). */
 int64_t mg_sizeof(void* handle, int32_t what);
 int mg_read(void* handle, int32_t what, void* out_host, int64_t nbytes);
 int mg_write(void* handle, int32_t what, const void* in_host, int64_t nbytes);
+/* out5: bytes per token record, records per env, first record of an env's agents, assemblers, chests (records
+ * before that: one per map cell code). With mg_read what=18 this gives grid_objects() its feature entries
+ * (mettagrid_c.cpp:800-806). */
+int mg_token_record_layout(void* handle, int32_t* out5_host);
 
 /* MettaGrid::set_inventory (mettagrid_c.cpp:959-965): items_amounts = n item ids followed by n amounts. */
 int mg_set_inventory(void* handle, int32_t env, int32_t agent, const int32_t* items_amounts_host, int32_t n);

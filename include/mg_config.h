@@ -14,7 +14,7 @@
 #define MG_CONFIG_H_
 
 #define MG_CONFIG_MAGIC 0x4D473230 /* "MG20" */
-#define MG_CONFIG_VERSION 3
+#define MG_CONFIG_VERSION 4
 
 /* ---- capacity limits (checked at lowering time, errors are loud) ---- */
 #define MG_MAX_RESOURCES 13   /* <= 13 keeps libstdc++'s 13-bucket inventory map collision free */
@@ -168,12 +168,16 @@
 #define MG_GRP_INITIAL_INV (MG_GRP_INVCFG + 1)         /* list, in initial_inventory map order */
 #define MG_GRP_NUM_REWARDS (MG_GRP_INITIAL_INV + MG_LIST_WORDS)
 #define MG_GRP_REWARDS (MG_GRP_NUM_REWARDS + 1)        /* [MG_MAX_REWARDS] x MG_RWD_WORDS, stat_rewards map order */
-#define MG_RWD_WORDS 5
+#define MG_RWD_WORDS 6
 #define MG_RWD_AGENT_STAT 0  /* agent stat slot or -1 */
 #define MG_RWD_GAME_STAT 1   /* game stat slot or -1 */
 #define MG_RWD_WEIGHT 2      /* f32 bits */
 #define MG_RWD_HAS_MAX 3
 #define MG_RWD_MAX 4         /* f32 bits */
+#define MG_RWD_COLLECTIVE 5  /* f32 bits: the agent's collective's value of this stat (agent.cpp:115-117). Collective stats
+                                only change through activation handlers (not lowered), so it is a constant of the config:
+                                aligned.<type> member counts and collective.<res>.deposited of the initial inventory
+                                (objects/collective.hpp:36-62,100-108) */
 #define MG_GRP_DIVERSITY (MG_GRP_REWARDS + MG_MAX_REWARDS * MG_RWD_WORDS) /* [16] mask */
 #define MG_GRP_HAS_REGEN (MG_GRP_DIVERSITY + MG_RES_STRIDE)
 #define MG_GRP_NUM_REGEN (MG_GRP_HAS_REGEN + 1)
@@ -281,6 +285,12 @@
 #define MG_GS_CHEST_DEPOSITED (4 + MG_RES_STRIDE)
 #define MG_GS_CHEST_WITHDRAWN (4 + 2 * MG_RES_STRIDE)
 #define MG_GS_CHEST_AMOUNT (4 + 3 * MG_RES_STRIDE)
-#define MG_GS_COUNT (4 + 4 * MG_RES_STRIDE)
+#define MG_GS_OBJECTS (4 + 4 * MG_RES_STRIDE)         /* [MG_MAX_CELLTYPES] objects.<map cell name>, counted at construction (mettagrid_c.cpp:203,224,235) */
+#define MG_GS_COUNT (MG_GS_OBJECTS + MG_MAX_CELLTYPES)
+
+/* ---- per-agent record of out-of-range action ids (action.invalid_index.<id>, mettagrid_c.cpp:565-569): the first
+ * MG_INVALID_IDS distinct ids an agent sends in an episode with their counts, then a count of all further ones ---- */
+#define MG_INVALID_IDS 4
+#define MG_INVALID_WORDS (2 * MG_INVALID_IDS + 2) /* (id, count) pairs, count of the rest, pairs in use */
 
 #endif /* MG_CONFIG_H_ */

@@ -252,6 +252,18 @@ class Batch:
     def read_action_success(self) -> np.ndarray:
         return self._read(ST_ACTION_SUCCESS, np.uint8, (self.num_envs, self.num_agents)).astype(bool)
 
+    def read_token_records(self) -> tuple[np.ndarray, dict]:
+        """(u8 [N, records per env, bytes per record], layout): what every object currently shows to observers."""
+        lay = np.zeros(5, dtype=np.int32)
+        self._check(self._c.mg_token_record_layout(self._h, lay.ctypes.data))
+        rec = self._read(18, np.uint8, (self.num_envs, int(lay[1]), int(lay[0])))
+        return rec, {"agents": int(lay[2]), "assemblers": int(lay[3]), "chests": int(lay[4])}
+
+    def read_invalid_ids(self) -> np.ndarray:
+        """i32 [N, A, MG_INVALID_WORDS]: per agent the out-of-range action ids it sent this episode as (id, count)
+        pairs, the count of any further ones, and the number of pairs in use (action.invalid_index.<id>)."""
+        return self._read(17, np.int32, (self.num_envs, self.num_agents, L.MG_INVALID_WORDS))
+
     def read_episode_rewards(self) -> np.ndarray:
         return self.read_agents()["episode_reward"].copy()
 

@@ -19,7 +19,7 @@ SYMBOLS = [
     "mg_last_error", "mg_abi_version", "mg_umap_order_u8", "mg_umap_order_str", "mg_create", "mg_destroy",
     "mg_load_maps", "mg_set_buffers", "mg_reset", "mg_step", "mg_step_host", "mg_profile_step", "mg_compute_observations",
     "mg_set_options", "mg_set_early_reset", "mg_sizeof", "mg_read", "mg_write", "mg_set_inventory",
-    "mg_kernel_launches", "mg_sync", "mg_peek_observations_noalloc", "mg_set_host_export", "mg_transfer_bytes", "mg_set_obs_aux",
+    "mg_kernel_launches", "mg_sync", "mg_peek_observations_noalloc", "mg_set_host_export", "mg_transfer_bytes", "mg_set_obs_aux", "mg_token_record_layout",
 ]  # fmt: skip
 
 
@@ -72,6 +72,8 @@ def _declare(l: ctypes.CDLL) -> ctypes.CDLL:
     l.mg_set_host_export.restype = c_int
     l.mg_set_obs_aux.argtypes = [c_void_p] * 4
     l.mg_set_obs_aux.restype = c_int
+    l.mg_token_record_layout.argtypes = [c_void_p, c_void_p]
+    l.mg_token_record_layout.restype = c_int
     l.mg_transfer_bytes.argtypes = [c_void_p, c_void_p, c_void_p]
     l.mg_transfer_bytes.restype = c_int
     l.mg_kernel_launches.argtypes = [c_void_p]

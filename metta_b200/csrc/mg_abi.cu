@@ -342,6 +342,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &b.tok_counts, N * A * 2));
   TRY(dev_alloc(e, &b.last_action, N * A));
   TRY(dev_alloc(e, &b.action_success, N * A));
+  TRY(dev_alloc(e, &b.invalid_ids, N * A * MG_INVALID_WORDS));
   TRY(dev_alloc(e, &b.episode_accum, (size_t)(2 + b.S + b.GS)));
   TRY(dev_alloc(e, &e->d_mask, N));
   TRY(dev_alloc(e, &e->d_seeds, N));
@@ -443,6 +444,27 @@ int mg_load_maps(void* h, int32_t num_maps, const uint16_t* grids, const int32_t
   CUDA_TRY(cudaMemcpy(d_as, asms, M * b.max_asm * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(d_nc, n_chest, M * sizeof(int32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(d_ch, chests, M * b.max_chest * 3 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  {  // objects.<cell name>: walls, assemblers and chests per cell code and map (mettagrid_c.cpp:203,224,235)
+    std::vector<float> counts(M * MG_MAX_CELLTYPES, 0.0f);
+    for (size_t m = 0; m < M; m++) {
+      for (size_t c = 0; c < cells; c++) {
+        const uint16_t g = grids[m * cells + c];
+        if (g != 0 && MG_GRID_KIND(g) == MG_GK_STATIC && g < MG_MAX_CELLTYPES) counts[m * MG_MAX_CELLTYPES + g] += 1.0f;
+      }
+      for (int i = 0; i < n_asm[m]; i++) {
+        const int code = asms[(m * b.max_asm + i) * 3 + 2];
+        if (code > 0 && code < MG_MAX_CELLTYPES) counts[m * MG_MAX_CELLTYPES + code] += 1.0f;
+      }
+      for (int i = 0; i < n_chest[m]; i++) {
+        const int code = chests[(m * b.max_chest + i) * 3 + 2];
+        if (code > 0 && code < MG_MAX_CELLTYPES) counts[m * MG_MAX_CELLTYPES + code] += 1.0f;
+      }
+    }
+    float* d_counts;
+    TRY(dev_alloc(e, &d_counts, counts.size(), false));
+    CUDA_TRY(cudaMemcpy(d_counts, counts.data(), counts.size() * sizeof(float), cudaMemcpyHostToDevice));
+    b.pool_obj_counts = d_counts;
+  }
   {  // first-observation token counts per map: computed by the first env that starts an episode on the map
     uint16_t* d_t0; uint32_t* d_t0v;
     TRY(dev_alloc(e, &d_t0, M * b.A));
@@ -958,7 +980,7 @@ int mg_set_early_reset(void* h, const uint32_t* steps) {
 enum { MG_ST_ENV = 0, MG_ST_GRID = 1, MG_ST_AGENTS = 2, MG_ST_ASMS = 3, MG_ST_CHESTS = 4, MG_ST_AGENT_STATS = 5,
        MG_ST_GAME_STATS = 6, MG_ST_LAST_ACTION = 7, MG_ST_ACTION_SUCCESS = 8, MG_ST_EPISODE_ACCUM = 9, MG_ST_RNG = 10,
        MG_ST_OBS = 11, MG_ST_REWARDS = 12, MG_ST_TERMINALS = 13, MG_ST_TRUNCATIONS = 14, MG_ST_ACTIONS = 15,
-       MG_ST_DEBUG = 16, MG_ST_COUNT = 17 };
+       MG_ST_DEBUG = 16, MG_ST_INVALID_IDS = 17, MG_ST_TOKEN_RECORDS = 18, MG_ST_COUNT = 19 };
 
 static void* state_ptr(MgEnvs* e, int what, size_t* bytes) {
   MgBatch& b = e->b;
@@ -981,6 +1003,8 @@ static void* state_ptr(MgEnvs* e, int what, size_t* bytes) {
     case MG_ST_TRUNCATIONS: *bytes = N * A; return b.truncations;
     case MG_ST_ACTIONS: *bytes = N * A * sizeof(int32_t); return (void*)b.actions;
     case MG_ST_DEBUG: *bytes = b.dbg ? N * 16 * sizeof(uint32_t) : 0; return b.dbg;
+    case MG_ST_TOKEN_RECORDS: *bytes = (N * (size_t)b.rec_slots) << b.rec_shift; return b.etok;
+    case MG_ST_INVALID_IDS: *bytes = N * A * MG_INVALID_WORDS * sizeof(int32_t); return b.invalid_ids;
     default: *bytes = 0; return nullptr;
   }
 }
@@ -1063,6 +1087,20 @@ int mg_set_inventory(void* h, int32_t env, int32_t agent, const int32_t* items_a
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaDeviceSynchronize());
+  return MG_OK;
+}
+
+// Layout of the token records (mg_read what=18): out[0] = bytes per record, out[1] = records per env, out[2..4] = first
+// record of the agents, assemblers and chests of an env (records before out[2] belong to the map cell codes).
+int mg_token_record_layout(void* h, int32_t* out5) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e || !out5) return fail(MG_ERR_ARG, "mg_token_record_layout: bad arguments");
+  const MgBatch& b = e->b;
+  out5[0] = 1 << b.rec_shift;
+  out5[1] = b.rec_slots;
+  out5[2] = (int32_t)(b.rec_kind_base_lo >> 16);
+  out5[3] = (int32_t)(b.rec_kind_base_hi & 0xFFFFu);
+  out5[4] = (int32_t)(b.rec_kind_base_hi >> 16);
   return MG_OK;
 }
 

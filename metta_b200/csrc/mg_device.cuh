@@ -1053,6 +1053,7 @@ MG_DEVICE inline float stat_reward_delta(EnvCtx& e, int ai) {
       v = as < MG_HOT_STATS ? *sp : MG_LD_L2(sp);  // some of these slots are bumped with reductions (at L2)
     }
     v = MG_FADD(v, rw[MG_RWD_GAME_STAT] >= 0 ? MG_LD_L2(&e.gstats[rw[MG_RWD_GAME_STAT]]) : 0.0f);
+    v = MG_FADD(v, MG_INT_AS_FLOAT(rw[MG_RWD_COLLECTIVE]));  // the agent's collective's value of the stat: a constant (mg_config.h)
     float r = MG_FMUL(v, MG_INT_AS_FLOAT(rw[MG_RWD_WEIGHT]));
     if (rw[MG_RWD_HAS_MAX]) {
       float cap = MG_INT_AS_FLOAT(rw[MG_RWD_MAX]);

@@ -281,7 +281,10 @@ MG_DEVICE MG_NOINLINE void reset_env_warp(const MgBatch& b, int env, int lane, E
     for (int i = lane; i < b.A * MG_HOT_STATS / 4; i += 32) hot[i] = zero;
   }
   float* gstats = b.game_stats + (size_t)env * b.GS;
-  for (int i = lane; i < b.GS; i += 32) gstats[i] = 0.0f;
+  for (int i = lane; i < b.GS; i += 32)  // objects.<cell name> are counted at construction: constants of the map
+    gstats[i] = (i >= MG_GS_OBJECTS && i < MG_GS_OBJECTS + MG_MAX_CELLTYPES && b.pool_obj_counts != nullptr)
+                    ? b.pool_obj_counts[(size_t)map * MG_MAX_CELLTYPES + (i - MG_GS_OBJECTS)] : 0.0f;
+  for (int i = lane; i < b.A * MG_INVALID_WORDS; i += 32) b.invalid_ids[(size_t)env * b.A * MG_INVALID_WORDS + i] = 0;
   uint16_t* tc = b.tok_counts + (size_t)env * b.A * 2;
   for (int i = lane; i < b.A; i += 32) { tc[i * 2] = 0; tc[i * 2 + 1] = 0xFFFF; }
   AgentRec* agents = b.agents + (size_t)env * b.A;
@@ -842,6 +845,14 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
     if (a < 0 || a >= nact) {
       float* st = agent_stat(e, ai, MG_AS_INVALID_INDEX);
       *st = MG_FADD(MG_FADD(*st, 1.0f), 1.0f);
+      // action.invalid_index.<id>: the first few distinct ids with their counts, then a count of the rest
+      int32_t* t = b.invalid_ids + ((size_t)env * A + ai) * MG_INVALID_WORDS;
+      const int n = t[2 * MG_INVALID_IDS + 1];
+      int hit = -1;
+      for (int q = 0; q < n; q++)
+        if (t[2 * q] == a) hit = q;
+      if (hit < 0 && n < MG_INVALID_IDS) { hit = n; t[2 * n] = a; t[2 * n + 1] = 0; t[2 * MG_INVALID_IDS + 1] = n + 1; }
+      if (hit >= 0) t[2 * hit + 1] += 2; else t[2 * MG_INVALID_IDS] += 2;
     }
   }
   __syncwarp();

@@ -140,6 +140,7 @@ struct MgBatch {
   const int32_t* pool_asm;     // [M][max_asm][3]
   const int32_t* pool_n_chest; // [M]
   const int32_t* pool_chest;   // [M][max_chest][3]
+  const float* pool_obj_counts; // [M][MG_MAX_CELLTYPES] walls, assemblers and chests per cell code: the objects.<name> game stats
   uint16_t* pool_tok0;         // [M][A] token count of every agent's first observation on this map (filled on first use; without a clipper it depends on the map alone)
   uint32_t* pool_tok0_valid;   // [M] 1 once pool_tok0[m] is complete
   // state
@@ -159,6 +160,7 @@ struct MgBatch {
   uint16_t* tok_counts;        // [N][A][2] written, attempted: produced by the observation kernel
   int32_t* last_action;        // [N][A] executed action (0 when it failed), mettagrid_c.cpp:595-620
   uint8_t* action_success;     // [N][A]
+  int32_t* invalid_ids;        // [N][A][MG_INVALID_WORDS] out-of-range action ids per agent (action.invalid_index.<id>)
   long long* episode_accum;    // [2 + S + GS] sums over finished episodes (for infos / NCCL reduce), fixed point with 16 fraction bits:
                                // integer atomics only (double arithmetic measured ~1000 cycles per instruction on this part); mg_read converts
   MgQueueCtl* qctl;            // queue control block and entries [N] (see above)

@@ -201,7 +201,8 @@ def _invcfg(blob: _Blob, base: int, rid: dict[str, int], inv: InventoryConfig, w
         w[base + L.MG_INVCFG_ORDER + i] = insert_order[pos]
 
 
-def _stat_slots(name: str, rid: dict[str, int], own_group: str, group_index: dict[str, int]) -> tuple[int, int]:
+def _stat_slots(name: str, rid: dict[str, int], own_group: str, group_index: dict[str, int],
+                cell_codes: dict[str, int] | None = None) -> tuple[int, int]:
     """Resolve a stat name used as a reward key to (agent slot, game slot), -1 = never emitted.
 
     Names: SURVEY.md Appendix C (action_handler.hpp:102-149, agent.cpp:78-99,171-175,
@@ -268,8 +269,8 @@ def _stat_slots(name: str, rid: dict[str, int], own_group: str, group_index: dic
             a = L.MG_AS_TRANSFER_SELF + rid[rest[0]]
         if len(rest) == 3 and rest[0] in rid and rest[1] == "to" and rest[2] in group_index:
             a = L.MG_AS_TRANSFER_TO + group_index[rest[2]] * L.MG_RES_STRIDE + rid[rest[0]]
-    if name.startswith("objects."):
-        raise NotImplementedError(f"stat reward on per-map static counter {name!r} is not supported")
+    if name.startswith("objects.") and cell_codes and name[len("objects.") :] in cell_codes:
+        g = L.MG_GS_OBJECTS + cell_codes[name[len("objects.") :]]  # counted per map when an episode starts
     return a, g
 
 
@@ -311,8 +312,6 @@ def _i32(x: int) -> int:
 def lower_game_config(
     game: GameConfig, map_h: int, map_w: int, max_assemblers: int = 0, max_chests: int = 0
 ) -> LoweredConfig:
-    if game.collectives:
-        raise NotImplementedError("collectives are not supported yet (SURVEY.md 2.2: thin, reward-only)")
     resource_names = list(game.resource_names)
     R = len(resource_names)
     if R > L.MG_MAX_RESOURCES:
@@ -538,6 +537,35 @@ def lower_game_config(
         for n in names:
             cell_codes[n] = len(cell_defs)  # later registrations win, like the dict in the reference
 
+    # collectives (objects/collective.hpp): only agents are Alignable, and a collective's stats move only through
+    # activation handlers (not lowered), so what an agent's collective adds to a reward term is a constant:
+    # aligned.agent = members (addMember :36-43), collective.<res>.deposited = the initial inventory (:100-108).
+    # An object joins the collective its LAST "collective:<name>" tag names (mettagrid_c.cpp:102-131).
+    collective_names = {c.name for c in game.collectives}
+
+    def collective_of(ac) -> str | None:
+        name = None
+        for t in ac.tags:
+            if t.startswith("collective:") and t[len("collective:") :] in collective_names:
+                name = t[len("collective:") :]
+        return name
+
+    collective_members = {c.name: sum(1 for ac in agents if collective_of(ac) == c.name) for c in game.collectives}
+    collective_cfg = {c.name: c for c in game.collectives}
+
+    def collective_stat(ac, stat: str) -> float:
+        cname = collective_of(ac)
+        if cname is None:
+            return 0.0
+        if stat == "aligned.agent":
+            return float(collective_members[cname])
+        parts = stat.split(".")
+        if len(parts) == 3 and parts[0] == "collective" and parts[2] == "deposited":
+            amount = collective_cfg[cname].inventory.initial.get(parts[1], 0) if parts[1] in rid else 0
+            return float(amount) if amount > 0 else 0.0
+        return 0.0
+
+    pending_object_rewards: list[tuple[int, str]] = []
     group_recs: list[int] = []
     for gi, (team_id, members) in enumerate(teams.items()):
         first = members[0]
@@ -591,6 +619,9 @@ def lower_game_config(
             w[ro + L.MG_RWD_WEIGHT] = f32_bits(stat_rewards[nm])
             w[ro + L.MG_RWD_HAS_MAX] = int(nm in stat_max)
             w[ro + L.MG_RWD_MAX] = f32_bits(stat_max.get(nm, 0.0))
+            w[ro + L.MG_RWD_COLLECTIVE] = f32_bits(collective_stat(first, nm))
+            if nm.startswith("objects."):
+                pending_object_rewards.append((gi * L.MG_GRP_WORDS + (ro - go) + L.MG_RWD_GAME_STAT, nm[len("objects.") :]))
             # goal tokens, mettagrid_c.cpp:363-395
             dot = nm.find(".")
             if dot >= 0:
@@ -710,7 +741,7 @@ def lower_game_config(
 
     if len(asm_recs) > L.MG_MAX_ASM_TYPES or len(chest_recs) > L.MG_MAX_CHEST_TYPES:
         raise ValueError("too many assembler/chest types")
-    if len(cell_defs) > L.MG_MAX_CELLTYPES:
+    if len(cell_defs) >= L.MG_MAX_CELLTYPES:  # codes 1..MG_MAX_CELLTYPES-1 (a game stat slot each)
         raise ValueError("too many cell types")
 
     # ---- clipper (mettagrid_c_config.py:512-546)
@@ -741,6 +772,11 @@ def lower_game_config(
     w[L.MGC_OFF_GROUPS] = off_g
     for i, src in enumerate(group_recs):
         w[off_g + i * L.MG_GRP_WORDS : off_g + (i + 1) * L.MG_GRP_WORDS] = w[src : src + L.MG_GRP_WORDS]
+
+    for rel, cell_name in pending_object_rewards:  # reward terms on objects.<cell name>: a per-map game stat slot
+        code = cell_codes.get(cell_name)
+        if code is not None and cell_defs[code - 1]["kind"] != L.MG_KIND_AGENT:
+            w[off_g + rel] = L.MG_GS_OBJECTS + code
 
     off_i = blob.alloc(max(1, len(invcfg_offsets)) * L.MG_INVCFG_WORDS)
     w[L.MGC_OFF_INVCFG] = off_i

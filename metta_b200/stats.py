@@ -64,18 +64,33 @@ def game_stat_names(lowered: LoweredConfig) -> dict[int, str]:
     return out
 
 
-def agent_stats_dict(lowered: LoweredConfig, group: int, slots: np.ndarray) -> dict[str, float]:
+def agent_stats_dict(lowered: LoweredConfig, group: int, slots: np.ndarray, invalid_ids: np.ndarray | None = None) -> dict[str, float]:
+    """`invalid_ids`: the agent's i32[MG_INVALID_WORDS] record (Batch.read_invalid_ids) for the per-id breakdown
+    action.invalid_index.<id> (mettagrid_c.cpp:565-569); ids beyond the first MG_INVALID_IDS distinct ones of an
+    episode are reported together as action.invalid_index.other."""
     names = agent_stat_names(lowered, group)
     out: dict[str, float] = {}
     for slot in np.nonzero(slots)[0]:
         for n in names.get(int(slot), []):
             out[n] = float(slots[slot])
+    if invalid_ids is not None:
+        n = int(invalid_ids[2 * L.MG_INVALID_IDS + 1])
+        for q in range(n):
+            out[f"action.invalid_index.{int(invalid_ids[2 * q])}"] = float(invalid_ids[2 * q + 1])
+        if invalid_ids[2 * L.MG_INVALID_IDS]:
+            out["action.invalid_index.other"] = float(invalid_ids[2 * L.MG_INVALID_IDS])
     return out
 
 
 def game_stats_dict(lowered: LoweredConfig, slots: np.ndarray, map_codes: np.ndarray | None = None) -> dict[str, float]:
     names = game_stat_names(lowered)
     out = {names[int(s)]: float(slots[s]) for s in np.nonzero(slots)[0] if int(s) in names}
+    if len(slots) >= L.MG_GS_OBJECTS + L.MG_MAX_CELLTYPES:  # objects.<cell name> live in slots of their own
+        for code, name in lowered.cell_names.items():
+            v = float(slots[L.MG_GS_OBJECTS + code]) if code < L.MG_MAX_CELLTYPES else 0.0
+            if v:
+                out[f"objects.{name}"] = v
+        return out
     if map_codes is not None:  # objects.<cell name>, counted at construction (mettagrid_c.cpp:203,224,235)
         codes, counts = np.unique(map_codes, return_counts=True)
         for code, n in zip(codes, counts):

@@ -271,6 +271,14 @@ class GpuMettaGridVecEnv:
         """bool [num_envs, agents_per_env]: MettaGrid::action_success of the last step."""
         return self.batch.read_action_success()
 
+    def grid_objects(self, env_index: int = 0, min_row: int = -1, max_row: int = -1, min_col: int = -1, max_col: int = -1,
+                     ignore_types: Sequence[str] = ()) -> dict[int, dict]:
+        """MettaGrid::grid_objects (mettagrid_c.cpp:754-868) of one env: the reference's dicts, same ids, keys and
+        inventory iteration order (a host-side tooling path: it reads the env's records back)."""
+        from .grid_objects import grid_objects
+
+        return grid_objects(self.batch, env_index, min_row, max_row, min_col, max_col, tuple(ignore_types))
+
     def set_mg_config(self, cfg, maps: Optional[Sequence] = None, map_codes: Optional[np.ndarray] = None) -> None:
         """CurriculumEnv's hook (metta/rl/.../curriculum_env.py:105-117): the next `async_reset` builds the
         batch from this config (and these maps; the current pool is kept when none are given and the map

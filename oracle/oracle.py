@@ -45,6 +45,8 @@ def lib() -> ctypes.CDLL:
         for name in ("mgo_agent_state", "mgo_assembler_state", "mgo_chest_state"):
             getattr(l, name).argtypes = [vp, i32, vp]
         l.mgo_set_inventory.argtypes = [vp, i32, vp, vp, i32]
+        l.mgo_invalid_ids.argtypes = [vp, i32]
+        l.mgo_invalid_ids.restype = vp
         l.mgo_get_rng.argtypes = [vp, vp]
         l.mgo_set_rng.argtypes = [vp, vp]
         _lib = l
@@ -138,6 +140,11 @@ class OracleEnv:
         items = np.asarray([p[0] for p in pairs], dtype=np.int32)
         amounts = np.asarray([p[1] for p in pairs], dtype=np.int32)
         lib().mgo_set_inventory(self._h, agent, items.ctypes.data, amounts.ctypes.data, len(items))
+
+    def invalid_ids(self) -> np.ndarray:
+        """i32 [A][MG_INVALID_WORDS]: the record behind action.invalid_index.<id>."""
+        n = self.L.MG_INVALID_WORDS
+        return np.stack([self._arr(lib().mgo_invalid_ids(self._h, i), n, ctypes.c_int32) for i in range(self.num_agents)])
 
     def get_rng(self) -> np.ndarray:
         """The env generator: 624 state words followed by the position (std::mt19937 _M_x, _M_p). Test hook."""

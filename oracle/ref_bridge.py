@@ -204,6 +204,14 @@ def to_reference_config(game: GameConfig):
     )
     if game.reward_estimates is not None:
         kwargs["reward_estimates"] = game.reward_estimates
+    if game.collectives:  # mettagrid_c_config.py:543-575
+        colls = {}
+        for c in game.collectives:
+            cc_ = C.CollectiveConfig(c.name)
+            cc_.inventory_config = _limit_defs(C, c.inventory, rid, resource_names, False)
+            cc_.initial_inventory = {rid[k]: v for k, v in c.inventory.initial.items() if k in rid}
+            colls[c.name] = cc_
+        kwargs["collectives"] = colls
     if game.clipper is not None:
         cc = C.ClipperConfig()
         cc.unclipping_protocols = [_protocol(C, p, rid, vid) for p in game.clipper.unclipping_protocols]

@@ -183,6 +183,51 @@ def _twin_set_inventory(self, inventory):
         kt.batch.set_inventory(0, self._agent_id, ids)
 
 
+_orig_grid_objects = sim_mod.Simulation.grid_objects
+
+
+def _same_objects(ref: dict, mine: dict) -> str | None:
+    if set(ref) != set(mine):
+        return f"object ids differ: {sorted(set(ref) ^ set(mine))[:6]}"
+    for k, ro in ref.items():
+        mo = mine[k]
+        if set(ro) != set(mo):
+            return f"object {k} ({ro.get('type_name')}): keys differ {sorted(set(ro) ^ set(mo))}"
+        for f, v in ro.items():
+            mv = mo[f]
+            if f == "protocols":
+                ok = sorted(repr({**x, "inputs": dict(x["inputs"]), "outputs": dict(x["outputs"])}) for x in v) == sorted(map(repr, mv))
+            elif f == "vibe_transfers":
+                ok = {a: dict(b) for a, b in v.items()} == mv
+            elif isinstance(v, dict):
+                ok = list(v.items()) == list(mv.items())  # iteration order included (inventory tokens follow it)
+            elif isinstance(v, float):
+                ok = abs(v - mv) < 1e-6
+            else:
+                ok = v == mv
+            if not ok:
+                return f"object {k} ({ro.get('type_name')}): {f} = {mv!r}, reference {v!r}"
+    return None
+
+
+def _twin_grid_objects(self, bbox=None, ignore_types=None):
+    ref = _orig_grid_objects(self, bbox, ignore_types)
+    kt = getattr(self, "_kernel_twin", None)
+    if kt is not None:
+        from metta_b200.grid_objects import grid_objects
+
+        if bbox is None:
+            mine = grid_objects(kt.batch, 0, ignore_types=tuple(ignore_types or ()))
+        else:
+            mine = grid_objects(kt.batch, 0, bbox.min_row, bbox.max_row, bbox.min_col, bbox.max_col, tuple(ignore_types or ()))
+        why = _same_objects(ref, mine)
+        if why is not None:
+            raise AssertionError(f"kernel twin: grid_objects() differ from the reference: {why} ({_current_test[0]})")
+        STATS["grid_objects compared"] += 1
+    return ref
+
+
+sim_mod.Simulation.grid_objects = _twin_grid_objects
 sim_mod.Simulation.__init__ = _twin_init
 sim_mod.Simulation.step = _twin_step
 sim_mod.Simulation.close = _twin_close
@@ -231,7 +276,7 @@ def main():
         f"simulations constructed {STATS['simulations']}, with an oracle twin {STATS['twinned']}, "
         f"steps compared byte for byte {STATS['steps compared']}, set_inventory calls mirrored {STATS['set_inventory mirrored']}",
         f"kernel twins (the CUDA sources on tests/simt_emu, through the C-ABI) {STATS['kernel twins']}, "
-        f"steps compared byte for byte {STATS['kernel steps compared']}",
+        f"steps compared byte for byte {STATS['kernel steps compared']}, grid_objects() calls compared {STATS['grid_objects compared']}",
         "",
         "Simulations without a twin (config outside the hot path):",
     ]

@@ -120,6 +120,7 @@ class Lockstep:
         asm = self.batch.read_assemblers()
         ch = self.batch.read_chests()
         succ = self.batch.read_action_success()
+        inval = self.batch.read_invalid_ids()
         RS = L.MG_RES_STRIDE
         for i, o in enumerate(self.checkers):
             s = o.agent_state()
@@ -135,6 +136,7 @@ class Lockstep:
             g_ref = o.game_stats()
             assert np.array_equal(gs[i], g_ref), f"env {i}: game stats differ at {np.argwhere(gs[i] != g_ref)[:4].tolist()}"
             assert np.array_equal(succ[i], o.action_success()), f"env {i}: action_success"
+            assert np.array_equal(inval[i], o.invalid_ids()), f"env {i}: record of out-of-range action ids"
             os_ = o.assembler_state()
             n = len(os_)
             if n:

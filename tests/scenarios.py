@@ -304,5 +304,40 @@ def clipper_spread() -> tuple[MettaGridConfig, np.ndarray]:
     return MettaGridConfig(game=game), ascii_map(rows, legend)
 
 
+def collective_rewards() -> tuple[MettaGridConfig, np.ndarray]:
+    """Collectives as the core uses them without activation handlers (objects/collective.hpp, agent.cpp:115-117):
+    membership by "collective:<name>" tag, reward terms that read the collective's stats (aligned.agent,
+    collective.<res>.deposited of its initial inventory), plus reward terms on objects.<cell name> game stats."""
+    def agent(team, coll):
+        return {
+            "team_id": team,
+            "tags": ["agent", f"collective:{coll}"],
+            "inventory": {"default_limit": 20, "initial": {"heart": 1}},
+            "rewards": {
+                "inventory": {"heart": 0.5},
+                "stats": {"aligned.agent": 0.25, "collective.heart.deposited": 0.125, "collective.ore.deposited": 2.0,
+                          "objects.wall": 0.0078125, "objects.altar": 0.5, "action.invalid_index": 0.0625, "objects.nothing": 3.0},
+                "stats_max": {"objects.wall": 0.25},
+            },
+        }
+
+    game = {
+        "resource_names": ["heart", "ore"],
+        "num_agents": 5,
+        "max_steps": 0,
+        "obs": {"width": 5, "height": 5, "num_tokens": 40},
+        "agents": [agent(0, "red"), agent(0, "red"), agent(0, "red"), agent(1, "blue"), agent(1, "blue")],
+        "collectives": [{"name": "red", "inventory": {"initial": {"heart": 6}}}, {"name": "blue", "inventory": {"initial": {"ore": 3, "heart": 0}}}],
+        "actions": {"noop": {}, "move": {}, "change_vibe": {"enabled": False}},
+        "objects": {
+            "wall": {"pydantic_type": "wall", "name": "wall"},
+            "altar": {"pydantic_type": "assembler", "name": "altar", "protocols": [{"output_resources": {"heart": 1}, "cooldown": 2}]},
+        },
+    }
+    legend = {"#": "wall", ".": "empty", "A": "altar", "a": "agent.team_0", "b": "agent.team_1"}
+    rows = ["########", "#a.A..b#", "#..a.A.#", "#b...a.#", "########"]
+    return MettaGridConfig(game=game), ascii_map(rows, legend)
+
+
 SCENARIOS = {"kitchen_sink": kitchen_sink, "tiny_truncating": tiny_truncating, "clipped_start": clipped_start,
-             "dense_conflict": dense_conflict, "crowd_48": crowd_48, "clipper_spread": clipper_spread}
+             "dense_conflict": dense_conflict, "crowd_48": crowd_48, "clipper_spread": clipper_spread, "collective_rewards": collective_rewards}

@@ -57,7 +57,7 @@ def test_cuda_reproduces_reference_fixture(name, lib):
     b.close()
 
 
-@pytest.mark.parametrize("name,steps", [("kitchen_sink", 400), ("tiny_truncating", 40), ("clipped_start", 200)])
+@pytest.mark.parametrize("name,steps", [("kitchen_sink", 400), ("tiny_truncating", 40), ("clipped_start", 200), ("collective_rewards", 200)])
 def test_scenarios_vs_oracle(name, steps, lib):
     cfg, grid = SCENARIOS[name]()
     low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
@@ -66,7 +66,7 @@ def test_scenarios_vs_oracle(name, steps, lib):
     ls.compare_outputs()
     rng = np.random.RandomState(5)
     for s in range(steps):
-        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=31, step=s))
+        ls.step(random_actions(rng, cfg, ls.lowered, ls.N * ls.A, invalid_every=3 if name == "collective_rewards" else 31, step=s))
         if name != "tiny_truncating" and s % 100 == 99:
             ls.compare_state()
     ls.close()

@@ -198,3 +198,31 @@ def test_host_mode_uses_page_locked_arrays_and_matches_device_mode():
         assert np.array_equal(r_h, r_d.cpu().numpy()) and np.array_equal(d_h, d_d.cpu().numpy()) and np.array_equal(t_h, t_d.cpu().numpy())
     dev_env.close()
     host_env.close()
+
+
+def test_grid_objects_dicts_match_the_compiled_reference():
+    """GpuMettaGridVecEnv.grid_objects(): the reference's dicts (mettagrid_c.cpp:754-868) rebuilt from the
+    device records, against the compiled reference stepping the same env."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("compiled reference (oracle/_ref) not present")
+    from oracle.ref_bridge import RefEnv
+    from test_kernels_emulated import _same_grid_objects
+
+    cfg, low, codes, env = _make("kitchen_sink", 3)
+    A = cfg.game.num_agents
+    env.reset(seed=11)
+    from metta_b200.maps import codes_to_names
+
+    refs = [RefEnv(cfg.game, codes_to_names(low, codes), 11 + i) for i in range(3)]
+    rng = np.random.RandomState(2)
+    for s in range(50):
+        a = random_actions(rng, cfg, low, 3 * A)
+        env.step(a)
+        for i, r in enumerate(refs):
+            r.step(a[i * A : (i + 1) * A])
+        if s % 10 == 9:
+            for i, r in enumerate(refs):
+                _same_grid_objects(r.grid_objects(), env.grid_objects(i))
+    env.close()

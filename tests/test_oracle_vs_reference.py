@@ -39,7 +39,7 @@ def lockstep(cfg, codes, low, seed, steps, invalid_every=0):
 
 
 @needs_ref
-@pytest.mark.parametrize("name,steps", [("kitchen_sink", 400), ("tiny_truncating", 12), ("clipped_start", 200)])
+@pytest.mark.parametrize("name,steps", [("kitchen_sink", 400), ("tiny_truncating", 12), ("clipped_start", 200), ("collective_rewards", 300)])
 @pytest.mark.parametrize("seed", [1, 99])
 def test_scenarios(name, steps, seed, product_lib):
     cfg, grid = SCENARIOS[name]()
@@ -49,7 +49,7 @@ def test_scenarios(name, steps, seed, product_lib):
     from metta_b200.stats import agent_stats_dict, game_stats_dict
 
     st = ref.episode_stats()
-    game = game_stats_dict(low, orc.game_stats(), names_to_codes(low, grid))
+    game = game_stats_dict(low, orc.game_stats())
     for k, v in st["game"].items():
         assert game.get(k, 0.0) == pytest.approx(v), k
     astats = orc.agent_stats()
@@ -60,10 +60,8 @@ def test_scenarios(name, steps, seed, product_lib):
     for i, ref_stats in enumerate(st["agent"]):
         cell = int(pool.agents[0, i, 2])
         grp = int(low.words[low.words[L.MGC_OFF_CELLTYPES] + cell * L.MG_CELL_WORDS + L.MG_CELL_PARAM])
-        mine = agent_stats_dict(low, grp, astats[i])
+        mine = agent_stats_dict(low, grp, astats[i], orc.invalid_ids()[i])
         for k, v in ref_stats.items():
-            if k.startswith("action.invalid_index."):
-                continue  # per-id breakdown is not tracked
             assert mine.get(k, 0.0) == pytest.approx(v), (i, k)  # zero-valued keys are omitted
 
 
