@@ -41,7 +41,10 @@
 template <int MAXA>
 struct StepSmem {
   AgentRec ag[MAXA];
-  float hot[MAXA * MG_HOT_STATS];
+  float hot[MAXA * MG_HOT_STATS];  // (16-byte aligned: it follows whole 64-byte records)
+  unsigned long long stage_bar;    // mbarrier of the bulk copies that stage ag and hot (step_smem_init)
+  uint32_t stage_phase;            // its current phase bit
+  uint32_t publish;                // the env's writes must be complete when the step returns (the fused kernel hands envs to other SMs)
   int32_t action[MAXA];
   int32_t executed[MAXA];
   uint8_t success[MAXA];
@@ -625,6 +628,19 @@ MG_DEVICE MG_NOINLINE void clipper_step_warp(const MgBatch& b, EnvCtx& e, int32_
 // memory was three times the real data traffic, see profiles/r01e). All phases are called by the
 // full warp.
 
+// Once per warp, before its first env.
+template <int MAXA>
+MG_DEVICE inline void step_smem_init(StepSmem<MAXA>& sm, int lane, bool publish) {
+  if (lane == 0) {
+#ifdef MG_HAS_BULK_COPY
+    mg_mbar_init(reinterpret_cast<uint64_t*>(&sm.stage_bar), 1u);
+#endif
+    sm.stage_phase = 0u;
+    sm.publish = publish ? 1u : 0u;
+  }
+  __syncwarp();
+}
+
 // Phase 1: bring the env in (and start a new episode first if the last one ended).
 template <int MAXA>
 MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
@@ -637,6 +653,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
   // and their 16 per-step stat slots (16-byte loads), actions, the pending token counts of the last
   // observation pass and the three float totals they are folded into.
   constexpr int NV = MAXA * 4 / 32;  // 16-byte loads per lane for records (and for hot stats)
+  (void)NV;
   constexpr int NA = (MAXA + 31) / 32;
   const size_t abase = (size_t)env * A;
 #ifdef MG_PREFETCH_ENV
@@ -653,13 +670,32 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
 #endif
 #endif
   for (bool fresh = false;;) {
+#ifndef MG_HAS_BULK_COPY
     uint4 ag_v[NV], hot_v[NV];
+#endif
     int32_t act_v[NA];
     uint32_t tc_v[NA];
     const uint4* ag_src = reinterpret_cast<const uint4*>(b.agents + abase);
     const uint4* hot_src = reinterpret_cast<const uint4*>(b.hot_stats + abase * MG_HOT_STATS);
     uint16_t* tc = b.tok_counts + abase * 2;
     float* gs = b.game_stats + (size_t)env * b.GS;
+#ifdef MG_HAS_BULK_COPY
+    // agent records and hot stat slots: two bulk copies (TMA) straight into the warp's shared block, issued by
+    // one lane and waited for on the block's mbarrier further down; no registers, no per-lane address math
+    if (fresh) {
+      // the records were just written by this warp's own (generic) stores: read them back the same way
+      for (int i = lane; i < A * 4; i += 32) {
+        reinterpret_cast<uint4*>(sm.ag)[i] = ag_src[i];
+        reinterpret_cast<uint4*>(sm.hot)[i] = hot_src[i];
+      }
+    } else if (lane == 0) {
+      uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.stage_bar);
+      const uint32_t bytes = (uint32_t)A * (uint32_t)sizeof(AgentRec);
+      mg_mbar_expect_tx(bar, 2u * bytes);
+      mg_bulk_load(sm.ag, ag_src, bytes, bar);
+      mg_bulk_load(sm.hot, hot_src, bytes, bar);
+    }
+#else
 #pragma unroll
     for (int k = 0; k < NV; k++) {
       const int i = lane + 32 * k;
@@ -668,6 +704,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
         hot_v[k] = hot_src[i];
       }
     }
+#endif
 #pragma unroll
     for (int k = 0; k < NA; k++) {
       const int ai = lane + 32 * k;
@@ -723,6 +760,12 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     }
     MG_SM_TICK(sm, 0);
     if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
+#ifdef MG_HAS_BULK_COPY
+      mg_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_bar), sm.stage_phase);  // the old episode's records: let the copy land, then drop it
+      __syncwarp();
+      if (lane == 0) sm.stage_phase ^= 1u;
+      __syncwarp();
+#endif
       {  // everything the episode change will read, requested now
         const int next_map = b.num_maps > 0 ? (er.map_idx + b.map_stride) % b.num_maps : er.map_idx;
         prefetch_range_warp(b.pool_grid + (size_t)next_map * b.grid_stride, (size_t)b.grid_stride * sizeof(uint16_t), lane);
@@ -743,6 +786,13 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       fresh = true;
       continue;  // load the new episode's state
     }
+#ifdef MG_HAS_BULK_COPY
+    if (!fresh) {
+      mg_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_bar), sm.stage_phase);
+      __syncwarp();
+      if (lane == 0) sm.stage_phase ^= 1u;
+    }
+#else
 #pragma unroll
     for (int k = 0; k < NV; k++) {
       const int i = lane + 32 * k;
@@ -751,6 +801,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
         reinterpret_cast<uint4*>(sm.hot)[i] = hot_v[k];
       }
     }
+#endif
 #pragma unroll
     for (int k = 0; k < NA; k++) {
       const int ai = lane + 32 * k;
@@ -1083,6 +1134,21 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
     const uint4* src = reinterpret_cast<const uint4*>(sm.ag);
     const uint4* hot = reinterpret_cast<const uint4*>(sm.hot);
     uint4* hot_dst = reinterpret_cast<uint4*>(b.hot_stats + (size_t)env * A * MG_HOT_STATS);
+#ifdef MG_HAS_BULK_COPY
+    // two bulk copies (TMA) from the shared block: every lane's writes to it are made visible to the async proxy
+    // first; one lane issues and then only waits until the block has been read (until the writes have been
+    // performed where the env is handed to another SM right away)
+    (void)src; (void)hot; (void)NV;
+    mg_bulk_store_fence();
+    __syncwarp();
+    if (lane == 0) {
+      const uint32_t bytes = (uint32_t)A * (uint32_t)sizeof(AgentRec);
+      mg_bulk_store(dst, sm.ag, bytes);
+      mg_bulk_store(hot_dst, sm.hot, bytes);
+      mg_bulk_store_commit();
+      if (sm.publish) mg_bulk_store_wait_all(); else mg_bulk_store_wait_read();
+    }
+#else
 #pragma unroll
     for (int k = 0; k < NV; k++) {
       const int i = lane + 32 * k;
@@ -1091,8 +1157,10 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
         hot_dst[i] = hot[i];
       }
     }
+#endif
   }
   if (lane == 0) copy_env_rec(&b.env[env], &er);
+  __syncwarp();
 }
 
 // One env, one warp: the five phases.
@@ -1145,6 +1213,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
   const MgBatch& b = cfg_fits ? batch_s : b_param;
   const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
   if (env >= b.env_end) return;
+  step_smem_init<MAXA>(smem[warp], lane, false);
   step_env_warp<MAXA>(b, smem[warp], env, lane);
 }
 
@@ -1163,6 +1232,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(32, MG_QUEUE_STEP_MIN_CTAS) mg_step_queue_kernel
   const int lane = threadIdx.x & 31;
   const int env = b.env_begin + (int)blockIdx.x;
   if (env >= b.env_end) return;
+  step_smem_init<MAXA>(sm, lane, true);
   step_env_warp<MAXA>(b, sm, env, lane);
   // publish: every lane's writes first, then the entry
   __threadfence();
@@ -1370,6 +1440,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_FUSED_WARPS * 32, MG_FUSED_MIN_CTAS) mg_fused
   MgQueueCtl* ctl = b.qctl;
   const uint32_t n_envs = (uint32_t)(b.env_end - b.env_begin);
   const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&ctl->epoch);
+  step_smem_init<MAXA>(sm, lane, true);
   for (;;) {  // ---- stepping
     uint32_t k = 0;
     if (lane == 0) k = atomicAdd(&ctl->env_next, 1u);

@@ -49,6 +49,46 @@
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif
 
+#ifndef MG_SIMT_EMU
+// ---- 1-D bulk copies (TMA, cp.async.bulk) between this GPU's HBM and shared memory, completion on an mbarrier.
+// One thread issues a copy of any multiple of 16 bytes; the data never passes through registers.
+#define MG_HAS_BULK_COPY 1
+__device__ __forceinline__ uint32_t mg_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mg_mbar_init(uint64_t* bar, uint32_t arrivals) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mg_smem_addr(bar)), "r"(arrivals) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // the async proxy must see the initialised barrier
+}
+__device__ __forceinline__ void mg_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mg_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mg_bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(mg_smem_addr(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(mg_smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mg_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MG_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra MG_DONE_%=;\n"
+      "bra MG_WAIT_%=;\n"
+      "MG_DONE_%=:\n"
+      "}\n" ::"r"(mg_smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+// shared -> global; the caller has made its shared-memory writes visible to the async proxy (mg_bulk_store_fence)
+__device__ __forceinline__ void mg_bulk_store_fence() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mg_bulk_store(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(mg_smem_addr(smem_src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mg_bulk_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void mg_bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }  // shared memory may be reused
+__device__ __forceinline__ void mg_bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }        // the writes have been performed
+#endif
+
 #define MG_FULL_MASK 0xFFFFFFFFu
 
 #endif  // MG_PLATFORM_H_
