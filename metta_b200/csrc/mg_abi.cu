@@ -242,6 +242,37 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
       }
     }
   }
+  {  // one line per map cell code with everything a use of a one-protocol assembler reads (assembler_use_warp)
+    std::vector<int32_t> fast((size_t)MG_MAX_CELLTYPES * MG_AF_WORDS, 0);
+    for (int c = 1; c < cfg[MGC_NUM_CELLTYPES] && c < MG_MAX_CELLTYPES; c++) {
+      const int32_t* cc = cfg + cfg[MGC_OFF_CELLTYPES] + c * MG_CELL_WORDS;
+      if (cc[MG_CELL_KIND] != MG_KIND_ASSEMBLER) continue;
+      const int32_t* ty = cfg + cfg[MGC_OFF_ASM_TYPES] + cc[MG_CELL_PARAM] * MG_ASM_WORDS;
+      int32_t* f = &fast[(size_t)c * MG_AF_WORDS];
+      f[MG_AF_MAX_USES] = ty[MG_ASM_MAX_USES];
+      f[MG_AF_PARTIAL] = ty[MG_ASM_ALLOW_PARTIAL];
+      f[MG_AF_CHEST_DISTANCE] = ty[MG_ASM_CHEST_DISTANCE];
+      if (ty[MG_ASM_NUM_PROTOCOLS] != 1) continue;
+      const int pi = ty[MG_ASM_FIRST_PROTOCOL];
+      const int32_t* p = cfg + cfg[MGC_OFF_PROTOCOLS] + pi * MG_PROTO_WORDS;
+      // the one protocol must be what get_current_protocol finds for a lone actor of any vibe: key 0, min_agents <= 1
+      if (p[MG_PROTO_KEY_LO] != 0 || p[MG_PROTO_KEY_HI] != 0 || p[MG_PROTO_MIN_AGENTS] > 1) continue;
+      const int32_t* lin = p + MG_PROTO_INPUTS;
+      const int32_t* lout = p + MG_PROTO_OUTPUTS;
+      if (lin[MG_LIST_N] > 4 || lout[MG_LIST_N] > 4) continue;
+      f[MG_AF_COOLDOWN] = p[MG_PROTO_COOLDOWN] & 0xFFFF;
+      f[MG_AF_N_IN] = lin[MG_LIST_N];
+      f[MG_AF_N_OUT] = lout[MG_LIST_N];
+      f[MG_AF_PROTOCOL] = pi;
+      for (int i = 0; i < lin[MG_LIST_N]; i++) { f[MG_AF_IN_ITEM + i] = lin[MG_LIST_ITEM(i)]; f[MG_AF_IN_AMOUNT + i] = lin[MG_LIST_VAL(i)] & 0xFFFF; }
+      for (int i = 0; i < lout[MG_LIST_N]; i++) { f[MG_AF_OUT_ITEM + i] = lout[MG_LIST_ITEM(i)]; f[MG_AF_OUT_AMOUNT + i] = lout[MG_LIST_VAL(i)] & 0xFFFF; }
+      f[MG_AF_VALID] = 1;
+    }
+    int32_t* d_fast;
+    TRY(dev_alloc(e, &d_fast, fast.size(), false));
+    CUDA_TRY(cudaMemcpy(d_fast, fast.data(), fast.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    b.asm_fast = d_fast;
+  }
   std::vector<uint8_t> pat = make_pattern(cfg[MGC_OBS_H], cfg[MGC_OBS_W]);
   pat.resize(((pat.size() + 255) / 256 + 1) * 256, 0xFF);  // padded: lanes read whole runs of cells
   TRY(dev_alloc(e, &d_pat, pat.size()));

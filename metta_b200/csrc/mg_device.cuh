@@ -878,8 +878,7 @@ MG_DEVICE MG_NOINLINE void action_end(EnvCtx& e, int actor, int kind, bool succe
 // ---------------------------------------------------------------- assembler use by the whole warp
 // Inventory::update (inventory.cpp:37-85) for an agent, all 32 lanes with the same arguments: the limit's
 // member sum and its modifier bonus are one warp sum each (a lane per resource) instead of two loops.
-MG_DEVICE inline int inv_update_warp(EnvCtx& e, int actor, int item, int attempted_delta, int lane) {
-  InvView v = agent_inv(e, actor);
+MG_DEVICE inline int inv_update_warp(EnvCtx& e, InvView& v, int item, int attempted_delta, int lane) {
   const int initial = v.amt[item];
   int max = 65535;
   const int limit = v.invcfg[MG_INVCFG_ITEM_LIMIT + item];
@@ -923,13 +922,15 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
   const long long tk0 = clock64();
 #endif
   AsmRec* a = &e.asms[asm_idx];
-  const int32_t* t = asm_type_cfg(e.cfg, a->cell);
-  const uint32_t max_uses = (uint32_t)t[MG_ASM_MAX_USES];
+  // everything the type contributes, in one line: lane i holds word i of the cell code's record
+  const int32_t fw = e.batch->asm_fast[(int)a->cell * MG_AF_WORDS + lane];
+#define MG_AF(i) __shfl_sync(MG_FULL_MASK, fw, (i))
+  const uint32_t max_uses = (uint32_t)MG_AF(MG_AF_MAX_USES);
   if (max_uses > 0 && a->uses_count >= max_uses) return false;
   const uint32_t remaining = a->cooldown_end <= e.current_step ? 0u : a->cooldown_end - e.current_step;
-  const bool partial = t[MG_ASM_ALLOW_PARTIAL] != 0;
+  const bool partial = MG_AF(MG_AF_PARTIAL) != 0;
   if (remaining > 0 && !partial) return false;
-  bool simple = remaining == 0 && (a->flags & MG_ASMF_CLIPPED) == 0 && t[MG_ASM_CHEST_DISTANCE] <= 0;
+  bool simple = MG_AF(MG_AF_VALID) != 0 && remaining == 0 && (a->flags & MG_ASMF_CLIPPED) == 0 && MG_AF(MG_AF_CHEST_DISTANCE) <= 0;
   if (simple && !alone) {  // who stands in the ring? One cell per lane.
     bool agent_here = false;
     if (lane < 8) {
@@ -938,35 +939,27 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
     }
     simple = __popc(__ballot_sync(MG_FULL_MASK, agent_here)) == 1;
   }
-  int pi = -1;
-  const int32_t* p = nullptr;
-  if (simple) {
-    pi = asm_protocol_for(e, a, (uint64_t)e.ag[actor].vibe, 1);
-    if (pi < 0) return false;
-    p = proto_cfg(e.cfg, pi);
-  }
   if (!simple) {  // the general case, as before
     int ok = 0;
     __syncwarp();  // every lane has read the assembler's record before lane 0 changes it
     if (lane == 0) ok = assembler_on_use(e, asm_idx, actor) ? 1 : 0;
     return __shfl_sync(MG_FULL_MASK, ok, 0) != 0;
   }
-  // one inventory pays (the actor) and, with a single agent around, the same one receives
+  // One protocol (key 0, min_agents <= 1: what get_current_protocol :378-408 finds for a lone actor of any
+  // vibe); one inventory pays (the actor) and, with a single agent around, the same one receives
   // (get_output_inventories :198-223: the actor unless vibing participants claim the slots, and the only
   // candidate is the actor)
-  const int32_t* lin = p + MG_PROTO_INPUTS;
-  const int32_t* lout = p + MG_PROTO_OUTPUTS;
-  const int n_in = lin[MG_LIST_N], n_out = lout[MG_LIST_N];
+  const int n_in = MG_AF(MG_AF_N_IN), n_out = MG_AF(MG_AF_N_OUT);
   const AgentRec* ac = &e.ag[actor];
-  int my_item = 0, my_amount = 0;  // lanes [0, n_in): inputs; lanes [16, 16 + n_out): outputs
-  if (lane < n_in) { my_item = lin[MG_LIST_ITEM(lane)]; my_amount = (int)(uint16_t)lin[MG_LIST_VAL(lane)]; }
-  if (lane >= 16 && lane - 16 < n_out) { my_item = lout[MG_LIST_ITEM(lane - 16)]; my_amount = (int)(uint16_t)lout[MG_LIST_VAL(lane - 16)]; }
+  // lanes [0, n_in): inputs; lanes [16, 16 + n_out): outputs
+  const int my_item = __shfl_sync(MG_FULL_MASK, fw, lane < 16 ? MG_AF_IN_ITEM + (lane & 3) : MG_AF_OUT_ITEM + (lane & 3));
+  const int my_amount = __shfl_sync(MG_FULL_MASK, fw, lane < 16 ? MG_AF_IN_AMOUNT + (lane & 3) : MG_AF_OUT_AMOUNT + (lane & 3));
   const bool short_of = lane < n_in && (int)ac->amt[my_item] < my_amount;  // can_afford_protocol :124-137
   if (__ballot_sync(MG_FULL_MASK, short_of) != 0u) return false;
   const bool gives = lane >= 16 && lane - 16 < n_out && my_amount > 0;
   const uint32_t giving = __ballot_sync(MG_FULL_MASK, gives);
+  InvView v = agent_inv(e, actor);
   if (giving != 0u) {  // can_receive_output :143-171: room for at least one unit of some output
-    InvView v = agent_inv(e, actor);
     const bool room = gives && inv_free_space(v, my_item) >= 1;
     if (__ballot_sync(MG_FULL_MASK, room) == 0u) return false;
   }
@@ -975,23 +968,36 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
 #endif
   for (int i = 0; i < n_in; i++) {  // consume_resources_for_protocol :228-234
     const int item = __shfl_sync(MG_FULL_MASK, my_item, i), amount = __shfl_sync(MG_FULL_MASK, my_amount, i);
-    inv_update_warp(e, actor, item, -amount, lane);
+    inv_update_warp(e, v, item, -amount, lane);
   }
   for (int i = 0; i < n_out; i++) {  // give_output_for_protocol :174-184
     const int item = __shfl_sync(MG_FULL_MASK, my_item, 16 + i), amount = __shfl_sync(MG_FULL_MASK, my_amount, 16 + i);
-    const int distributed = inv_update_warp(e, actor, item, amount, lane);
+    const int distributed = inv_update_warp(e, v, item, amount, lane);
     if (distributed > 0 && lane == 0) MG_RED_ADD(&e.gstats[MG_GS_ASM_CREATED + item], (float)distributed);
   }
 #ifdef MG_TIMING
   const long long tk2 = clock64();
 #endif
+  const uint32_t cooldown = (uint32_t)MG_AF(MG_AF_COOLDOWN);
+#undef MG_AF
   if (lane == 0) {
-    a->cooldown_duration = (uint32_t)(uint16_t)p[MG_PROTO_COOLDOWN];
-    a->cooldown_end = e.current_step + a->cooldown_duration;
+    a->cooldown_duration = cooldown;
+    a->cooldown_end = e.current_step + cooldown;
     a->uses_count++;
+    if (e.asm_records_on_use) {
+      // What observers see of this assembler only changes in two places (it is neither clipped nor does its
+      // protocol depend on neighbours here): the cooldown end in the record's header and, where uses are
+      // limited, the remaining_uses token, which is the record's first (write_asm_tokens: [clipped][remaining_uses]...)
+      uint8_t* rec = token_record(*e.batch, e.env, MG_GK_ASM, (uint32_t)asm_idx);
+      *reinterpret_cast<uint32_t*>(rec + 4) = a->cooldown_end;
+      if (max_uses > 0u) {
+        uint32_t left = a->uses_count < max_uses ? max_uses - a->uses_count : 0u;
+        left = left > 255u ? 255u : left;
+        rec[MG_REC_TOKENS + 1] = (uint8_t)left;
+      }
+    }
   }
   __syncwarp();
-  if (e.asm_records_on_use) write_asm_tokens_warp(*e.batch, a, e.current_step, token_record(*e.batch, e.env, MG_GK_ASM, (uint32_t)asm_idx), lane);
 #ifdef MG_TIMING
   if (lane == 0 && e.batch->dbg != nullptr) {  // set-up and checks | (unused) | consume and give | record
     uint32_t* d = e.batch->dbg + (size_t)e.env * 16 + 12;

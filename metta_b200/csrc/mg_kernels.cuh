@@ -670,7 +670,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
 #endif
 #endif
   for (bool fresh = false;;) {
-#ifndef MG_HAS_BULK_COPY
+#ifndef MG_HAS_BULK_LOAD
     uint4 ag_v[NV], hot_v[NV];
 #endif
     int32_t act_v[NA];
@@ -679,7 +679,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     const uint4* hot_src = reinterpret_cast<const uint4*>(b.hot_stats + abase * MG_HOT_STATS);
     uint16_t* tc = b.tok_counts + abase * 2;
     float* gs = b.game_stats + (size_t)env * b.GS;
-#ifdef MG_HAS_BULK_COPY
+#ifdef MG_HAS_BULK_LOAD
     // agent records and hot stat slots: two bulk copies (TMA) straight into the warp's shared block, issued by
     // one lane and waited for on the block's mbarrier further down; no registers, no per-lane address math
     if (fresh) {
@@ -716,7 +716,9 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     // round trip of its own in the next phase
     const uint32_t rng_first = er.rng_idx;
     const uint32_t rng_n = rng_first < MT_N ? (MT_N - rng_first < 32u ? MT_N - rng_first : 32u) : 0u;
-    const uint32_t rng_w = (uint32_t)lane < rng_n ? b.rng[(size_t)env * MT_N + rng_first + lane] : 0u;
+    // straight into the shared block, in the background: the decide phase waits for it where it draws (this load
+    // depends on EnvRec, so it is a memory round trip of its own; nothing in this phase needs its result)
+    if ((uint32_t)lane < rng_n) MG_ASYNC_COPY4(&sm.rngbuf[lane], &b.rng[(size_t)env * MT_N + rng_first + lane]);
 
     // fold the pending token counts (written | attempted << 16; attempted 0xFFFF = nothing pending)
     {
@@ -760,7 +762,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
     }
     MG_SM_TICK(sm, 0);
     if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
-#ifdef MG_HAS_BULK_COPY
+#ifdef MG_HAS_BULK_LOAD
       mg_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_bar), sm.stage_phase);  // the old episode's records: let the copy land, then drop it
       __syncwarp();
       if (lane == 0) sm.stage_phase ^= 1u;
@@ -786,7 +788,7 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
       fresh = true;
       continue;  // load the new episode's state
     }
-#ifdef MG_HAS_BULK_COPY
+#ifdef MG_HAS_BULK_LOAD
     if (!fresh) {
       mg_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_bar), sm.stage_phase);
       __syncwarp();
@@ -811,7 +813,6 @@ MG_DEVICE MG_NOINLINE void step_phase_load(const MgBatch& b, StepSmem<MAXA>& sm,
         sm.success[ai] = 0;
       }
     }
-    sm.rngbuf[lane] = rng_w;
     if (lane == 0) { sm.rng_base = rng_first; sm.rng_n = rng_n; }
     break;
   }
@@ -879,6 +880,8 @@ MG_DEVICE MG_NOINLINE void step_phase_decide(const MgBatch& b, StepSmem<MAXA>& s
   MG_SM_TICK(sm, 3);
   // random processing order (mettagrid_c.cpp:591-593); the words it needs are fetched in one go
   MtStream rs = mt_stream(mt, sm.er.rng_idx);
+  MG_ASYNC_COPY_WAIT();  // the generator words the load phase asked for
+  __syncwarp();
   if (sm.rng_n != 0u && sm.rng_base == rs.idx) {  // staged by the load phase
     rs.buf = sm.rngbuf; rs.buf_base = sm.rng_base; rs.buf_n = sm.rng_n;
   } else {

@@ -49,10 +49,13 @@
 #define MG_GRID_CONSTANT __grid_constant__ /* the parameter's address may be taken without a per-thread copy */
 #endif
 
-#ifndef MG_SIMT_EMU
+#if !defined(MG_SIMT_EMU) && !defined(MG_NO_BULK_COPY)
 // ---- 1-D bulk copies (TMA, cp.async.bulk) between this GPU's HBM and shared memory, completion on an mbarrier.
 // One thread issues a copy of any multiple of 16 bytes; the data never passes through registers.
 #define MG_HAS_BULK_COPY 1
+#ifndef MG_NO_BULK_LOAD
+#define MG_HAS_BULK_LOAD 1 /* the staging of records at the start of a step; the write-back uses bulk copies either way */
+#endif
 __device__ __forceinline__ uint32_t mg_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mg_mbar_init(uint64_t* bar, uint32_t arrivals) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mg_smem_addr(bar)), "r"(arrivals) : "memory");
@@ -87,6 +90,13 @@ __device__ __forceinline__ void mg_bulk_store(void* gmem_dst, const void* smem_s
 __device__ __forceinline__ void mg_bulk_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void mg_bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }  // shared memory may be reused
 __device__ __forceinline__ void mg_bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }        // the writes have been performed
+#endif
+
+#ifndef MG_SIMT_EMU
+// A 4-byte global -> shared copy that completes in the background (LDGSTS); MG_ASYNC_COPY_WAIT before the first read.
+#define MG_ASYNC_COPY4(smem_dst, gmem_src) \
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory")
+#define MG_ASYNC_COPY_WAIT() asm volatile("cp.async.wait_all;" ::: "memory")
 #endif
 
 #define MG_FULL_MASK 0xFFFFFFFFu

@@ -32,6 +32,22 @@
 #define MG_GTOK_STRIDE 64
 #define MG_REC_TOKENS 8 /* byte offset of the tokens inside a token record */
 
+/* asm_fast record (32 words): valid, max_uses, allow_partial, chest_distance, cooldown, n_in, n_out, protocol, then
+ * input items [8..12), input amounts [12..16), output items [16..20), output amounts [20..24) */
+#define MG_AF_VALID 0
+#define MG_AF_MAX_USES 1
+#define MG_AF_PARTIAL 2
+#define MG_AF_CHEST_DISTANCE 3
+#define MG_AF_COOLDOWN 4
+#define MG_AF_N_IN 5
+#define MG_AF_N_OUT 6
+#define MG_AF_PROTOCOL 7
+#define MG_AF_IN_ITEM 8
+#define MG_AF_IN_AMOUNT 12
+#define MG_AF_OUT_ITEM 16
+#define MG_AF_OUT_AMOUNT 20
+#define MG_AF_WORDS 32
+
 #define MG_ORDER_EMPTY 0xFFFFFFFFFFFFFFFFull /* inventory order list: 4-bit item ids, 0xF ends the list */
 
 struct alignas(16) AgentRec {
@@ -119,6 +135,7 @@ struct MgBatch {
   int32_t reward_stat_prefetch;  // some reward term reads a stat slot that lives in HBM (not a hot slot, not <res>.amount)
   int32_t reward_game_stats;   // some reward term reads a game stat
   int32_t inv_masks_off;       // appended: per INVCFG record [MG_MAX_LIMITS] member masks, [MG_MAX_LIMITS] modifier masks
+  const int32_t* asm_fast;     // [MG_MAX_CELLTYPES][32] per map cell code: what a use of a one-protocol assembler needs, in one 128-byte line (mg_create)
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
   // static token templates, built once per config on the host (mg_abi.cu build_templates):

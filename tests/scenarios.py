@@ -331,7 +331,7 @@ def collective_rewards() -> tuple[MettaGridConfig, np.ndarray]:
         "actions": {"noop": {}, "move": {}, "change_vibe": {"enabled": False}},
         "objects": {
             "wall": {"pydantic_type": "wall", "name": "wall"},
-            "altar": {"pydantic_type": "assembler", "name": "altar", "protocols": [{"output_resources": {"heart": 1}, "cooldown": 2}]},
+            "altar": {"pydantic_type": "assembler", "name": "altar", "max_uses": 7, "protocols": [{"output_resources": {"heart": 1}, "cooldown": 2}]},
         },
     }
     legend = {"#": "wall", ".": "empty", "A": "altar", "a": "agent.team_0", "b": "agent.team_1"}

@@ -31,6 +31,8 @@
 #define MG_PREFETCH_L2(p) ((void)(p))
 #define MG_RED_ADD(p, v) ((void)(*(p) += (v)))
 #define MG_LDCG(p) (*(p))
+#define MG_ASYNC_COPY4(smem_dst, gmem_src) (*(smem_dst) = *(gmem_src))
+#define MG_ASYNC_COPY_WAIT() ((void)0)
 #define MG_STAT_BUMP(p, v) ((void)(*(p) += (v)))
 #define MG_PREFETCH_TO_L2(p) ((void)(p))
 #define MG_LD_L2(p) (*(p))

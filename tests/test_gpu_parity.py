@@ -449,3 +449,32 @@ def test_token_stats_beyond_2_pow_24(lib):
     ls.compare_state()
     assert ls.batch.read_game_stats()[:, L.MG_GS_TOKENS_FREE_SPACE].min() > 2.0**24
     ls.close()
+
+
+def test_library_owned_buffers_are_rebound_by_every_all_null_call(lib):
+    """mg_set_buffers(all NULL) -> caller buffers -> all NULL again: the third call must bind the library's own
+    buffers again (it used to leave the handle pointing at the caller's, possibly freed, memory)."""
+    import torch
+
+    cfg, grid = SCENARIOS["tiny_truncating"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    n, A, T = 4, cfg.game.num_agents, cfg.game.obs.num_tokens
+    b = Batch(low, build_pool(low, codes), n)
+    b.use_internal_buffers()
+    b.reset(np.arange(n, dtype=np.uint32) + 1, np.zeros(n, np.int32))
+    own_first = b.read_obs().copy()
+    buf = HostBuffers(n * A, T, cuda=True)
+    b.set_buffers(*buf.ptrs)
+    b.compute_observations()
+    torch.cuda.synchronize()
+    assert np.array_equal(buf.fetch()[0], own_first)
+    ptr = buf.t_obs.data_ptr()
+    b.use_internal_buffers()
+    h = lambda shape, dt: np.zeros(shape, dt)  # noqa: E731
+    obs, rew, term, trunc = h((n * A, T, 3), np.uint8), h(n * A, np.float32), h(n * A, np.uint8), h(n * A, np.uint8)
+    buf.t_obs.fill_(7)  # the caller's buffer must not be touched any more
+    b.step_host(np.zeros(n * A, np.int32), obs, rew, term, trunc)
+    assert int(buf.t_obs.min()) == 7 and buf.t_obs.data_ptr() == ptr
+    assert np.array_equal(obs, b.read_obs())
+    b.close()
