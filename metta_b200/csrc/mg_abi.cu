@@ -278,6 +278,19 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   TRY(dev_alloc(e, &d_pat, pat.size()));
   CUDA_TRY(cudaMemcpy(d_pat, pat.data(), pat.size(), cudaMemcpyHostToDevice));
   b.pattern = d_pat;
+  {
+    std::vector<int32_t> off(pat.size(), -1);
+    for (size_t i = 0; i < pat.size(); i++)
+      if (pat[i] != 0xFF) off[i] = (int32_t)(pat[i] >> 4) * b.W + (int32_t)(pat[i] & 0xF);
+    int32_t* d_off;
+    TRY(dev_alloc(e, &d_off, off.size(), false));
+    CUDA_TRY(cudaMemcpy(d_off, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    b.pattern_off = d_off;
+    const int cpl = (b.obs_cells + 31) / 32;
+    const int cpl_t = cpl <= 1 ? 1 : cpl <= 2 ? 2 : cpl <= 4 ? 4 : 8;
+    b.obs_slot = (b.T * 3 + 16 + 15) & ~15;
+    b.obs_warp_bytes = b.obs_slot + MG_OBS_DESC_BYTES(cpl_t);
+  }
   TRY(dev_alloc(e, &b.env, N));
   TRY(dev_alloc(e, &b.grid, N * (size_t)b.grid_stride));
   TRY(dev_alloc(e, &b.agents, N * A));

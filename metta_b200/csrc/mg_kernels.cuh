@@ -1264,7 +1264,7 @@ template <int CPL>
 MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* warp_smem) {
   const size_t g = (size_t)env * b.A + ai;  // global agent index
   const int row_bytes = b.T * 3;
-  const int slot = (row_bytes + 16 + 15) & ~15;
+  const int slot = b.obs_slot;
   uint8_t* out = b.obs + (size_t)g * row_bytes;
 #ifdef MG_OBS_STORE16
   const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
@@ -1312,9 +1312,12 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
   if ((row_bytes & 7) == 0 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0) {
     const uint2* s2 = reinterpret_cast<const uint2*>(row);
     uint2* d2 = reinterpret_cast<uint2*>(out);
-    const int n8 = row_bytes >> 3;
-#pragma unroll 3
-    for (int i = lane; i < n8; i += 32) d2[i] = s2[i];
+    const int n8 = row_bytes >> 3;  // 75 for 200 tokens: three rounds, spelled out (a compiler-unrolled loop cost 79 instructions per row)
+    if (lane < n8) d2[lane] = s2[lane];
+    if (lane + 32 < n8) d2[lane + 32] = s2[lane + 32];
+    if (lane + 64 < n8) d2[lane + 64] = s2[lane + 64];
+#pragma unroll 1
+    for (int i = lane + 96; i < n8; i += 32) d2[i] = s2[i];
   } else {
     for (int i = lane; i < row_bytes; i += 32) out[i] = row[i];
   }
@@ -1361,8 +1364,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
   if (ai >= b.A) return;
   if (mask != nullptr && !mask[env]) return;
-  const int slot = (b.T * 3 + 16 + 15) & ~15;
-  obs_row_warp<CPL>(b, env, ai, lane, dyn + (size_t)warp * (slot + MG_OBS_DESC_BYTES(CPL)));
+  obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 }
 
 #ifndef MG_SIMT_EMU

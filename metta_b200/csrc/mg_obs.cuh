@@ -110,12 +110,19 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
     // the whole window lies inside the map (always, where the map's border is at least as wide as the window's
     // radius, as in the arena): one add per cell, no range tests
     const uint16_t* corner = grid + (my_r - hr) * b.W + (my_c - wr);
+    int32_t off[CPL];  // the lane's cells as offsets from the corner, precomputed per config (-1: no cell)
+    if (CPL == 4) {
+      const int4 o4 = *reinterpret_cast<const int4*>(b.pattern_off + lane * 4);
+      off[0] = o4.x; off[1 % CPL] = o4.y; off[2 % CPL] = o4.z; off[3 % CPL] = o4.w;
+    } else {
 #pragma unroll
-    for (int j = 0; j < CPL; j++) {
-      const uint32_t loc = (uint32_t)(locs >> (8 * j)) & 0xFFu;
-      const uint32_t g = loc != 0xFFu ? (uint32_t)corner[(loc >> 4) * (uint32_t)b.W + (loc & 0xFu)] : 0u;
-      cell[j] = g != 0u ? (g | (loc << 16)) : 0u;
+      for (int j = 0; j < CPL; j++) off[j] = b.pattern_off[lane * CPL + j];
     }
+    uint32_t g[CPL];
+#pragma unroll
+    for (int j = 0; j < CPL; j++) g[j] = off[j] >= 0 ? (uint32_t)corner[off[j]] : 0u;
+#pragma unroll
+    for (int j = 0; j < CPL; j++) cell[j] = g[j] != 0u ? (g[j] | (((uint32_t)(locs >> (8 * j)) & 0xFFu) << 16)) : 0u;
   } else {
 #pragma unroll
     for (int j = 0; j < CPL; j++) {

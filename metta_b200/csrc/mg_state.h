@@ -138,6 +138,8 @@ struct MgBatch {
   const int32_t* asm_fast;     // [MG_MAX_CELLTYPES][32] per map cell code: what a use of a one-protocol assembler needs, in one 128-byte line (mg_create)
   const int32_t* cfg;          // lowered config
   const uint8_t* pattern;      // Manhattan-order packed window locations (packed_coordinate.hpp:74-143)
+  const int32_t* pattern_off;  // the same cells as offsets (row * W + col) from the window's top-left cell, -1 behind the last; padded to 8 per lane
+  int32_t obs_slot, obs_warp_bytes;  // shared memory per observation warp: row image bytes (16-byte multiple), and with the descriptors behind it
   // static token templates, built once per config on the host (mg_abi.cu build_templates):
   // a token is feature | value << 8; an index entry is offset << 8 | count
   const uint16_t* tmpl_tok;

@@ -49,6 +49,7 @@ static inline float MG_INT_AS_FLOAT(int32_t x) { float f; memcpy(&f, &x, 4); ret
 
 struct uint4 { uint32_t x, y, z, w; } __attribute__((aligned(16)));
 struct uint2 { uint32_t x, y; } __attribute__((aligned(8)));
+struct int4 { int32_t x, y, z, w; } __attribute__((aligned(16)));
 struct emu_dim3 { unsigned x, y, z; };
 struct dim3 {
   unsigned x, y, z;
