@@ -912,11 +912,55 @@ MG_DEVICE inline int inv_update_warp(EnvCtx& e, InvView& v, int item, int attemp
   return delta;
 }
 
+// HasInventory::shared_update (has_inventory.cpp:7-74) for a negative delta over 2..8 agent inventories, all 32
+// lanes with the same arguments: the reference's rounds (whoever holds no more than an equal share gives all
+// of it, the share of the others grows, until nobody drops out; the rest is split from the back) walked by
+// every lane alike, each single update by inv_update_warp.
+MG_DEVICE inline int shared_consume_warp(EnvCtx& e, uint64_t agents, int n, int item, int delta, int lane) {
+  int delta_remaining = delta;
+  uint32_t active = (1u << n) - 1u;
+  int num_remaining = n;
+  int per = delta_remaining / num_remaining;
+  MG_ROLLED
+  for (;;) {
+    uint32_t next = 0u;
+    int ncur = 0, nnext = 0;
+    MG_ROLLED
+    for (int i = 0; i < n; i++) {
+      if (!((active >> i) & 1u)) continue;
+      ncur++;
+      InvView v = agent_inv(e, (int)((agents >> (8 * i)) & 0xFFull));
+      if ((int)v.amt[item] <= -per) {
+        delta_remaining -= inv_update_warp(e, v, item, per, lane);
+        num_remaining--;
+        if (num_remaining > 0) per = delta_remaining / num_remaining;
+      } else {
+        next |= 1u << i;
+        nnext++;
+      }
+    }
+    active = next;
+    if (ncur == nnext) break;
+  }
+  if (num_remaining == 0) return delta - delta_remaining;
+  int cnt = __popc(active);
+  MG_ROLLED
+  for (int i = n - 1; i >= 0; i--) {  // reverse order: earlier inventories get the remainder
+    if (!((active >> i) & 1u)) continue;
+    const int d = delta_remaining / cnt;
+    InvView v = agent_inv(e, (int)((agents >> (8 * i)) & 0xFFull));
+    delta_remaining -= inv_update_warp(e, v, item, d, lane);
+    cnt--;
+  }
+  return delta - delta_remaining;
+}
+
 // Assembler::onUse (assembler.hpp:455-526) called by all 32 lanes with the same arguments. The common case
-// -- the actor is the only agent around the assembler, which is neither clipped, nor cooling down, nor
-// searching chests -- runs here with a lane per ring cell / per protocol item; everything else is handed
-// to assembler_on_use on lane 0, unchanged. `alone`: the caller knows that no other agent stands next to
-// the assembler (step_phase_decide, rule 3).
+// -- a one-protocol assembler that is neither clipped, nor cooling down, nor searching chests -- runs here
+// with a lane per ring cell / per protocol item, whether the actor is alone at the assembler or other agents
+// stand around it and pay their share (shared_consume_warp); everything else is handed to assembler_on_use
+// on lane 0, unchanged. `alone`: the caller knows that no other agent stands next to the assembler
+// (step_phase_decide, rule 3).
 MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor, bool alone, int lane) {
 #ifdef MG_TIMING
   const long long tk0 = clock64();
@@ -931,13 +975,29 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
   const bool partial = MG_AF(MG_AF_PARTIAL) != 0;
   if (remaining > 0 && !partial) return false;
   bool simple = MG_AF(MG_AF_VALID) != 0 && remaining == 0 && (a->flags & MG_ASMF_CLIPPED) == 0 && MG_AF(MG_AF_CHEST_DISTANCE) <= 0;
-  if (simple && !alone) {  // who stands in the ring? One cell per lane.
-    bool agent_here = false;
+  uint64_t payers = (uint64_t)actor;  // the agents around the assembler, from the actor on in ring order (8 bits each)
+  int n_payers = 1;
+  if (simple && !alone) {  // who stands in the ring? One cell per lane (get_surrounding_agents :48-92).
+    int here = 0xFF;
     if (lane < 8) {
       const int rr = (int)a->r + (int)((0xA940u >> (2 * lane)) & 3u) - 1, cc = (int)a->c + (int)((0x9224u >> (2 * lane)) & 3u) - 1;
-      if (rr >= 0 && cc >= 0 && rr < e.H && cc < e.W) agent_here = MG_GRID_KIND(grid_at(e, rr, cc)) == MG_GK_AGENT;
+      if (rr >= 0 && cc >= 0 && rr < e.H && cc < e.W) {
+        const uint16_t g = grid_at(e, rr, cc);
+        if (MG_GRID_KIND(g) == MG_GK_AGENT) here = (int)MG_GRID_INDEX(g);
+      }
     }
-    simple = __popc(__ballot_sync(MG_FULL_MASK, agent_here)) == 1;
+    const uint32_t present = __ballot_sync(MG_FULL_MASK, here != 0xFF);
+    if (__popc(present) > 1) {
+      const uint32_t at_actor = __ballot_sync(MG_FULL_MASK, here == actor);
+      const int start = at_actor != 0u ? __ffs((int)at_actor) - 1 : 0;
+      payers = 0ull;
+      n_payers = 0;
+      MG_ROLLED
+      for (int j = 0; j < 8; j++) {
+        const int idx = __shfl_sync(MG_FULL_MASK, here, (start + j) & 7);
+        if (idx != 0xFF) payers |= (uint64_t)idx << (8 * n_payers++);
+      }
+    }
   }
   if (!simple) {  // the general case, as before
     int ok = 0;
@@ -945,17 +1005,28 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
     if (lane == 0) ok = assembler_on_use(e, asm_idx, actor) ? 1 : 0;
     return __shfl_sync(MG_FULL_MASK, ok, 0) != 0;
   }
-  // One protocol (key 0, min_agents <= 1: what get_current_protocol :378-408 finds for a lone actor of any
-  // vibe); one inventory pays (the actor) and, with a single agent around, the same one receives
-  // (get_output_inventories :198-223: the actor unless vibing participants claim the slots, and the only
-  // candidate is the actor)
+  // One protocol (key 0, min_agents <= 1: what get_current_protocol :378-408 finds whatever the vibes around
+  // are, directly or through its key-0 fallback); every agent around pays, from the actor on in ring order;
+  // the protocol names no vibes, so the actor alone receives (get_output_inventories :198-223)
   const int n_in = MG_AF(MG_AF_N_IN), n_out = MG_AF(MG_AF_N_OUT);
   const AgentRec* ac = &e.ag[actor];
   // lanes [0, n_in): inputs; lanes [16, 16 + n_out): outputs
   const int my_item = __shfl_sync(MG_FULL_MASK, fw, lane < 16 ? MG_AF_IN_ITEM + (lane & 3) : MG_AF_OUT_ITEM + (lane & 3));
   const int my_amount = __shfl_sync(MG_FULL_MASK, fw, lane < 16 ? MG_AF_IN_AMOUNT + (lane & 3) : MG_AF_OUT_AMOUNT + (lane & 3));
-  const bool short_of = lane < n_in && (int)ac->amt[my_item] < my_amount;  // can_afford_protocol :124-137
-  if (__ballot_sync(MG_FULL_MASK, short_of) != 0u) return false;
+  if (n_payers == 1) {
+    const bool short_of = lane < n_in && (int)ac->amt[my_item] < my_amount;  // can_afford_protocol :124-137
+    if (__ballot_sync(MG_FULL_MASK, short_of) != 0u) return false;
+  } else {
+    // everybody around pays: the u16 sum over the payers per input, input i on lanes [8 i, 8 i + 8), payer k on lane 8 i + k
+    const int i = lane >> 3, k = lane & 7;
+    const int item = __shfl_sync(MG_FULL_MASK, my_item, i), amount = __shfl_sync(MG_FULL_MASK, my_amount, i);
+    uint32_t total = (i < n_in && k < n_payers) ? (uint32_t)e.ag[(int)((payers >> (8 * k)) & 0xFFull)].amt[item] : 0u;
+    total += __shfl_xor_sync(MG_FULL_MASK, total, 1);
+    total += __shfl_xor_sync(MG_FULL_MASK, total, 2);
+    total += __shfl_xor_sync(MG_FULL_MASK, total, 4);
+    const bool short_of = i < n_in && (total & 0xFFFFu) < (uint32_t)amount;
+    if (__ballot_sync(MG_FULL_MASK, short_of) != 0u) return false;
+  }
   const bool gives = lane >= 16 && lane - 16 < n_out && my_amount > 0;
   const uint32_t giving = __ballot_sync(MG_FULL_MASK, gives);
   InvView v = agent_inv(e, actor);
@@ -968,7 +1039,8 @@ MG_DEVICE MG_NOINLINE bool assembler_use_warp(EnvCtx& e, int asm_idx, int actor,
 #endif
   for (int i = 0; i < n_in; i++) {  // consume_resources_for_protocol :228-234
     const int item = __shfl_sync(MG_FULL_MASK, my_item, i), amount = __shfl_sync(MG_FULL_MASK, my_amount, i);
-    inv_update_warp(e, v, item, -amount, lane);
+    if (n_payers == 1) inv_update_warp(e, v, item, -amount, lane);
+    else shared_consume_warp(e, payers, n_payers, item, -amount, lane);
   }
   for (int i = 0; i < n_out; i++) {  // give_output_for_protocol :174-184
     const int item = __shfl_sync(MG_FULL_MASK, my_item, 16 + i), amount = __shfl_sync(MG_FULL_MASK, my_amount, 16 + i);

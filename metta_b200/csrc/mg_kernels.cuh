@@ -1170,7 +1170,13 @@ MG_DEVICE MG_NOINLINE void step_phase_finish(const MgBatch& b, StepSmem<MAXA>& s
 template <int MAXA>
 MG_DEVICE inline void step_env_warp(const MgBatch& b, StepSmem<MAXA>& sm, int env, int lane) {
 #ifdef MG_TIMING
-  if (lane == 0) { sm.tick_last = clock64(); for (int i = 0; i < 16; i++) sm.ticks[i] = 0; }
+  if (lane == 0) {
+    sm.tick_last = clock64();
+    for (int i = 0; i < 16; i++) sm.ticks[i] = 0;
+    unsigned long long wall;  // slot 10: when this env started (ns, low word), to tell waves from chains
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wall));
+    sm.ticks[10] = (uint32_t)wall;
+  }
   if (lane >= 12 && lane < 16 && b.dbg != nullptr) b.dbg[(size_t)env * 16 + lane] = 0u;
   __syncwarp();
 #endif

@@ -1,10 +1,17 @@
 #!/bin/bash
 mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
-python tools/obs_ab.py 2>&1 | tail -1 | tee gpurun_out/obs_ab.txt
-ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:mg_obs_kernel -c 1 -o gpurun_out/r02_obs -f python tools/profile_steady.py > gpurun_out/ncu_obs.log 2>&1
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "queue" 2>&1 | tail -3 | tee gpurun_out/gpu_tests.txt
 B="python bench.py --no-cpu-baseline --no-other-configs --steps 100"
 $B > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err
-MG_STEP_MODE=queue MG_QUEUE_EARLY=8 MG_QUEUE_LATE=0 $B > gpurun_out/bench_queue_e8_l0.json 2> gpurun_out/bench_queue_e8_l0.err
+run() { name=$1; shift; env "$@" MG_STEP_MODE=queue $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
+run q24_e8 MG_QUEUE_EARLY=8 MG_QUEUE_LATE=0
+run q24_e4l4 MG_QUEUE_EARLY=4 MG_QUEUE_LATE=4
+for v in q28 q28r4 q28r1; do
+  run ${v}_e8 MG_LIB_PATH=build_variants/lib_$v.so MG_QUEUE_EARLY=8 MG_QUEUE_LATE=0
+done
+run q28_e6 MG_LIB_PATH=build_variants/lib_q28.so MG_QUEUE_EARLY=6 MG_QUEUE_LATE=0
+run q28_e4l4 MG_LIB_PATH=build_variants/lib_q28.so MG_QUEUE_EARLY=4 MG_QUEUE_LATE=4
+run q28_e0l8 MG_LIB_PATH=build_variants/lib_q28.so MG_QUEUE_EARLY=0 MG_QUEUE_LATE=8
 python - <<'PY' | tee gpurun_out/summary.txt
 import json,glob
 for f in sorted(glob.glob('gpurun_out/bench_*.json')):

@@ -32,6 +32,7 @@ for s in range(STEPS):
 uses = b.read_assemblers()["uses_count"].astype(np.int64).sum(1) - uses0
 sp=b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64)
 names=['load: loads+fold','load: reset/stage','load: rest(prefetch,ctx)','decide: intents','decide: shuffle draws','decide: conflicts+apply','act parallel','act ordered','post','finish: rewards+records','', 'finish: write-back']
+start=sp[:,10].copy(); sp[:,10]=0
 tot=sp.sum(1)
 print('N',N,'flush',FLUSH); print('per-env total cycles: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f'%(tot.mean(),np.percentile(tot,50),np.percentile(tot,90),np.percentile(tot,99),tot.max()))
 print('envs with ordered work: %.1f%%' % (100.0*(sp[:,7] > 2000).mean()))
@@ -60,3 +61,12 @@ m = sp[:,0] > 100000
 if m.any():
     print('envs that started a new episode in this step: %d; load %.0f = accumulate %.0f | reset up to the assembler records %.0f | assembler records %.0f | count pass %.0f' % (
         m.sum(), sp[m,0].mean(), sp[m,12].mean(), sp[m,13].mean(), sp[m,14].mean(), sp[m,15].mean()))
+
+rel=(start-start.min())%2**32
+end=rel+tot/1.92
+print('env start after the first one (ns): p50 %.0f p90 %.0f p99 %.0f max %.0f; started later than 10 us: %d envs' % (np.percentile(rel,50),np.percentile(rel,90),np.percentile(rel,99),rel.max(),(rel>10000).sum()))
+print('env end (ns, start + cycles/1.92): p50 %.0f p90 %.0f p99 %.0f max %.0f' % (np.percentile(end,50),np.percentile(end,90),np.percentile(end,99),end.max()))
+order=np.argsort(-end)[:16]
+print('the envs that end last: env start end | load decide act-par act-ord post finish | uses')
+for e in order:
+    print('%5d %7.0f %7.0f | %6.0f %6.0f %6.0f %6.0f %6.0f %6.0f | %d' % (e, rel[e], end[e], sp[e,0:3].sum(), sp[e,3:6].sum(), sp[e,6], sp[e,7], sp[e,8], sp[e,9]+sp[e,11], uses[e]))
