@@ -531,10 +531,52 @@ def run_ours(args):
     # the export must leave the host buffer identical to the device observations
     if not np.array_equal(h_obs, batch.read_obs().reshape(h_obs.shape)):
         raise SystemExit("bench: host observation buffer differs from the device buffer after the changed-rows export")
+    # ---- the same with the rank's envs split over two handles that are kept in flight together
+    # (mg_step_host_begin / _end): one half's observations cross the host link while the other half steps --
+    # how the reference's trainer runs its vectorised env (async_factor 2: num_envs = 2 x batch_size,
+    # metta/rl/training/training_environment.py:45, batch.py:19)
+    halves = []
+    for hix in range(2):
+        n = N // 2
+        sl = slice(hix * n, (hix + 1) * n)
+        r = Rig(torch, low, pool, n, A, T, 5, dev, seeds[sl], maps[sl], 100 + 2 * rank + hix, args.flush)
+        if not args.no_stagger:
+            r.stagger(max_steps, rank * N + hix * n)
+        r.batch.set_host_export(True)
+        bufs = (pin((n * A, T, 3), torch.uint8), pin((n * A,), torch.float32), pin((n * A,), torch.uint8), pin((n * A,), torch.uint8))
+        acts = pin((e2e_steps + 3, n * A), torch.int32)
+        acts[...] = np.random.RandomState(1000 + 2 * rank + hix).randint(0, 5, size=acts.shape)
+        halves.append((r, bufs, acts))
+    for i in range(3):
+        for r, bufs, acts in halves:
+            r.batch.step_host(acts[i], *bufs)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    hb0 = [r.batch.transfer_bytes() for r, _, _ in halves]
+    t0 = time.perf_counter()
+    for r, bufs, acts in halves:
+        r.batch.step_host_begin(acts[3], *bufs)
+    for i in range(1, e2e_steps):
+        for r, bufs, acts in halves:
+            r.batch.step_host_end()  # this half's step i-1 is on the host: a policy would read it here ...
+            r.batch.step_host_begin(acts[3 + i], *bufs)  # ... and answer with the next actions, while the other half is in flight
+    for r, _, _ in halves:
+        r.batch.step_host_end()
+    torch.cuda.synchronize()
+    e2e_halves_s = time.perf_counter() - t0
+    hb1 = [r.batch.transfer_bytes() for r, _, _ in halves]
+    halves_h2d = sum(b1[0] - b0[0] for b0, b1 in zip(hb0, hb1)) / e2e_steps
+    halves_d2h = sum(b1[1] - b0[1] for b0, b1 in zip(hb0, hb1)) / e2e_steps
+    for r, bufs, _ in halves:
+        if not np.array_equal(bufs[0], r.batch.read_obs().reshape(bufs[0].shape)):
+            raise SystemExit("bench: host observation buffer differs from the device buffer after the two-halves run")
+        r.close()
+    del halves
     link = host_link_ceiling(torch, dist, dev, world)
     # ---- the only collective of the env path: episode stats (a few KB) over NCCL
     acc = torch.from_numpy(batch.read_episode_accum()).to(dev)
-    t = torch.tensor([total_ms, free_ms, e2e_s, e2e_full_s], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, free_ms, e2e_s, e2e_full_s, e2e_halves_s], dtype=torch.float64, device=dev)
     per_rank = torch.zeros(world, dtype=torch.float64, device=dev)
     per_rank[rank] = total_ms / args.steps
     ep = torch.tensor([episodes_timed], dtype=torch.float64, device=dev)
@@ -543,7 +585,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(per_rank, op=dist.ReduceOp.SUM)
         dist.all_reduce(ep, op=dist.ReduceOp.SUM)
-    total_ms, free_ms, e2e_s, e2e_full_s = (float(x) for x in t.cpu())
+    total_ms, free_ms, e2e_s, e2e_full_s, e2e_halves_s = (float(x) for x in t.cpu())
     peak, peak_kind = peaks()
     rig.close()
     others = None
@@ -567,6 +609,8 @@ def run_ours(args):
         e2e_value = world * N * A * e2e_steps / e2e_s
         e2e_full_value = world * N * A * e2e_steps / e2e_full_s
         d2h_rate = e2e_d2h * e2e_steps / e2e_s / 1e9  # GB/s this rank moved in changed-rows mode
+        e2e_halves_value = world * 2 * (N // 2) * A * e2e_steps / e2e_halves_s
+        halves_rate = halves_d2h * e2e_steps / e2e_halves_s / 1e9
         full_rate = full_d2h * e2e_steps / e2e_full_s / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -581,15 +625,21 @@ def run_ours(args):
             "clocks": clocks,
             "per_rank_ms": [float(x) for x in per_rank.cpu()],
             "step_ms": {"min": float(np.min(step_ms)), "median": float(np.median(step_ms)), "p90": float(np.percentile(step_ms, 90)), "max": float(np.max(step_ms))},
-            "e2e": {"value": e2e_value, "unit": "agent-steps/s",
-                    "h2d_bytes_per_step": int(e2e_h2d), "d2h_bytes_per_step": int(e2e_d2h),
-                    "mode": "changed_rows: mg_step_host with page-locked caller buffers and mg_set_host_export 1 (what GpuMettaGridVecEnv(host=True) "
-                            "uses): observations as changed row pieces written by a kernel; host buffer checked equal to the device buffer after the run",
-                    "modes": {"changed_rows": {"value": e2e_value, "d2h_bytes_per_step": int(e2e_d2h), "d2h_gbs_per_rank": d2h_rate},
+            "e2e": {"value": e2e_halves_value, "unit": "agent-steps/s",
+                    "h2d_bytes_per_step": int(halves_h2d), "d2h_bytes_per_step": int(halves_d2h),
+                    "mode": "two_halves: the rank's envs as two handles of N/2 envs kept in flight together (mg_step_host_begin / mg_step_host_end, "
+                            "the reference trainer's async_factor 2), page-locked caller buffers, mg_set_host_export 1 (observations as changed row "
+                            "pieces written by a kernel); every step's actions go host->device and its observations, rewards and flags come back "
+                            "inside the timed region; host buffers checked equal to the device buffers after the run. The single-handle numbers "
+                            "of the same call are under modes",
+                    "modes": {"two_halves": {"value": e2e_halves_value, "d2h_bytes_per_step": int(halves_d2h), "d2h_gbs_per_rank": halves_rate},
+                              "changed_rows": {"value": e2e_value, "d2h_bytes_per_step": int(e2e_d2h), "d2h_gbs_per_rank": d2h_rate,
+                                               "note": "one handle, mg_step_host with mg_set_host_export 1 (what GpuMettaGridVecEnv(host=True) uses)"},
                               "full_rows": {"value": e2e_full_value, "d2h_bytes_per_step": int(full_d2h), "d2h_gbs_per_rank": full_rate,
                                             "note": "same call with every observation byte copied (mg_set_host_export 0, the C-ABI default)"}},
                     "host_link": link,
-                    "host_link_frac": {"changed_rows": d2h_rate * world / link["d2h_10MB_gbs_all_ranks"], "full_rows": full_rate * world / link["d2h_60MB_gbs_all_ranks"]}},
+                    "host_link_frac": {"two_halves": halves_rate * world / link["d2h_10MB_gbs_all_ranks"],
+                                       "changed_rows": d2h_rate * world / link["d2h_10MB_gbs_all_ranks"], "full_rows": full_rate * world / link["d2h_60MB_gbs_all_ranks"]}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "whole step: mg_step_kernel + mg_obs_kernel in overlapped slices", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "alg_bytes_per_agent_step": ALG_BYTES_STEP,

@@ -60,6 +60,16 @@ int mg_step(void* handle, void* cuda_stream);
 int mg_step_host(void* handle, const int32_t* actions_host, uint8_t* obs_host, float* rewards_host,
                  uint8_t* terminals_host, uint8_t* truncations_host);
 
+/* mg_step_host in two halves (mg_step_host = _begin, then _end): _begin enqueues the copies and the step and
+ * returns at once, _end waits until the buffers given to _begin are filled; the buffers (and actions_host)
+ * must stay untouched in between. For callers that split their envs over two handles and keep both in
+ * flight, the way the reference's vectorised env overlaps its workers (pufferlib's send/recv with
+ * batch_size = num_envs / 2, as metta/rl's async_factor 2 sets it up): one half's observations cross
+ * the host link while the other half steps. One _begin per handle at a time. */
+int mg_step_host_begin(void* handle, const int32_t* actions_host, uint8_t* obs_host, float* rewards_host,
+                       uint8_t* terminals_host, uint8_t* truncations_host);
+int mg_step_host_end(void* handle);
+
 /* How mg_step_host fills a page-locked obs_host (no counterpart in the reference, whose
  * _compute_observations rewrites every byte of the caller's buffer each step, mettagrid_c.cpp:557-563,
  * 580). mode 0 (default): the whole buffer crosses the host link every call. mode 1: after one full

@@ -160,6 +160,19 @@ class Batch:
             )
         )
 
+    def step_host_begin(self, actions, obs, rewards, terminals, truncations) -> None:
+        """step_host without the wait: returns once the copies and the step are enqueued. The arrays must
+        stay untouched until step_host_end()."""
+        self._check(
+            self._c.mg_step_host_begin(
+                self._h, actions.ctypes.data, obs.ctypes.data, rewards.ctypes.data, terminals.ctypes.data,
+                truncations.ctypes.data,
+            )
+        )
+
+    def step_host_end(self) -> None:
+        self._check(self._c.mg_step_host_end(self._h))
+
     def set_host_export(self, changed_rows_only: bool) -> None:
         """step_host with page-locked buffers: False = copy the whole observation buffer every call,
         True = after one full copy only write the part of each row that changed (the caller must not

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("MG_LIB_PATH") or os.path.join(_HERE, "csrc", "libmett
 # every symbol include/mettagrid_b200.h declares
 SYMBOLS = [
     "mg_last_error", "mg_abi_version", "mg_umap_order_u8", "mg_umap_order_str", "mg_create", "mg_destroy",
-    "mg_load_maps", "mg_set_buffers", "mg_reset", "mg_step", "mg_step_host", "mg_profile_step", "mg_compute_observations",
+    "mg_load_maps", "mg_set_buffers", "mg_reset", "mg_step", "mg_step_host", "mg_step_host_begin", "mg_step_host_end", "mg_profile_step", "mg_compute_observations",
     "mg_set_options", "mg_set_early_reset", "mg_sizeof", "mg_read", "mg_write", "mg_set_inventory",
     "mg_kernel_launches", "mg_sync", "mg_peek_observations_noalloc", "mg_set_host_export", "mg_transfer_bytes", "mg_set_obs_aux", "mg_token_record_layout",
 ]  # fmt: skip
@@ -50,6 +50,10 @@ def _declare(l: ctypes.CDLL) -> ctypes.CDLL:
     l.mg_step.restype = c_int
     l.mg_step_host.argtypes = [c_void_p] * 6
     l.mg_step_host.restype = c_int
+    l.mg_step_host_begin.argtypes = [c_void_p] * 6
+    l.mg_step_host_begin.restype = c_int
+    l.mg_step_host_end.argtypes = [c_void_p]
+    l.mg_step_host_end.restype = c_int
     l.mg_profile_step.argtypes = [c_void_p, c_void_p, c_void_p]
     l.mg_profile_step.restype = c_int
     l.mg_compute_observations.argtypes = [c_void_p, c_void_p]

@@ -75,6 +75,12 @@ struct MgEnvs {
   int step_mode;
   int sm_count;
   int q_early, q_late;  // observation CTAs per SM beside / behind the step kernel in queue mode
+  // mg_step_host_begin .. mg_step_host_end: what _end still has to do
+  struct HostPending {
+    bool active = false, staged = false;
+    uint8_t* obs = nullptr; float* rewards = nullptr; uint8_t* terminals = nullptr; uint8_t* truncations = nullptr;
+    size_t NA = 0, obs_bytes = 0, off_obs = 0, off_rew = 0, off_term = 0, off_trunc = 0;
+  } host_pending;
   bool graph_dirty;
   long long graph_launches, hgraph_launches;  // kernels per replay of the two graphs
   cudaGraph_t graph;
@@ -875,10 +881,14 @@ static bool is_pinned_host(const void* p) {
 // Host-buffer step: the call a numpy caller makes. actions i32 [N*A] in; obs, rewards, terminals,
 // truncations out. Page-locked caller buffers are used directly by the copy engines; pageable ones
 // go through the library's pinned staging buffer. Runs on the library's stream; returns when done.
-int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, uint8_t* terminals, uint8_t* truncations) {
+// mg_step_host in two halves: _begin enqueues the copies and the step on the handle's own stream and returns,
+// _end waits for them. A caller that keeps two handles (two halves of its envs) in flight has one half's
+// observations crossing the host link while the other half steps.
+int mg_step_host_begin(void* h, const int32_t* actions, uint8_t* obs, float* rewards, uint8_t* terminals, uint8_t* truncations) {
   MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
   if (!e || !actions || !obs || !rewards || !terminals || !truncations) return fail(MG_ERR_ARG, "mg_step_host: null pointer");
   if (!e->buffers_bound) return fail(MG_ERR_STATE, "mg_step_host: call mg_set_buffers first (all nulls = library-owned)");
+  if (e->host_pending.active) return fail(MG_ERR_STATE, "mg_step_host_begin: the previous mg_step_host_begin has not been ended");
   CUDA_TRY(cudaSetDevice(e->device));
   MgBatch& b = e->b;
   const size_t NA = (size_t)b.num_envs * b.A;
@@ -935,7 +945,8 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
       e->launches += e->hgraph_launches;
     }
     CUDA_TRY(cudaMemcpyAsync(e->h_export_bytes, e->d_export_bytes, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
+    e->host_pending = MgEnvs::HostPending();
+    e->host_pending.active = true;
     return MG_OK;
   }
 #endif
@@ -951,14 +962,37 @@ int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, 
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)rewards : (void*)(st + off_rew), b.rewards, NA * 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)terminals : (void*)(st + off_term), b.terminals, NA, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaMemcpyAsync(direct ? (void*)truncations : (void*)(st + off_trunc), b.truncations, NA, cudaMemcpyDeviceToHost, s));
-  CUDA_TRY(cudaStreamSynchronize(s));
-  if (!direct) {
-    memcpy(obs, st + off_obs, obs_bytes);
-    memcpy(rewards, st + off_rew, NA * 4);
-    memcpy(terminals, st + off_term, NA);
-    memcpy(truncations, st + off_trunc, NA);
+  MgEnvs::HostPending& hp = e->host_pending;
+  hp = MgEnvs::HostPending();
+  hp.active = true;
+  hp.staged = !direct;
+  hp.obs = obs; hp.rewards = rewards; hp.terminals = terminals; hp.truncations = truncations;
+  hp.NA = NA; hp.obs_bytes = obs_bytes; hp.off_obs = off_obs; hp.off_rew = off_rew; hp.off_term = off_term; hp.off_trunc = off_trunc;
+  return MG_OK;
+}
+
+int mg_step_host_end(void* h) {
+  MgEnvs* e = reinterpret_cast<MgEnvs*>(h);
+  if (!e) return fail(MG_ERR_ARG, "mg_step_host_end: null handle");
+  if (!e->host_pending.active) return fail(MG_ERR_STATE, "mg_step_host_end: no mg_step_host_begin to end");
+  CUDA_TRY(cudaSetDevice(e->device));
+  const MgEnvs::HostPending hp = e->host_pending;
+  e->host_pending.active = false;
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  if (hp.staged) {
+    const uint8_t* st = e->h_pinned;
+    memcpy(hp.obs, st + hp.off_obs, hp.obs_bytes);
+    memcpy(hp.rewards, st + hp.off_rew, hp.NA * 4);
+    memcpy(hp.terminals, st + hp.off_term, hp.NA);
+    memcpy(hp.truncations, st + hp.off_trunc, hp.NA);
   }
   return check_queue_error(e, "mg_step_host");
+}
+
+int mg_step_host(void* h, const int32_t* actions, uint8_t* obs, float* rewards, uint8_t* terminals, uint8_t* truncations) {
+  const int rc = mg_step_host_begin(h, actions, obs, rewards, terminals, truncations);
+  if (rc != MG_OK) return rc;
+  return mg_step_host_end(h);
 }
 
 // How mg_step_host delivers observations into a page-locked caller buffer. 0 (default): the whole

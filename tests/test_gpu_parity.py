@@ -240,6 +240,56 @@ def test_host_buffer_step_matches_oracle(pinned, changed_only, lib):
     b.close()
 
 
+@pytest.mark.parametrize("pinned", [False, True])
+def test_two_handles_in_flight_match_oracle(pinned, lib):
+    """mg_step_host_begin / mg_step_host_end: two handles (two halves of a caller's envs) stepped as a
+    software pipeline -- one half's results are read while the other half is in flight -- give what the
+    oracle gives for each half; a second _begin without _end and an _end without _begin are refused."""
+    import torch
+
+    from metta_b200.capi import MgError
+    from oracle.oracle import OracleEnv
+
+    cfg, grid = SCENARIOS["kitchen_sink"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    n, A, T = 6, cfg.game.num_agents, cfg.game.obs.num_tokens
+    mk = (lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()) if pinned else (
+        lambda shape, dt: np.empty(shape, dtype=torch.empty(0, dtype=dt).numpy().dtype))
+    halves = []
+    for h in range(2):
+        b = Batch(low, build_pool(low, codes[None]), n)
+        b.use_internal_buffers()
+        b.set_host_export(pinned)
+        seeds = np.arange(n, dtype=np.uint32) + 100 * (h + 1)
+        b.reset(seeds, np.zeros(n, np.int32))
+        bufs = (mk((n * A, T, 3), torch.uint8), mk((n * A,), torch.float32), mk((n * A,), torch.uint8), mk((n * A,), torch.uint8))
+        halves.append((b, bufs, mk((n * A,), torch.int32), [OracleEnv(low.words, codes, int(s)) for s in seeds]))
+    with pytest.raises(MgError):
+        halves[0][0].step_host_end()
+    rng = np.random.RandomState(3)
+    sent = [None, None]
+    for h, (b, bufs, act, _) in enumerate(halves):
+        act[:] = random_actions(rng, cfg, low, n * A)
+        sent[h] = act.copy()
+        b.step_host_begin(act, *bufs)
+    with pytest.raises(MgError):
+        halves[0][0].step_host_begin(halves[0][2], *halves[0][1])
+    for s in range(30):
+        for h, (b, bufs, act, orcs) in enumerate(halves):
+            b.step_host_end()
+            for i, o in enumerate(orcs):
+                o.step(sent[h][i * A : (i + 1) * A])
+                assert np.array_equal(bufs[0][i * A : (i + 1) * A], o.observations), f"step {s} half {h} env {i}"
+                assert np.array_equal(bufs[1][i * A : (i + 1) * A], o.rewards)
+            act[:] = random_actions(rng, cfg, low, n * A)
+            sent[h] = act.copy()
+            b.step_host_begin(act, *bufs)
+    for b, _, _, _ in halves:
+        b.step_host_end()
+        b.close()
+
+
 @pytest.mark.parametrize("chunks", ["1", "3"])
 def test_changed_rows_export_follows_resets(chunks, lib, monkeypatch):
     """Export mode 1 across episode ends (token counts drop back at a reset), a second buffer and a
