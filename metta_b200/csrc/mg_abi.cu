@@ -728,9 +728,14 @@ static int launch_fused_t(MgEnvs* e, const MgBatch& b, cudaStream_t s) {
   return MG_OK;
 }
 
+// The modes that hand an env to observation warps while other envs are still stepping rely on every cache
+// line a consumer reads belonging to one env. Agent and global-token records are 64 bytes per agent,
+// contiguous per env: whole 128-byte lines only for an even agent count. Otherwise the sliced graph is used.
+static bool handover_supported(const MgBatch& b) { return ((size_t)b.A * sizeof(AgentRec)) % 128 == 0; }
+
 static bool fused_supported(const MgBatch& b) {
   const int cpl = (b.obs_cells + 31) / 32;
-  return b.A <= 32 ? (cpl <= 4) : (cpl <= 4);
+  return handover_supported(b) && cpl <= 4;
 }
 
 static int enqueue_fused_step(MgEnvs* e, cudaStream_t s, const MgHostTargets* ht) {
@@ -797,7 +802,7 @@ static int capture_step_graph(MgEnvs* e, const MgHostTargets* ht, cudaGraph_t* g
   CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
   int rc;
   if (e->step_mode == 2 && fused_supported(e->b)) rc = enqueue_fused_step(e, e->capture_stream, ht);
-  else if (e->step_mode == 1 && ht == nullptr) rc = enqueue_queue_step(e, e->capture_stream);
+  else if (e->step_mode == 1 && ht == nullptr && handover_supported(e->b)) rc = enqueue_queue_step(e, e->capture_stream);
   else rc = enqueue_chunked_step(e, e->capture_stream, ht);
   cudaError_t end = cudaStreamEndCapture(e->capture_stream, graph);
   (ht != nullptr ? e->hgraph_launches : e->graph_launches) = e->launches - before;  // kernels one replay of this graph launches
