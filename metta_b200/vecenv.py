@@ -259,7 +259,9 @@ class GpuMettaGridVecEnv:
 
     @property
     def object_type_names(self) -> list[str]:
-        n = max(self.lowered.type_names) + 1 if self.lowered.type_names else 0
+        # MettaGrid::object_type_names: sized by the number of object configs (map cell names) first, then by
+        # the largest type id (mettagrid_c.cpp:163-178)
+        n = max(len(self.lowered.cell_codes), max(self.lowered.type_names) + 1) if self.lowered.type_names else 0
         return [self.lowered.type_names.get(i, "") for i in range(n)]
 
     @property

@@ -176,8 +176,47 @@ def clipper():
     run("cogames_clip_period", cfg, grid, 3, 700, c_cfg=c_cfg)
 
 
+def replay():
+    """An arena episode of 60 steps recorded by the reference's own replay writer (EpisodeReplay through the
+    Simulation event handlers, mettagrid/simulator/replay_log_writer.py): tests/golden/arena_replay.*"""
+    import zlib
+
+    import mettagrid.config.mettagrid_config  # noqa: F401  (first: mettagrid.simulator imports it back)
+    from mettagrid.builder.envs import make_arena
+    from mettagrid.simulator.replay_log_writer import InMemoryReplayWriter
+    from mettagrid.simulator.simulator import Simulation
+
+    ref_cfg = make_arena(24)
+    ref_cfg.game.map_builder.seed = 1000
+    ref_cfg.game.max_steps = 60
+    grid = ref_cfg.game.map_builder.create().build_for_num_agents(24).grid
+    writer = InMemoryReplayWriter()
+    sim = Simulation(ref_cfg, seed=42, event_handlers=[writer])
+    rng = np.random.RandomState(77)
+    acts = []
+    n_actions = len(sim.action_names)
+    while not sim.is_done():
+        a = rng.randint(0, min(n_actions, 6), size=24).astype(np.int32)
+        sim._c_sim.actions()[:] = a
+        sim.step()
+        acts.append(a)
+    (done,) = writer.get_completed_replays()
+    data = done.get_replay_data()
+    dump = ref_cfg.model_dump()
+    dump["game"]["map_builder"] = None
+    cfg = MettaGridConfig.from_reference(dump)
+    with open(os.path.join(HERE, "arena_replay.json"), "w") as f:
+        json.dump(cfg.model_dump(), f, indent=1, sort_keys=False, default=str)
+    np.savez_compressed(os.path.join(HERE, "arena_replay.npz"), grid=grid, seed=np.int64(42), actions=np.array(acts, np.int32))
+    with open(os.path.join(HERE, "arena_replay.replay.json.z"), "wb") as f:
+        f.write(zlib.compress(json.dumps(data).encode("utf-8"), 9))
+    print("arena_replay: steps", len(acts), "objects", len(data["objects"]), "bytes", os.path.getsize(os.path.join(HERE, "arena_replay.replay.json.z")))
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "clipper":
+    if len(sys.argv) > 1 and sys.argv[1] == "replay":
+        replay()
+    elif len(sys.argv) > 1 and sys.argv[1] == "clipper":
         cogames_clipper_config()
     elif len(sys.argv) > 1 and sys.argv[1] == "cogames":
         cogames()

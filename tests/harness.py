@@ -166,3 +166,43 @@ def random_actions(rng: np.random.RandomState, cfg, lowered, n: int, invalid_eve
         a[rng.randint(0, n)] = nact + rng.randint(0, 3)
         a[rng.randint(0, n)] = -1
     return a
+
+
+def check_replay_against_reference(clib=None, cuda: bool = False) -> None:
+    """tests/golden/arena_replay.*: an arena episode of 60 steps recorded by the reference's own EpisodeReplay
+    (tests/golden/make_golden.py replay). The same episode stepped here (env 1 of 2, so that the env index is
+    exercised) and recorded by metta_b200.replay must give the same replay: header, object records, every
+    change list -- everything but the embedded config dump, which is each side's own schema object."""
+    import json
+    import zlib
+
+    from golden_util import GOLDEN, load
+
+    from metta_b200.maps import names_to_codes
+    from metta_b200.replay import EpisodeReplay
+
+    cfg, grid, data = load("arena_replay")
+    with open(GOLDEN + "/arena_replay.replay.json.z", "rb") as f:
+        want = json.loads(zlib.decompress(f.read()))
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    seed = int(data["seed"])
+    ls = Lockstep(cfg, codes, num_envs=2, seeds=[seed + 5, seed], clib=clib, cuda=cuda)
+    rep = EpisodeReplay(ls.batch, 1, mg_config=None)
+    A = ls.A
+    rng = np.random.RandomState(4)
+    for s, a in enumerate(data["actions"]):
+        ls.step(np.concatenate([rng.randint(0, 5, size=A), a]))
+        _, rew, _, _ = ls.buf.fetch()
+        rep.log_step(s + 1, a, rew[A : 2 * A], ls.batch.read_action_success()[1])
+    got = json.loads(json.dumps(rep.data()))  # tuples -> lists, as the file would hold them
+    ls.close()
+    for key in want:
+        if key in ("mg_config", "objects"):
+            continue
+        assert got[key] == want[key], f"replay header {key}: {got[key]} vs {want[key]}"
+    assert len(got["objects"]) == len(want["objects"])
+    for i, (g, w) in enumerate(zip(got["objects"], want["objects"])):
+        assert g.keys() == w.keys(), f"object {i}: keys {sorted(g.keys() ^ w.keys())}"
+        for k in w:
+            assert g[k] == w[k], f"object {i} ({w.get('type_name')}) {k}: {g[k]} vs {w[k]}"

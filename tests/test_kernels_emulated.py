@@ -217,3 +217,9 @@ def test_emulated_grid_objects_match_the_reference(name, emu_lib):
     ref = ls.checkers[0].sim.grid_objects(1, 4, 2, 7, ["wall"])
     _same_grid_objects(ref, sub)
     ls.close()
+
+
+def test_emulated_replay_matches_the_reference_writer(emu_lib):
+    from harness import check_replay_against_reference
+
+    check_replay_against_reference(clib=emu_lib)
