@@ -167,6 +167,8 @@ class ReplayLogWriter:
 
     def on_step(self, actions) -> None:
         v, A, i = self.vecenv, self.vecenv.batch.num_agents, self.env
+        if getattr(v, "_inflight", False):
+            v._wait()  # host mode: the step that send() enqueued
         to_np = lambda x: x.detach().cpu().numpy() if hasattr(x, "detach") else np.asarray(x)  # noqa: E731
         sl = slice(i * A, (i + 1) * A)
         rewards = to_np(v._h_rew if v.host else v.rewards)[sl]

@@ -58,6 +58,7 @@ class GpuMettaGridVecEnv:
         host: bool = False,
         map_stride: int = 0,
         obs_mask: bool = False,
+        first_env: int = 0,
     ):
         import torch
 
@@ -97,7 +98,10 @@ class GpuMettaGridVecEnv:
         self.actions = torch.zeros(NA, dtype=torch.int32, device=dev)
         self.teacher_actions = torch.zeros(NA, dtype=torch.int32, device=dev)
         self.masks = torch.ones(NA, dtype=torch.bool, device=dev)
-        self.agent_ids = np.arange(NA)
+        # this object's envs are envs [first_env, first_env + num_envs) of a larger job (another rank, or the other
+        # half of a GpuMettaGridVecEnvPair): seeds, maps, agent ids and env_index in infos count from there
+        self.first_env = int(first_env)
+        self.agent_ids = np.arange(NA) + self.first_env * self.agents_per_env
         self.batch.set_buffers(
             self.observations.data_ptr(), self.terminals.data_ptr(), self.truncations.data_ptr(),
             self.rewards.data_ptr(), self.actions.data_ptr(),
@@ -121,6 +125,7 @@ class GpuMettaGridVecEnv:
             self._h_trunc = pin((NA,), torch.uint8).view(np.bool_)
             self._h_act = pin((NA,), torch.int32)
             self.batch.set_host_export(True)
+        self._inflight = False  # host mode: a step has been enqueued by send() and not yet waited for by recv()
         self._seed = seed
         self._map_stride = map_stride
         self._pending = None
@@ -143,8 +148,11 @@ class GpuMettaGridVecEnv:
             self._seed = seed
         if self._pending is not None:
             self._apply_pending_config()
-        seeds = (np.arange(self.num_envs, dtype=np.int64) + int(self._seed)) & 0xFFFFFFFF
-        maps = np.arange(self.num_envs) % len(self.pool.codes)
+        if self._inflight:
+            self.batch.step_host_end()
+            self._inflight = False
+        seeds = (self.first_env + np.arange(self.num_envs, dtype=np.int64) + int(self._seed)) & 0xFFFFFFFF
+        maps = (self.first_env + np.arange(self.num_envs)) % len(self.pool.codes)
         self.batch.reset(seeds.astype(np.uint32), maps.astype(np.int32))
         self._accum_prev = None
         self._steps[:] = 0
@@ -171,15 +179,27 @@ class GpuMettaGridVecEnv:
             limit = np.minimum(limit, self._max_steps)
         self._done = self._steps >= limit
         if self.host:
+            # enqueue and return (pufferlib's send); recv() waits. The caller's thread is free in between -- with a
+            # second object (GpuMettaGridVecEnvPair) it is acting on the other half of the envs
+            if self._inflight:
+                self.batch.step_host_end()
             self._h_act[...] = np.asarray(actions).reshape(-1)
-            self.batch.step_host(self._h_act, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
+            self.batch.step_host_begin(self._h_act, self._h_obs, self._h_rew, self._h_term.view(np.uint8), self._h_trunc.view(np.uint8))
+            self._inflight = True
             return
         if isinstance(actions, np.ndarray):
             actions = torch.from_numpy(np.ascontiguousarray(actions.reshape(-1), dtype=np.int32))
         self.actions.copy_(actions.reshape(-1).to(torch.int32), non_blocking=True)
         self.batch.step(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def _wait(self) -> None:
+        """Host mode: let the step that send() enqueued finish (everything that reads the batch does this first)."""
+        if self._inflight:
+            self.batch.step_host_end()
+            self._inflight = False
+
     def recv(self):
+        self._wait()
         infos = self._infos()
         if self.host:
             return (self._h_obs, self._h_rew, self._h_term, self._h_trunc, None, infos, self.agent_ids, None)
@@ -192,6 +212,9 @@ class GpuMettaGridVecEnv:
         return o, r, d, t, infos
 
     def close(self) -> None:
+        if self._inflight:
+            self.batch.step_host_end()
+            self._inflight = False
         self.batch.close()
 
     # ---- metta/rl TrainingEnvironment surface
@@ -212,6 +235,7 @@ class GpuMettaGridVecEnv:
     def episode_stats(self) -> dict[str, float]:
         """Sums over all episodes finished on this GPU since construction (a dense vector that
         ``reduce_episode_stats`` all-reduces across ranks)."""
+        self._wait()
         acc = self.batch.read_episode_accum()
         names_a = agent_stat_names(self.lowered, 0)
         names_g = game_stat_names(self.lowered)
@@ -228,6 +252,7 @@ class GpuMettaGridVecEnv:
     def set_early_reset(self, steps) -> None:
         """EarlyResetHandler (mettagrid/envs/early_reset_handler.py:12-20): truncate the running episode of
         env i once its step count reaches steps[i] (0 = never)."""
+        self._wait()
         steps = np.ascontiguousarray(steps, dtype=np.uint32)
         self.batch.set_early_reset(steps)
         self._early[:] = steps
@@ -271,12 +296,14 @@ class GpuMettaGridVecEnv:
 
     def action_success(self) -> np.ndarray:
         """bool [num_envs, agents_per_env]: MettaGrid::action_success of the last step."""
+        self._wait()
         return self.batch.read_action_success()
 
     def grid_objects(self, env_index: int = 0, min_row: int = -1, max_row: int = -1, min_col: int = -1, max_col: int = -1,
                      ignore_types: Sequence[str] = ()) -> dict[int, dict]:
         """MettaGrid::grid_objects (mettagrid_c.cpp:754-868) of one env: the reference's dicts, same ids, keys and
         inventory iteration order (a host-side tooling path: it reads the env's records back)."""
+        self._wait()
         from .grid_objects import grid_objects
 
         return grid_objects(self.batch, env_index, min_row, max_row, min_col, max_col, tuple(ignore_types))
@@ -288,16 +315,18 @@ class GpuMettaGridVecEnv:
         self._pending = (cfg, maps, map_codes)
 
     def _apply_pending_config(self) -> None:
+        self._wait()
         cfg, maps, map_codes = self._pending
         self._pending = None
         if maps is None and map_codes is None:
             map_codes = self.pool.codes
         self.batch.close()
         self.__init__(cfg, self.num_envs, maps=maps, map_codes=map_codes, seed=self._seed, device=self.device, host=self.host,
-                      map_stride=self._map_stride, obs_mask=self._want_obs_mask)
+                      map_stride=self._map_stride, obs_mask=self._want_obs_mask, first_env=self.first_env)
 
     def get_episode_rewards(self):
         """f32 [num_envs, agents_per_env] (MettaGrid::get_episode_rewards; CurriculumEnv takes its mean)."""
+        self._wait()
         return self.batch.read_episode_rewards()
 
     def _infos(self) -> list[dict]:
@@ -332,15 +361,64 @@ class GpuMettaGridVecEnv:
                     "steps": int(recs["current_step"][k]), "max_steps": self._max_steps, "completion_time": now,
                 },
                 "episode_rewards": rewards[k].copy(),
-                "env_index": int(env),
+                "env_index": self.first_env + int(env),
             })
         return out
 
     def reduce_episode_stats(self):
         """All-reduce (SUM) the episode accumulators over the process group: the only collective of
         the env path. Returns a float64 tensor on this rank's GPU."""
+        self._wait()
         torch = self._torch
         from .sharding import reduce_episode_accumulators
 
         acc = torch.from_numpy(self.batch.read_episode_accum()).to(self.device)
         return reduce_episode_accumulators(acc)
+
+
+class GpuMettaGridVecEnvPair:
+    """The envs as two halves that are stepped alternately, for numpy callers: `recv()` hands out the halves in
+    turn, `send(actions)` answers the half received last and returns at once, so one half's observations cross
+    the host link while the caller works on the other half. This is pufferlib's asynchronous contract with
+    `batch_size = num_envs / 2`, which the reference's trainer sets up with `async_factor` 2
+    (metta/rl/training/training_environment.py:45,152-169, batch.py:10-19): every `recv()` returns the arrays of
+    `num_agents / 2` agents and their `agent_ids`.
+
+    Each half is a complete GpuMettaGridVecEnv(host=True) of its own (own handle, own page-locked arrays); seeds,
+    maps, agent ids and `env_index` in the infos are those of one env object over all `num_envs`."""
+
+    def __init__(self, cfg, num_envs: int, seed: int = 0, **kw):
+        if num_envs % 2:
+            raise ValueError("GpuMettaGridVecEnvPair needs an even number of envs")
+        kw.pop("host", None)
+        half = num_envs // 2
+        self.halves = [GpuMettaGridVecEnv(cfg, half, seed=seed, host=True, first_env=h * half, **kw) for h in range(2)]
+        first = self.halves[0]
+        self.num_envs, self.agents_per_env = num_envs, first.agents_per_env
+        self.num_agents = num_envs * first.agents_per_env
+        self.batch_size = self.num_agents // 2  # agents per recv()
+        self.single_observation_space, self.single_action_space = first.single_observation_space, first.single_action_space
+        self.action_names = first.action_names
+        self.driver_env = first
+        self._next = self._last = 0
+
+    def async_reset(self, seed: Optional[int] = None) -> None:
+        for h in self.halves:
+            h.async_reset(seed)
+        self._next = self._last = 0
+
+    def recv(self):
+        self._last = self._next
+        self._next ^= 1
+        return self.halves[self._last].recv()
+
+    def send(self, actions) -> None:
+        self.halves[self._last].send(actions)
+
+    def close(self) -> None:
+        for h in self.halves:
+            h.close()
+
+    def episode_stats(self) -> dict[str, float]:
+        a, b = (h.episode_stats() for h in self.halves)
+        return {k: a.get(k, 0.0) + b.get(k, 0.0) for k in set(a) | set(b)}

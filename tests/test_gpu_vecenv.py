@@ -264,3 +264,44 @@ def test_replay_log_writer_writes_one_file_per_episode(tmp_path):
         agents = [o for o in rep["objects"] if o.get("is_agent")]
         assert len(agents) == A and all("location" in o and "total_reward" in o for o in agents)
     env.close()
+
+
+def test_pair_of_halves_matches_one_env_object():
+    """GpuMettaGridVecEnvPair (pufferlib's asynchronous contract with batch_size = num_envs / 2, the reference
+    trainer's async_factor 2): the halves handed out in turn carry, step for step, what one host-mode env object
+    over all envs returns for those envs -- observations, rewards, flags, agent ids, and the infos of finished
+    episodes with their global env indices."""
+    from metta_b200.vecenv import GpuMettaGridVecEnv, GpuMettaGridVecEnvPair
+
+    cfg, grid = SCENARIOS["tiny_truncating"]()
+    low = lower_game_config(cfg.game, grid.shape[0], grid.shape[1])
+    codes = names_to_codes(low, grid)
+    n, A = 6, cfg.game.num_agents
+    one = GpuMettaGridVecEnv(cfg, n, map_codes=codes[None], seed=21, host=True)
+    pair = GpuMettaGridVecEnvPair(cfg, n, map_codes=codes[None], seed=21)
+    assert pair.batch_size == n * A // 2
+    one.async_reset(21)
+    pair.async_reset(21)
+    rng = np.random.RandomState(5)
+    episodes = 0
+    for step in range(2 * cfg.game.max_steps + 3):
+        o, r, d, t, _, infos, ids, _ = one.recv()
+        acts = []
+        for h in range(2):
+            ph = pair.recv()
+            sl = slice(h * n * A // 2, (h + 1) * n * A // 2)
+            assert np.array_equal(ph[0], o[sl]), f"step {step} half {h}: observations"
+            assert np.array_equal(ph[1], r[sl]) and np.array_equal(ph[2], d[sl]) and np.array_equal(ph[3], t[sl])
+            assert np.array_equal(ph[6], ids[sl])
+            want = [i for i in infos if (i["env_index"] >= n // 2) == bool(h)]
+            assert [i["env_index"] for i in ph[5]] == [i["env_index"] for i in want]
+            for got, w in zip(ph[5], want):
+                assert got["game"] == w["game"] and got["agent"] == w["agent"] and got["attributes"]["seed"] == w["attributes"]["seed"]
+            episodes += len(ph[5])
+            a = random_actions(rng, cfg, low, n * A // 2)
+            pair.send(a)
+            acts.append(a)
+        one.send(np.concatenate(acts))
+    assert episodes == 2 * n
+    one.close()
+    pair.close()

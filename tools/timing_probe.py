@@ -28,6 +28,8 @@ for s in range(STEPS):
     if FLUSH: flush.fill_(s)
     torch.cuda.synchronize()
     if s == STEPS-1: uses0 = b.read_assemblers()["uses_count"].astype(np.int64).sum(1)
+    if s == STEPS-1:
+        prev_sp = b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64); prev_sp[:,10] = 0; prev_tot = prev_sp.sum(1)
     b.step(); torch.cuda.synchronize()
 uses = b.read_assemblers()["uses_count"].astype(np.int64).sum(1) - uses0
 sp=b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64)
@@ -70,3 +72,11 @@ order=np.argsort(-end)[:16]
 print('the envs that end last: env start end | load decide act-par act-ord post finish | uses')
 for e in order:
     print('%5d %7.0f %7.0f | %6.0f %6.0f %6.0f %6.0f %6.0f %6.0f | %d' % (e, rel[e], end[e], sp[e,0:3].sum(), sp[e,3:6].sum(), sp[e,6], sp[e,7], sp[e,8], sp[e,9]+sp[e,11], uses[e]))
+
+# is a slow env slow again in the next step? (what sorting envs into slices by their last chain length could buy)
+ok = (prev_tot < 100000) & (tot < 100000)
+r = np.corrcoef(prev_tot[ok], tot[ok])[0,1]
+heavy_prev = prev_tot > np.percentile(prev_tot, 75); heavy_now = tot > np.percentile(tot, 75)
+print('chain length, this step against the previous one: correlation %.3f; P(top quarter now | top quarter before) %.3f; P(top quarter now | not before) %.3f' % (r, heavy_now[heavy_prev].mean(), heavy_now[~heavy_prev].mean()))
+very = tot > np.percentile(tot, 95)
+print('of the slowest 5%% now, %.1f%% were in the top quarter before; the light three quarters (by the previous step) would end at p99 %.0f max %.0f cycles, all envs p99 %.0f max %.0f' % (100*heavy_prev[very].mean(), np.percentile(tot[~heavy_prev],99), tot[~heavy_prev & ok].max(), np.percentile(tot,99), tot[ok].max()))
