@@ -1,3 +1,10 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_vecenv.py -m gpu -x -q 2>&1 | tail -15 | tee gpurun_out/gpu_tests.txt
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 | tee gpurun_out/gpu_tests.txt
+( time python bench.py > gpurun_out/bench_final.json 2> gpurun_out/bench_final.err ) 2>&1 | grep real
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_final.json').read().strip().splitlines()[-1])
+print('value %.1f M/s e2e %.1f M/s frac %.3f launches %d' % (d['value']/1e6, d['e2e']['value']/1e6, d['roofline']['frac'], d['gpu_launches']))
+PY
