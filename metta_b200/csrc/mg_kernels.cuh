@@ -1436,14 +1436,16 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
   obs_row_finish_warp(b, env, ai, g, attempted, done_word, lane);
 }
 
-template <int CPL>
+// MASKED: only the envs with mask[env] != 0 (mg_reset / mg_compute_observations of some envs); the pass behind a
+// step is the unmasked instantiation, which does not carry the test
+template <int CPL, bool MASKED = true>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
   if (ai >= b.A) return;
-  if (mask != nullptr && !mask[env]) return;
+  if (MASKED && mask != nullptr && !mask[env]) return;
   obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 }
 
