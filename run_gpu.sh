@@ -1,17 +1,13 @@
 #!/bin/bash
-mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
-B="python bench.py --no-cpu-baseline --no-other-configs --steps 100"
-run() { name=$1; shift; env "$@" $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
-run default A=1
-run default2 A=1
-run default3 A=1
-python - <<'PY' | tee gpurun_out/summary.txt
-import json,glob
-for f in sorted(glob.glob('gpurun_out/bench_*.json')):
-    try:
-        d=json.loads(open(f).read().strip().splitlines()[-1])
-        pk=d['roofline']['per_kernel']; sm=d['step_ms']
-        print('%-28s %7.1f M/s  %.4f ms  frac %.3f  step %.4f obs %.4f free %7.1f  min %.4f med %.4f p90 %.4f max %.4f' % (f.split('/')[-1], d['value']/1e6, d['ms_per_step'], d['roofline']['frac'], pk['mg_step_kernel']['ms'], pk['mg_obs_kernel']['ms'], d['free_running']['value']/1e6, sm['min'], sm['median'], sm['p90'], sm['max']))
-    except Exception as ex:
-        print(f, 'FAILED', ex); print(open(f.replace('.json','.err')).read()[-500:])
+mkdir -p gpurun_out
+for n in 4 8; do
+( time python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --steps 20 --warmup 5 > gpurun_out/bench_${n}gpu.json 2> gpurun_out/bench_${n}gpu.err ) 2>&1 | grep real
+tail -c 300 gpurun_out/bench_${n}gpu.err
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/bench_${n}gpu.json').read().strip().splitlines()[-1])
+print('n_gpus %d value %.1f M/s ms %.4f per_rank %s' % (d['n_gpus'], d['value']/1e6, d['ms_per_step'], [round(x,4) for x in d['per_rank_ms']]))
+print('e2e', {k:round(v['value']/1e6,1) for k,v in d['e2e']['modes'].items()}, {k:round(v,1) for k,v in d['e2e']['host_link'].items()})
+print({k:round(v['value']/1e6,1) for k,v in d['other_configs'].items()})
 PY
+done
