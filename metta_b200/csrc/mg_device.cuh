@@ -326,32 +326,28 @@ MG_DEVICE inline const int32_t* asm_type_cfg(const int32_t* cfg, int cell) {
 
 // Assembler::get_local_vibe + surrounding agent count (assembler.hpp:30-45,353-375)
 MG_DEVICE inline uint64_t asm_local_vibe(const EnvCtx& e, int r, int c, int* num_agents) {
-  uint32_t vibes[8];
-  int nv = 0, na = 0;
-  MG_ROLLED
-  for (int i = -1; i <= 1; i++)
-    MG_ROLLED
-    for (int j = -1; j <= 1; j++) {
-      if (i == 0 && j == 0) continue;
-      int rr = r + i, cc = c + j;
-      if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
-      uint16_t g = grid_at(e, rr, cc);
-      if (MG_GRID_KIND(g) == MG_GK_AGENT) {
-        na++;
-        uint32_t vb = e.ag[MG_GRID_INDEX(g)].vibe;
-        if (vb != 0) vibes[nv++] = vb;
-      }
-    }
-  MG_ROLLED
-  for (int i = 1; i < nv; i++) {
-    uint32_t x = vibes[i];
-    int j = i - 1;
-    while (j >= 0 && vibes[j] > x) { vibes[j + 1] = vibes[j]; j--; }
-    vibes[j + 1] = x;
+  // the eight cells first (eight loads in flight), then what stands there; row-major order as in the reference
+  uint16_t cell[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const int rr = r + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = c + (int)((0x9224u >> (2 * k)) & 3u) - 1;
+    cell[k] = (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) ? (uint16_t)0 : grid_at(e, rr, cc);
   }
-  uint64_t key = 0;
-  MG_ROLLED
-  for (int i = 0; i < nv; i++) key = (key << 8) | vibes[i];
+  uint64_t key = 0;  // non-zero vibes, sorted, smallest in the highest used byte (inserted one by one)
+  int nv = 0, na = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    if (MG_GRID_KIND(cell[k]) != MG_GK_AGENT) continue;
+    na++;
+    const uint32_t vb = e.ag[MG_GRID_INDEX(cell[k])].vibe;
+    if (vb == 0u) continue;
+    int gt = 0;  // entries already in the key that are larger: they sit at the low end
+    while (gt < nv && ((key >> (8 * gt)) & 0xFFull) > vb) gt++;
+    const uint64_t low = gt == 0 ? 0ull : (key & ((1ull << (8 * gt)) - 1ull));
+    const uint64_t high = gt >= 7 ? 0ull : ((key >> (8 * gt)) << (8 * (gt + 1)));
+    key = high | ((uint64_t)vb << (8 * gt)) | low;
+    nv++;
+  }
   *num_agents = na;
   return key;
 }

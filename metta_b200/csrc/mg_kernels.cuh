@@ -212,20 +212,19 @@ MG_DEVICE MG_NOINLINE void fold_token_stats_warp(const MgBatch& b, int env, int 
 // step (see sink_object). One agent per lane; duplicates write identical values.
 MG_DEVICE MG_NOINLINE void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
   if (!b.cfg[MGC_HAS_VIBE_ASM] || !b.cfg[MGC_PROTOCOL_DETAILS_OBS]) return;
-  for (int ai = lane; ai < e.A; ai += 32) {
-    const int r = e.ag[ai].r, c = e.ag[ai].c;
-    for (int i = -1; i <= 1; i++)
-      for (int j = -1; j <= 1; j++) {
-        if (i == 0 && j == 0) continue;
-        const int rr = r + i, cc = c + j;
-        if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
-        const uint16_t g = grid_at(e, rr, cc);
-        if (MG_GRID_KIND(g) != MG_GK_ASM) continue;
-        AsmRec* a = &e.asms[MG_GRID_INDEX(g)];
-        const int pi = asm_current_protocol(e, a);
-        a->cache_protocol = pi;
-        a->cache_step = e.current_step;
-      }
+  // one (agent, neighbouring cell) pair per lane: with a handful of agents per env a lane per agent would
+  // leave most of the warp idle while each agent walks its eight cells and every assembler it finds walks its
+  // own eight. An assembler next to two agents is computed twice, with the same result.
+  for (int pair = lane; pair < e.A * 8; pair += 32) {
+    const int ai = pair >> 3, k = pair & 7;
+    const int rr = (int)e.ag[ai].r + (int)((0xA940u >> (2 * k)) & 3u) - 1, cc = (int)e.ag[ai].c + (int)((0x9224u >> (2 * k)) & 3u) - 1;
+    if (rr < 0 || cc < 0 || rr >= e.H || cc >= e.W) continue;
+    const uint16_t g = grid_at(e, rr, cc);
+    if (MG_GRID_KIND(g) != MG_GK_ASM) continue;
+    AsmRec* a = &e.asms[MG_GRID_INDEX(g)];
+    const int pi = asm_current_protocol(e, a);
+    a->cache_protocol = pi;
+    a->cache_step = e.current_step;
   }
   __syncwarp();
 }
@@ -1143,7 +1142,13 @@ MG_DEVICE MG_PHASE_POST_FN void step_phase_post(const MgBatch& b, StepSmem<MAXA>
     if (lane == 0) er.clip_rng_idx = cidx;
   }
 
+#ifdef MG_TIMING_SPLIT_POST
+  MG_SM_TICK(sm, 2);  // (probe: regen, damage, clipper land in slot 2, the protocol cache in slot 1, the record rewrite in slot 8)
+#endif
   update_protocol_cache_warp(b, e, lane);
+#ifdef MG_TIMING_SPLIT_POST
+  MG_SM_TICK(sm, 1);
+#endif
   // where the visible protocol can change without the assembler being used (vibes of neighbours, the
   // clipper), all assembler records are refreshed; otherwise assembler_on_use already did it
   if (cfg[MGC_HAS_VIBE_ASM]) write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);

@@ -80,3 +80,13 @@ heavy_prev = prev_tot > np.percentile(prev_tot, 75); heavy_now = tot > np.percen
 print('chain length, this step against the previous one: correlation %.3f; P(top quarter now | top quarter before) %.3f; P(top quarter now | not before) %.3f' % (r, heavy_now[heavy_prev].mean(), heavy_now[~heavy_prev].mean()))
 very = tot > np.percentile(tot, 95)
 print('of the slowest 5%% now, %.1f%% were in the top quarter before; the light three quarters (by the previous step) would end at p99 %.0f max %.0f cycles, all envs p99 %.0f max %.0f' % (100*heavy_prev[very].mean(), np.percentile(tot[~heavy_prev],99), tot[~heavy_prev & ok].max(), np.percentile(tot,99), tot[ok].max()))
+
+# what would the kernel's end be if a phase were capped? (which tail is worth working on)
+okk = sp[:,0] < 100000  # leave the env that started a new episode out
+def kernel_end(adj_tot, first_wave_only=False):
+    e = rel + adj_tot/1.92
+    m = okk & ((rel < 10000) if first_wave_only else True)
+    return e[m].max()
+print('kernel end (ns), slowest env: now %.0f; ordered pass capped at 10k cycles %.0f; parallel pass capped at 15k %.0f; both %.0f; first wave only, now %.0f' % (
+    kernel_end(tot), kernel_end(tot - np.maximum(0, sp[:,7]-10000)), kernel_end(tot - np.maximum(0, sp[:,6]-15000)),
+    kernel_end(tot - np.maximum(0, sp[:,7]-10000) - np.maximum(0, sp[:,6]-15000)), kernel_end(tot, True)))
