@@ -248,6 +248,11 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
       }
     }
   }
+  b.any_chest_search = 0;
+  for (int c = 1; c < cfg[MGC_NUM_CELLTYPES] && c < MG_MAX_CELLTYPES; c++) {
+    const int32_t* cc = cfg + cfg[MGC_OFF_CELLTYPES] + c * MG_CELL_WORDS;
+    if (cc[MG_CELL_KIND] == MG_KIND_ASSEMBLER && cfg[cfg[MGC_OFF_ASM_TYPES] + cc[MG_CELL_PARAM] * MG_ASM_WORDS + MG_ASM_CHEST_DISTANCE] > 0) b.any_chest_search = 1;
+  }
   {  // one line per map cell code with everything a use of a one-protocol assembler reads (assembler_use_warp)
     std::vector<int32_t> fast((size_t)MG_MAX_CELLTYPES * MG_AF_WORDS, 0);
     for (int c = 1; c < cfg[MGC_NUM_CELLTYPES] && c < MG_MAX_CELLTYPES; c++) {

@@ -755,10 +755,6 @@ MG_DEVICE MG_PHASE_LOAD_FN void step_phase_load(const MgBatch& b, StepSmem<MAXA>
     // the generator words the shuffle will draw from: one more load in this batch instead of an HBM
     // round trip of its own in the next phase
     const uint32_t rng_first = er.rng_idx;
-#ifdef MG_TIMING_SPLIT_LOAD
-    if (rng_first == 0xDEADBEEFu) sm.publish = 7u;  // (forces the wait for EnvRec before the tick)
-    MG_SM_TICK(sm, 0);
-#endif
     const uint32_t rng_n = rng_first < MT_N ? (MT_N - rng_first < 32u ? MT_N - rng_first : 32u) : 0u;
     // straight into the shared block, in the background: the decide phase waits for it where it draws (this load
     // depends on EnvRec, so it is a memory round trip of its own; nothing in this phase needs its result)
@@ -815,11 +811,7 @@ MG_DEVICE MG_PHASE_LOAD_FN void step_phase_load(const MgBatch& b, StepSmem<MAXA>
         }
       }
     }
-#ifdef MG_TIMING_SPLIT_LOAD
-    MG_SM_TICK(sm, 1);
-#else
     MG_SM_TICK(sm, 0);
-#endif
     if (er.done && b.auto_reset && !fresh) {  // MettaGridPufferEnv.step: new Simulation, then apply the actions
 #ifdef MG_HAS_BULK_LOAD
       mg_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_bar), sm.stage_phase);  // the old episode's records: let the copy land, then drop it
@@ -876,9 +868,7 @@ MG_DEVICE MG_PHASE_LOAD_FN void step_phase_load(const MgBatch& b, StepSmem<MAXA>
     break;
   }
   __syncwarp();
-#ifndef MG_TIMING_SPLIT_LOAD
   MG_SM_TICK(sm, 1);
-#endif
   // the stat slots the rewards will read at the end of the step: start pulling them in now (configs whose
   // rewards only look at hot counters and <res>.amount, like the arena, have none)
   if (b.reward_stat_prefetch) {
@@ -999,9 +989,9 @@ MG_DEVICE MG_PHASE_DECIDE_FN void step_phase_decide(const MgBatch& b, StepSmem<M
     }
     bool uses_asm = moving && tkind == MG_GK_ASM;
     if (moving && tkind == MG_GK_CHEST) ordered = true;                                     // (4)
-    if (uses_asm) {
+    if (uses_asm && (b.has_clipper || b.any_chest_search)) {  // (4); most configs have neither: no look at the record then
       const AsmRec* ar = &e.asms[MG_GRID_INDEX(my_target)];
-      if (b.has_clipper || asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE] > 0) ordered = true;  // (4)
+      if (b.has_clipper || asm_type_cfg(cfg, ar->cell)[MG_ASM_CHEST_DISTANCE] > 0) ordered = true;
     }
     // (3) every agent compares its own cell and the cell it moves into with the block of each user: no
     // grid reads (agents stand where their records say)
@@ -1142,13 +1132,7 @@ MG_DEVICE MG_PHASE_POST_FN void step_phase_post(const MgBatch& b, StepSmem<MAXA>
     if (lane == 0) er.clip_rng_idx = cidx;
   }
 
-#ifdef MG_TIMING_SPLIT_POST
-  MG_SM_TICK(sm, 2);  // (probe: regen, damage, clipper land in slot 2, the protocol cache in slot 1, the record rewrite in slot 8)
-#endif
   update_protocol_cache_warp(b, e, lane);
-#ifdef MG_TIMING_SPLIT_POST
-  MG_SM_TICK(sm, 1);
-#endif
   // where the visible protocol can change without the assembler being used (vibes of neighbours, the
   // clipper), all assembler records are refreshed; otherwise assembler_on_use already did it
   if (cfg[MGC_HAS_VIBE_ASM]) write_all_asm_tokens_warp(b, env, lane, er.n_asm, er.current_step);

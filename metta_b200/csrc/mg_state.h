@@ -132,6 +132,7 @@ struct MgBatch {
   // derived from the config once, on the host (mg_create):
   uint32_t req_mask[3], con_mask[3];  // per action kind: resources it requires / consumes (bit per item)
   int32_t any_damage;          // some agent group has damage enabled
+  int32_t any_chest_search;    // some assembler type searches chests (chest_search_distance > 0): its users are ordered
   int32_t reward_stat_prefetch;  // some reward term reads a stat slot that lives in HBM (not a hot slot, not <res>.amount)
   int32_t reward_game_stats;   // some reward term reads a game stat
   int32_t inv_masks_off;       // appended: per INVCFG record [MG_MAX_LIMITS] member masks, [MG_MAX_LIMITS] modifier masks

@@ -174,7 +174,8 @@ class ReplayLogWriter:
         rewards = to_np(v._h_rew if v.host else v.rewards)[sl]
         term = to_np(v._h_term if v.host else v.terminals)[sl]
         trunc = to_np(v._h_trunc if v.host else v.truncations)[sl]
-        self.replay.log_step(self.replay.step + 1, to_np(actions).reshape(-1)[sl], rewards, v.action_success()[i])
+        # the env's own step count (host mirror): a step that was not logged shows up as a mismatch, as in the reference
+        self.replay.log_step(int(v._steps[i]), to_np(actions).reshape(-1)[sl], rewards, v.action_success()[i])
         if term.all() or trunc.all():
             path = os.path.join(self.dir, self.episode_id + ".json.z")
             self.replay.write(path)
