@@ -1376,6 +1376,7 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 #ifndef MG_OBS_DONE_LATE
   const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
 #endif
+#ifdef MG_OBS_STORE16
   {
     uint4 ff;
     ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
@@ -1388,6 +1389,10 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
   }
   __syncwarp();
   const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step);
+#else
+  // (the image is filled with 0xFF inside, behind the first loads)
+  const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step, slot >> 4);
+#endif
   __syncwarp();
 #ifdef MG_OBS_STORE16
   {  // bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)

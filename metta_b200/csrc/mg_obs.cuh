@@ -78,27 +78,41 @@ MG_DEVICE inline int obs_count_cells_warp(const MgBatch& b, int env, int ai, int
 // then looks at one OBJECT per lane (record header, cooldown, token count, prefix sum, descriptor)
 // instead of CPL cells per lane. The cell list shares `desc`'s second half: an entry is read before the
 // descriptors written in the same round can reach it (descriptors are 8 bytes, at most one per object).
+// `fill_words`: > 0 = first set that many 16-byte words at `row` (the whole image) to 0xFF. The caller's fill is
+// done here so that the loads everything else waits for -- the agent's position, its global tokens, the
+// lane's pattern entries -- are already in flight while the image is filled.
 template <int CPL>
-MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step) {
+MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step,
+                                         int fill_words = 0) {
   const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
   const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
+  // ---- global tokens: prepared by the step kernel (a count, then up to 21 triples in a 64-byte record)
+  const uint8_t* gt = b.gtok + ((size_t)env * b.A + ai) * MG_GTOK_STRIDE;
+  const int n_global = gt[0];
+  const uint8_t gt_lo = gt[1 + lane], gt_hi = lane < 31 ? gt[33 + lane] : (uint8_t)0xFF;
+  const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);
+  if (fill_words > 0) {
+    uint4 ff;
+    ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
+    uint4* p = reinterpret_cast<uint4*>(row);
+    if (lane < fill_words) p[lane] = ff;
+    if (lane + 32 < fill_words) p[lane + 32] = ff;
+#pragma unroll 1
+    for (int i = lane + 64; i < fill_words; i += 32) p[i] = ff;
+    __syncwarp();
+  }
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
   const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
   const int T = b.T;
   uint32_t* cells = reinterpret_cast<uint32_t*>(desc) + CPL * 32;
-
-  // ---- global tokens: prepared by the step kernel, copied byte by byte
-  const uint8_t* gt = b.gtok + ((size_t)env * b.A + ai) * MG_GTOK_STRIDE;
-  const int n_global = gt[0];
   {
     const int nb = (n_global < T ? n_global : T) * 3;  // <= 63 bytes (MG_GTOK_STRIDE)
-    if (lane < nb) row[lane] = gt[1 + lane];
-    if (lane + 32 < nb) row[lane + 32] = gt[33 + lane];
+    if (lane < nb) row[lane] = gt_lo;
+    if (lane + 32 < nb) row[lane + 32] = gt_hi;
   }
 
   // ---- pass 1a: grid values of my CPL cells; non-empty ones go to the cell list in window order
-  const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);
   uint32_t cell[CPL];  // grid value | location << 16, 0 = nothing there
   const uint32_t lower = (1u << lane) - 1u;
   int rank = 0, n_obj = 0;
