@@ -210,7 +210,7 @@ MG_DEVICE MG_NOINLINE void fold_token_stats_warp(const MgBatch& b, int env, int 
 
 // Cache, on every assembler that has an agent next to it, the protocol observers will see this
 // step (see sink_object). One agent per lane; duplicates write identical values.
-MG_DEVICE MG_NOINLINE void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
+MG_DEVICE inline void update_protocol_cache_warp(const MgBatch& b, EnvCtx& e, int lane) {
   if (!b.cfg[MGC_HAS_VIBE_ASM] || !b.cfg[MGC_PROTOCOL_DETAILS_OBS]) return;
   // one (agent, neighbouring cell) pair per lane: with a handful of agents per env a lane per agent would
   // leave most of the warp idle while each agent walks its eight cells and every assembler it finds walks its
