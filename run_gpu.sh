@@ -2,10 +2,10 @@
 mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
 B="python bench.py --no-cpu-baseline --no-other-configs --steps 100"
 run() { name=$1; shift; env "$@" $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
-for i in 1 2 3; do
-run base$i MG_LIB_PATH=build_variants/lib_base.so
-run rw4_$i MG_LIB_PATH=build_variants/lib_rw4.so
-done
+run base1 A=1
+run rpw3_1 MG_OBS_RPW=3
+run base2 A=1
+run rpw3_2 MG_OBS_RPW=3
 python - <<'PY' | tee gpurun_out/summary.txt
 import json,glob
 for f in sorted(glob.glob('gpurun_out/bench_*.json')):
