@@ -28,6 +28,7 @@ for s in range(STEPS):
     if FLUSH: flush.fill_(s)
     torch.cuda.synchronize()
     if s == STEPS-1: uses0 = b.read_assemblers()["uses_count"].astype(np.int64).sum(1)
+    if s == STEPS-1: ord0 = b.read_env()["spare"][:, 0].astype(np.int64)
     if s == STEPS-1:
         prev_sp = b.read_buffer(16, np.uint32, (N, 16)).astype(np.float64); prev_sp[:,10] = 0; prev_tot = prev_sp.sum(1)
     b.step(); torch.cuda.synchronize()
@@ -90,3 +91,15 @@ def kernel_end(adj_tot, first_wave_only=False):
 print('kernel end (ns), slowest env: now %.0f; ordered pass capped at 10k cycles %.0f; parallel pass capped at 15k %.0f; both %.0f; first wave only, now %.0f' % (
     kernel_end(tot), kernel_end(tot - np.maximum(0, sp[:,7]-10000)), kernel_end(tot - np.maximum(0, sp[:,6]-15000)),
     kernel_end(tot - np.maximum(0, sp[:,7]-10000) - np.maximum(0, sp[:,6]-15000)), kernel_end(tot, True)))
+
+# what does one agent cost in the ordered pass?
+n_ord = b.read_env()["spare"][:, 0].astype(np.int64) - ord0
+m = (n_ord > 0) & okk
+if m.any():
+    A_ = np.vstack([n_ord[m], uses[m] * (sp[m, 7] > sp[m, 6]), np.ones(m.sum())]).T
+    coef = np.linalg.lstsq(A_, sp[m, 7], rcond=None)[0]
+    print('ordered pass: %d envs with ordered agents, %.1f agents each on average (max %d); cycles ~ %.0f per agent + %.0f per successful use there + %.0f' % (
+        m.sum(), n_ord[m].mean(), n_ord[m].max(), coef[0], coef[1], coef[2]))
+    for k in (1, 2, 3, 4, 6, 8, 12):
+        mk = m & (n_ord == k)
+        if mk.any(): print('  %2d ordered agents: %4d envs, ordered pass mean %6.0f p90 %6.0f cycles' % (k, mk.sum(), sp[mk, 7].mean(), np.percentile(sp[mk, 7], 90)))
