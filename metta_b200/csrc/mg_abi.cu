@@ -577,7 +577,10 @@ static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const u
   const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
   const int cpl_t = cpl <= 1 ? 1 : cpl <= 2 ? 2 : cpl <= 4 ? 4 : 8;
   const size_t smem = (size_t)(slot + MG_OBS_DESC_BYTES(cpl_t)) * MG_OBS_WARPS;
-  if (mask == nullptr) {
+  if (mask == nullptr && cpl_t == 4 && b.A < MG_OBS_WARPS) {  // few agents per env: rows back to back, no idle warps
+    const dim3 fgrid((unsigned)(((b.env_end - b.env_begin) * b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
+    MG_LAUNCH((mg_obs_kernel<4, false, true>), fgrid, MG_OBS_WARPS * 32, smem, s, b, mask);
+  } else if (mask == nullptr) {
     if (cpl_t == 1) { MG_LAUNCH((mg_obs_kernel<1, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else if (cpl_t == 2) { MG_LAUNCH((mg_obs_kernel<2, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else if (cpl_t == 4) { MG_LAUNCH((mg_obs_kernel<4, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }

@@ -1431,14 +1431,26 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 }
 
 // MASKED: only the envs with mask[env] != 0 (mg_reset / mg_compute_observations of some envs); the pass behind a
-// step is the unmasked instantiation, which does not carry the test
-template <int CPL, bool MASKED = true>
+// step is the unmasked instantiation, which does not carry the test.
+// FLAT: the slice's rows back to back, grid (ceil(rows / MG_OBS_WARPS)), for envs with few agents -- with the
+// default grid (envs, ceil(A / MG_OBS_WARPS)) a 4-agent env would leave half of every CTA's warps without a row.
+template <int CPL, bool MASKED = true, bool FLAT = false>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const int env = b.env_begin + (int)blockIdx.x, ai = (int)blockIdx.y * MG_OBS_WARPS + warp;  // grid: (envs, ceil(A / MG_OBS_WARPS))
-  if (ai >= b.A) return;
+  int env, ai;
+  if (FLAT) {
+    const int row = (int)blockIdx.x * MG_OBS_WARPS + warp;
+    const int e = row / b.A;
+    env = b.env_begin + e;
+    ai = row - e * b.A;
+    if (env >= b.env_end) return;
+  } else {
+    env = b.env_begin + (int)blockIdx.x;
+    ai = (int)blockIdx.y * MG_OBS_WARPS + warp;
+    if (ai >= b.A) return;
+  }
   if (MASKED && mask != nullptr && !mask[env]) return;
   obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 }

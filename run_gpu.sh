@@ -1,4 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-MG_LIB_PATH=build_variants/lib_timing.so MG_CHUNKS=1 python tools/timing_probe.py 4096 flush 12 stagger > gpurun_out/timing_default.txt 2>&1
-tail -10 gpurun_out/timing_default.txt
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 | tee gpurun_out/gpu_tests.txt
+python tools/other_config_split.py 2>&1 | tail -2
+python bench.py --no-cpu-baseline --no-other-configs --steps 100 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('arena %.1f M/s' % (d['value']/1e6))"
