@@ -75,6 +75,7 @@ struct MgEnvs {
   int step_mode;
   int sm_count;
   int q_early, q_late;  // observation CTAs per SM beside / behind the step kernel in queue mode
+  cudaStream_t prio_hi, prio_lo;  // flag mode: the step kernel's stream (its pending CTAs go first) and the observation kernel's
   // mg_step_host_begin .. mg_step_host_end: what _end still has to do
   struct HostPending {
     bool active = false, staged = false;
@@ -184,6 +185,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   e->ev_fork = nullptr;
   e->capture_stream = nullptr;
   for (int i = 0; i < MG_MAX_CHUNKS; i++) { e->chunk_stream[i] = nullptr; e->ev_join[i] = nullptr; }
+  e->prio_hi = e->prio_lo = nullptr;
   e->cfg_host.assign(cfg, cfg + n_words);
   MgBatch& b = e->b;
   b.num_envs = num_envs;
@@ -417,6 +419,20 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
                                 (int)(sizeof(StepSmem<32>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
   CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<MG_MAX_AGENTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(sizeof(StepSmem<MG_MAX_AGENTS>) * MG_STEP_WARPS + MG_CFG_SMEM_LIMIT)));
+  // Kernels whose shared-memory carve-outs differ do not share an SM: a CTA of the observation kernel would wait
+  // until the SM has drained of step CTAs (and the other way round) and the two kernels of a step would only
+  // overlap at SM granularity. Ask for the same carve-out for all of them (MG_SMEM_CARVEOUT: per cent of the
+  // maximum; 0 = leave the choice to the driver).
+  if (const char* v = getenv("MG_SMEM_CARVEOUT")) {
+    const int pct = atoi(v);
+    if (pct > 0) {
+      CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<32>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+      CUDA_TRY(cudaFuncSetAttribute(mg_step_kernel<MG_MAX_AGENTS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+      CUDA_TRY(cudaFuncSetAttribute((mg_obs_kernel<4, false>), cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+      CUDA_TRY(cudaFuncSetAttribute((mg_obs_kernel<4, false, false, true>), cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+      CUDA_TRY(cudaFuncSetAttribute((mg_obs_kernel<4, true>), cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    }
+  }
 #endif
   // slices of about 1024 envs: measured on B200, 4096 arena envs in the bench's steady state, 2 slices 701 M
   // agent-steps/s, 3: 706, 4: 729-738, 6: 722, 8: 720, 12: 704
@@ -433,7 +449,7 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   if (e->chunks_host > MG_MAX_CHUNKS) e->chunks_host = MG_MAX_CHUNKS;
   e->step_mode = MG_DEFAULT_STEP_MODE;
   if (const char* env_mode = getenv("MG_STEP_MODE"))  // tuning knob: "sliced", "queue", "fused"
-    e->step_mode = strcmp(env_mode, "queue") == 0 ? 1 : (strcmp(env_mode, "fused") == 0 ? 2 : 0);
+    e->step_mode = strcmp(env_mode, "queue") == 0 ? 1 : (strcmp(env_mode, "fused") == 0 ? 2 : (strcmp(env_mode, "flags") == 0 ? 3 : 0));
   e->q_early = MG_QUEUE_OBS_CTAS_EARLY;
   e->q_late = MG_QUEUE_OBS_CTAS_LATE;
   if (const char* v = getenv("MG_QUEUE_EARLY")) e->q_early = atoi(v);
@@ -450,6 +466,12 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   for (int i = 0; i < (e->chunks_host < 2 ? 2 : e->chunks_host); i++) {
     CUDA_TRY(cudaStreamCreateWithFlags(&e->chunk_stream[i], cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
+  }
+  {
+    int least = 0, greatest = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    CUDA_TRY(cudaStreamCreateWithPriority(&e->prio_hi, cudaStreamNonBlocking, greatest));
+    CUDA_TRY(cudaStreamCreateWithPriority(&e->prio_lo, cudaStreamNonBlocking, least));
   }
   *out = e;
   return MG_OK;
@@ -470,6 +492,8 @@ void mg_destroy(void* h) {
   if (e->hgraph) cudaGraphDestroy(e->hgraph);
   if (e->capture_stream) cudaStreamDestroy(e->capture_stream);
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->prio_hi) cudaStreamDestroy(e->prio_hi);
+  if (e->prio_lo) cudaStreamDestroy(e->prio_lo);
   for (int i = 0; i < MG_MAX_CHUNKS; i++) {
     if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
     if (e->chunk_stream[i]) cudaStreamDestroy(e->chunk_stream[i]);
@@ -571,13 +595,16 @@ int mg_set_buffers(void* h, void* obs, void* terminals, void* truncations, void*
   return MG_OK;
 }
 
-static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask, bool count = true) {
+static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const uint8_t* mask, bool count = true, bool wait_flags = false) {
   const dim3 grid((unsigned)(b.env_end - b.env_begin), (unsigned)((b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
   const int slot = (b.T * 3 + 16 + 15) & ~15;
   const int cpl = (b.obs_cells + 31) / 32;  // window cells per lane: 11x11 -> 4
   const int cpl_t = cpl <= 1 ? 1 : cpl <= 2 ? 2 : cpl <= 4 ? 4 : 8;
   const size_t smem = (size_t)(slot + MG_OBS_DESC_BYTES(cpl_t)) * MG_OBS_WARPS;
-  if (mask == nullptr && cpl_t == 4 && b.A < MG_OBS_WARPS) {  // few agents per env: rows back to back, no idle warps
+  if (wait_flags) {  // flag mode (arena-sized windows only; enqueue_flag_step checks)
+    const dim3 wgrid(grid.y, grid.x);  // groups fastest: the CTAs of one env are dispatched together, envs in the order they finish
+    MG_LAUNCH((mg_obs_kernel<4, false, false, true>), wgrid, MG_OBS_WARPS * 32, smem, s, b, mask);
+  } else if (mask == nullptr && cpl_t == 4 && b.A < MG_OBS_WARPS) {  // few agents per env: rows back to back, no idle warps
     const dim3 fgrid((unsigned)(((b.env_end - b.env_begin) * b.A + MG_OBS_WARPS - 1) / MG_OBS_WARPS));
     MG_LAUNCH((mg_obs_kernel<4, false, true>), fgrid, MG_OBS_WARPS * 32, smem, s, b, mask);
   } else if (mask == nullptr) {
@@ -713,6 +740,37 @@ static int enqueue_queue_step(MgEnvs* e, cudaStream_t s) {
 #endif
 
 #ifndef MG_SIMT_EMU
+// Flag mode: [begin] -> { step kernel, whole batch, on the high-priority stream } beside { observation kernel,
+// whole batch, on the low-priority stream: every CTA waits for its env's mark }, joined back into `s`. The
+// observation kernel keeps its shape (one short-lived warp per row); rows are encoded as soon as their env is
+// done and an SM has room, instead of when the slowest env of a slice is done.
+static bool flags_supported(const MgBatch& b) {
+  const int cpl = (b.obs_cells + 31) / 32;
+  return ((size_t)b.A * sizeof(AgentRec)) % 128 == 0 && cpl > 2 && cpl <= 4;
+}
+static int enqueue_flag_step(MgEnvs* e, cudaStream_t s) {
+  MgBatch b = e->b;
+  int rc;
+  if ((rc = begin_obs_pass(e, s)) != MG_OK) return rc;
+  MG_LAUNCH(mg_queue_begin_kernel, 1, 32, 0, s, b.qctl);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaEventRecord(e->ev_fork, s));
+  CUDA_TRY(cudaStreamWaitEvent(e->prio_hi, e->ev_fork, 0));
+  CUDA_TRY(cudaStreamWaitEvent(e->prio_lo, e->ev_fork, 0));
+  b.env_flags = 1;
+  if ((rc = launch_step_slice(e, b, e->prio_hi)) != MG_OK) return rc;
+  b.after_step = 1;
+  if ((rc = launch_obs_slice(e, b, e->prio_lo, nullptr, true, true)) != MG_OK) return rc;
+  CUDA_TRY(cudaEventRecord(e->ev_join[0], e->prio_hi));
+  CUDA_TRY(cudaEventRecord(e->ev_join[1], e->prio_lo));
+  CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[0], 0));
+  CUDA_TRY(cudaStreamWaitEvent(s, e->ev_join[1], 0));
+  return MG_OK;
+}
+#endif
+
+#ifndef MG_SIMT_EMU
 }  // extern "C" (templates below)
 // Fused mode: one persistent kernel steps the envs and encodes their observations (mg_fused_kernel).
 template <int MAXA, int CPL>
@@ -814,7 +872,8 @@ static int capture_step_graph(MgEnvs* e, const MgHostTargets* ht, cudaGraph_t* g
   const long long before = e->launches;
   CUDA_TRY(cudaStreamBeginCapture(e->capture_stream, cudaStreamCaptureModeThreadLocal));
   int rc;
-  if (e->step_mode == 2 && fused_supported(e->b)) rc = enqueue_fused_step(e, e->capture_stream, ht);
+  if (e->step_mode == 3 && ht == nullptr && flags_supported(e->b)) rc = enqueue_flag_step(e, e->capture_stream);
+  else if (e->step_mode == 2 && fused_supported(e->b)) rc = enqueue_fused_step(e, e->capture_stream, ht);
   else if (e->step_mode == 1 && ht == nullptr && handover_supported(e->b)) rc = enqueue_queue_step(e, e->capture_stream);
   else rc = enqueue_chunked_step(e, e->capture_stream, ht);
   cudaError_t end = cudaStreamEndCapture(e->capture_stream, graph);

@@ -1278,8 +1278,20 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_STEP_WARPS * 32, MG_STEP_MIN_CTAS) mg_step_ke
 #endif
   const int env = b.env_begin + blockIdx.x * MG_STEP_WARPS + warp;
   if (env >= b.env_end) return;
-  step_smem_init<MAXA>(smem[warp], lane, false);
+  step_smem_init<MAXA>(smem[warp], lane, b.env_flags != 0);
   step_env_warp<MAXA>(b, smem[warp], env, lane);
+#ifndef MG_SIMT_EMU
+  if (b.env_flags) {  // hand-over mode: every lane's writes first, then the env's entry in the order of completion
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+      const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&b.qctl->epoch);
+      const uint32_t pos = atomicAdd(&b.qctl->tail, 1u);
+      const unsigned long long v = ((unsigned long long)epoch << 32) | (unsigned long long)(uint32_t)env;
+      asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(b.queue + pos), "l"(v) : "memory");
+    }
+  }
+#endif
 }
 
 #ifndef MG_SIMT_EMU
@@ -1434,12 +1446,43 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 // step is the unmasked instantiation, which does not carry the test.
 // FLAT: the slice's rows back to back, grid (ceil(rows / MG_OBS_WARPS)), for envs with few agents -- with the
 // default grid (envs, ceil(A / MG_OBS_WARPS)) a 4-agent env would leave half of every CTA's warps without a row.
-template <int CPL, bool MASKED = true, bool FLAT = false>
+// WAIT (hand-over mode): the kernel is launched beside the step kernel; CTA x takes the x-th env to finish its
+// step (the step kernel appends finished envs to a queue), so CTAs are dispatched in the order their work
+// becomes available and only the ones at the frontier wait (bounded: a broken launch ends with the error flag
+// of the queue block instead of a hung GPU).
+template <int CPL, bool MASKED = true, bool FLAT = false, bool WAIT = false>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   int env, ai;
+#ifndef MG_SIMT_EMU
+  int handed = -1;
+#ifdef MG_TIMING
+  unsigned long long t_dispatch = 0;
+  if (WAIT && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_dispatch));
+#endif
+  if (WAIT) {
+    MG_SHARED int s_env;
+    if (threadIdx.x == 0) {
+      const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&b.qctl->epoch);
+      const unsigned long long* entry = b.queue + blockIdx.y;  // grid (groups, envs): an env's CTAs are dispatched together
+      const long long t0 = clock64();
+      int got = -1;
+      for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(entry) : "memory");
+        if ((uint32_t)(v >> 32) == epoch) { got = (int)(uint32_t)v; break; }
+        if (clock64() - t0 > 6000000000ll) { atomicExch(&b.qctl->error, 1u); break; }
+        MG_NANOSLEEP(100);
+      }
+      s_env = got;
+    }
+    __syncthreads();
+    handed = s_env;
+    if (handed < 0) return;
+  }
+#endif
   if (FLAT) {
     const int row = (int)blockIdx.x * MG_OBS_WARPS + warp;
     const int e = row / b.A;
@@ -1449,10 +1492,28 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   } else {
     env = b.env_begin + (int)blockIdx.x;
     ai = (int)blockIdx.y * MG_OBS_WARPS + warp;
+#ifndef MG_SIMT_EMU
+    if (WAIT) { env = handed; ai = (int)blockIdx.x * MG_OBS_WARPS + warp; }
+#endif
     if (ai >= b.A) return;
   }
   if (MASKED && mask != nullptr && !mask[env]) return;
+#if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
+  if (WAIT && threadIdx.x == 0 && blockIdx.x == 0 && b.dbg != nullptr) {  // probe: when this env's first CTA was dispatched, and when its env was there
+    unsigned long long t_go;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_go));
+    b.dbg[(size_t)env * 16 + 13] = (uint32_t)t_dispatch;
+    b.dbg[(size_t)env * 16 + 14] = (uint32_t)t_go;
+  }
+#endif
   obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
+#if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
+  if (WAIT && threadIdx.x == 0 && blockIdx.x == 0 && b.dbg != nullptr) {
+    unsigned long long t_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+    b.dbg[(size_t)env * 16 + 15] = (uint32_t)t_end;
+  }
+#endif
 }
 
 #ifndef MG_SIMT_EMU

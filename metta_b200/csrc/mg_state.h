@@ -127,6 +127,7 @@ struct MgBatch {
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
+  int32_t env_flags;           // flag mode: the step kernel marks every finished env in queue[env], the observation kernel waits per env
   int32_t after_step;          // this observation pass follows a step: envs whose episode just ended are summed into episode_accum here
   int32_t cfg_words;           // length of cfg in int32 words, including what mg_create appends to the blob
   // derived from the config once, on the host (mg_create):

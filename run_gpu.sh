@@ -1,4 +1,19 @@
 #!/bin/bash
-mkdir -p gpurun_out
-for v in w1 w2 w4; do echo $v; MG_LIB_PATH=build_variants/lib_$v.so python tools/other_config_split.py 2>&1 | tail -2; done
-echo default; python tools/other_config_split.py 2>&1 | tail -2
+mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "flag_mode" 2>&1 | tail -3 | tee gpurun_out/gpu_tests.txt
+MG_LIB_PATH=build_variants/lib_timing_w1c28.so MG_STEP_MODE=flags python tools/handover_probe.py 2>&1 | tail -10 | tee gpurun_out/handover.txt
+B="timeout 300 python bench.py --no-cpu-baseline --no-other-configs --steps 100"
+run() { name=$1; shift; env "$@" $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
+run default A=1
+run flags MG_STEP_MODE=flags
+for v in w1c28 w4c7; do run flags_$v MG_STEP_MODE=flags MG_LIB_PATH=build_variants/lib_$v.so; done
+python - <<'PY' | tee gpurun_out/summary.txt
+import json,glob
+for f in sorted(glob.glob('gpurun_out/bench_*.json')):
+    try:
+        d=json.loads(open(f).read().strip().splitlines()[-1])
+        pk=d['roofline']['per_kernel']; sm=d['step_ms']
+        print('%-28s %7.1f M/s  %.4f ms  frac %.3f  step %.4f obs %.4f free %7.1f  min %.4f med %.4f p90 %.4f max %.4f' % (f.split('/')[-1], d['value']/1e6, d['ms_per_step'], d['roofline']['frac'], pk['mg_step_kernel']['ms'], pk['mg_obs_kernel']['ms'], d['free_running']['value']/1e6, sm['min'], sm['median'], sm['p90'], sm['max']))
+    except Exception as ex:
+        print(f, 'FAILED', ex); print(open(f.replace('.json','.err')).read()[-500:])
+PY

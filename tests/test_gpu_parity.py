@@ -136,6 +136,24 @@ def test_queue_mode_matches_oracle(lib, monkeypatch):
     ls.close()
 
 
+@pytest.mark.parametrize("n", [40, 1500])
+def test_flag_mode_matches_oracle(n, lib, monkeypatch):
+    """MG_STEP_MODE=flags: the observation kernel runs beside the step kernel and every CTA waits for its
+    env's mark. Same results as the default sliced launch, across episode ends (auto-reset), also with more
+    envs than fit beside each other on the GPU's SMs at the observation kernel's CTA size."""
+    monkeypatch.setenv("MG_STEP_MODE", "flags")
+    cfg = make_arena(24, max_steps=25)
+    cfg.game.episode_truncates = True
+    low = lower_game_config(cfg.game, 62, 62)
+    ls = Lockstep(cfg, arena_maps(low, 4, seed=6), num_envs=n, seeds=np.arange(n) + 70, cuda=True)
+    rng = np.random.RandomState(9)
+    for s in range(60 if n < 100 else 8):
+        ls.step(rng.randint(0, 5, size=n * 24))
+    ls.compare_state()
+    ls.batch.sync()
+    ls.close()
+
+
 @pytest.mark.skipif(not ref_loader.available(), reason="compiled reference (oracle/_ref) not present")
 def test_arena_vs_compiled_reference(lib):
     cfg = make_arena(24)
