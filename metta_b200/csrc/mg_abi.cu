@@ -467,12 +467,14 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
     CUDA_TRY(cudaStreamCreateWithFlags(&e->chunk_stream[i], cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
   }
+#ifndef MG_SIMT_EMU
   {
     int least = 0, greatest = 0;
     CUDA_TRY(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     CUDA_TRY(cudaStreamCreateWithPriority(&e->prio_hi, cudaStreamNonBlocking, greatest));
     CUDA_TRY(cudaStreamCreateWithPriority(&e->prio_lo, cudaStreamNonBlocking, least));
   }
+#endif
   *out = e;
   return MG_OK;
 }
