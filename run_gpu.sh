@@ -1,19 +1,9 @@
 #!/bin/bash
-mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
-timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "flag_mode" 2>&1 | tail -3 | tee gpurun_out/gpu_tests.txt
-MG_LIB_PATH=build_variants/lib_timing_w1c28.so MG_STEP_MODE=flags python tools/handover_probe.py 2>&1 | tail -10 | tee gpurun_out/handover.txt
-B="timeout 300 python bench.py --no-cpu-baseline --no-other-configs --steps 100"
-run() { name=$1; shift; env "$@" $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
-run default A=1
-run flags MG_STEP_MODE=flags
-for v in w1c28 w4c7; do run flags_$v MG_STEP_MODE=flags MG_LIB_PATH=build_variants/lib_$v.so; done
-python - <<'PY' | tee gpurun_out/summary.txt
-import json,glob
-for f in sorted(glob.glob('gpurun_out/bench_*.json')):
-    try:
-        d=json.loads(open(f).read().strip().splitlines()[-1])
-        pk=d['roofline']['per_kernel']; sm=d['step_ms']
-        print('%-28s %7.1f M/s  %.4f ms  frac %.3f  step %.4f obs %.4f free %7.1f  min %.4f med %.4f p90 %.4f max %.4f' % (f.split('/')[-1], d['value']/1e6, d['ms_per_step'], d['roofline']['frac'], pk['mg_step_kernel']['ms'], pk['mg_obs_kernel']['ms'], d['free_running']['value']/1e6, sm['min'], sm['median'], sm['p90'], sm['max']))
-    except Exception as ex:
-        print(f, 'FAILED', ex); print(open(f.replace('.json','.err')).read()[-500:])
-PY
+mkdir -p gpurun_out
+python tools/profile_steady.py > gpurun_out/profile_plain.log 2>&1 || exit 1
+ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_launches.csv python tools/profile_steady.py > gpurun_out/ncu_launches.log 2>&1
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:mg_obs_kernel -c 1 -o gpurun_out/r02_obs -f python tools/profile_steady.py > gpurun_out/ncu_obs.log 2>&1
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:mg_step_kernel -c 1 -o gpurun_out/r02_step -f python tools/profile_steady.py > gpurun_out/ncu_step.log 2>&1
+python bench.py > gpurun_out/bench_r02.json 2> gpurun_out/bench_r02.err
+python bench.py --impl reference --steps 20 --warmup 2 > gpurun_out/bench_r02_reference.json 2> gpurun_out/bench_r02_reference.err
+tail -c 300 gpurun_out/bench_r02.err
