@@ -1460,7 +1460,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   int handed = -1;
 #ifdef MG_TIMING
   unsigned long long t_dispatch = 0;
-  if (WAIT && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_dispatch));
+  if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_dispatch));
 #endif
   if (WAIT) {
     MG_SHARED int s_env;
@@ -1499,7 +1499,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
   }
   if (MASKED && mask != nullptr && !mask[env]) return;
 #if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
-  if (WAIT && threadIdx.x == 0 && blockIdx.x == 0 && b.dbg != nullptr) {  // probe: when this env's first CTA was dispatched, and when its env was there
+  if (threadIdx.x == 0 && (WAIT ? blockIdx.x == 0 : blockIdx.y == 0) && b.dbg != nullptr && b.after_step) {  // probe: when this env's first CTA was dispatched, and when its env was there
     unsigned long long t_go;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_go));
     b.dbg[(size_t)env * 16 + 13] = (uint32_t)t_dispatch;
@@ -1508,7 +1508,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
 #endif
   obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 #if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
-  if (WAIT && threadIdx.x == 0 && blockIdx.x == 0 && b.dbg != nullptr) {
+  if (threadIdx.x == 0 && (WAIT ? blockIdx.x == 0 : blockIdx.y == 0) && b.dbg != nullptr && b.after_step) {
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
     b.dbg[(size_t)env * 16 + 15] = (uint32_t)t_end;

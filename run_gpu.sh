@@ -1,9 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python tools/profile_steady.py > gpurun_out/profile_plain.log 2>&1 || exit 1
-ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_launches.csv python tools/profile_steady.py > gpurun_out/ncu_launches.log 2>&1
-ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:mg_obs_kernel -c 1 -o gpurun_out/r02_obs -f python tools/profile_steady.py > gpurun_out/ncu_obs.log 2>&1
-ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:mg_step_kernel -c 1 -o gpurun_out/r02_step -f python tools/profile_steady.py > gpurun_out/ncu_step.log 2>&1
-python bench.py > gpurun_out/bench_r02.json 2> gpurun_out/bench_r02.err
-python bench.py --impl reference --steps 20 --warmup 2 > gpurun_out/bench_r02_reference.json 2> gpurun_out/bench_r02_reference.err
-tail -c 300 gpurun_out/bench_r02.err
+MG_LIB_PATH=build_variants/lib_timing.so python tools/handover_probe.py 2>&1 | tail -11 | tee gpurun_out/handover_sliced.txt
+MG_LIB_PATH=build_variants/lib_timing.so MG_CHUNKS=1 python tools/handover_probe.py 2>&1 | tail -11 | tee -a gpurun_out/handover_sliced.txt

@@ -24,7 +24,7 @@ for s in range(5):
     act.copy_(torch.randint(0, 5, (N*A,), dtype=torch.int32, device=dev)); flush.fill_(s); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); b.step(torch.cuda.current_stream().cuda_stream); e1.record(); torch.cuda.synchronize()
-print('step ms', e0.elapsed_time(e1))
+print('mode', os.environ.get('MG_STEP_MODE', 'sliced'), 'step ms (CUDA events around the call)', e0.elapsed_time(e1))
 sp = b.read_buffer(16, np.uint32, (N, 16)).astype(np.int64)
 start = sp[:, 10]; cyc = sp[:, :10].sum(1) + sp[:, 11]
 t0 = start.min()
@@ -40,4 +40,5 @@ print('obs CTA found its env       ', pct(go))
 print('obs row done                ', pct(done))
 print('wait inside the CTA         ', pct(go - disp))
 print('env done -> obs starts      ', pct(go - s_end))
+print('first step warp -> last group-0 row done: %.1f us' % done.max())
 b.close()
