@@ -1,4 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-MG_LIB_PATH=build_variants/lib_timing.so python tools/handover_probe.py 2>&1 | tail -11 | tee gpurun_out/handover_sliced.txt
-MG_LIB_PATH=build_variants/lib_timing.so MG_CHUNKS=1 python tools/handover_probe.py 2>&1 | tail -11 | tee -a gpurun_out/handover_sliced.txt
+for i in 1 2; do
+python bench.py --no-cpu-baseline --no-other-configs --steps 100 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('arena %.1f M/s %.4f ms free %.1f' % (d['value']/1e6, d['ms_per_step'], d['free_running']['value']/1e6), d['step_ms'])"
+done
