@@ -434,8 +434,8 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
     }
   }
 #endif
-  // slices of about 1024 envs: measured on B200, 4096 arena envs in the bench's steady state, 2 slices 701 M
-  // agent-steps/s, 3: 706, 4: 729-738, 6: 722, 8: 720, 12: 704
+  // slices of about 1024 envs: measured on B200, 4096 arena envs in the bench's steady state, 2 slices 935 M
+  // agent-steps/s, 3: 934, 4: 954, 6: 945, 8: 921
   e->chunks = (num_envs + 1023) / 1024;
   if (e->chunks > 12) e->chunks = 12;
   if (const char* env_chunks = getenv("MG_CHUNKS")) e->chunks = atoi(env_chunks);  // tuning knob

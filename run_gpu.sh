@@ -1,12 +1,16 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -2 | tee gpurun_out/gpu_tests.txt
-python bench.py > gpurun_out/bench_r02.json 2> gpurun_out/bench_r02.err
-python bench.py --impl reference --steps 20 --warmup 2 > gpurun_out/bench_r02_reference.json 2> gpurun_out/bench_r02_reference.err
-python - <<'PY'
-import json
-d=json.loads(open('gpurun_out/bench_r02.json').read().strip().splitlines()[-1])
-print('value %.1f M/s ms %.4f frac %.3f e2e %.1f' % (d['value']/1e6, d['ms_per_step'], d['roofline']['frac'], d['e2e']['value']/1e6), {k:round(v['value']/1e6,1) for k,v in d['e2e']['modes'].items()})
-print({k:round(v['value']/1e6,1) for k,v in d['other_configs'].items()}, 'cpu', d['cpu_baseline']['value'])
-r=json.loads(open('gpurun_out/bench_r02_reference.json').read().strip().splitlines()[-1]); print('reference %.2f M/s' % (r['value']/1e6))
+mkdir -p gpurun_out; rm -f gpurun_out/bench_*.json gpurun_out/bench_*.err
+B="timeout 300 python bench.py --no-cpu-baseline --no-other-configs --steps 100"
+run() { name=$1; shift; env "$@" $B > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
+run default A=1
+run obsw4 MG_LIB_PATH=build_variants/lib_obsw4.so
+python - <<'PY' | tee gpurun_out/summary.txt
+import json,glob
+for f in sorted(glob.glob('gpurun_out/bench_*.json')):
+    try:
+        d=json.loads(open(f).read().strip().splitlines()[-1])
+        pk=d['roofline']['per_kernel']; sm=d['step_ms']
+        print('%-28s %7.1f M/s  %.4f ms  frac %.3f  step %.4f obs %.4f free %7.1f  min %.4f med %.4f p90 %.4f max %.4f' % (f.split('/')[-1], d['value']/1e6, d['ms_per_step'], d['roofline']['frac'], pk['mg_step_kernel']['ms'], pk['mg_obs_kernel']['ms'], d['free_running']['value']/1e6, sm['min'], sm['median'], sm['p90'], sm['max']))
+    except Exception as ex:
+        print(f, 'FAILED', ex); print(open(f.replace('.json','.err')).read()[-500:])
 PY
