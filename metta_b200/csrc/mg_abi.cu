@@ -612,6 +612,9 @@ static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const u
   } else if (mask == nullptr) {
     if (cpl_t == 1) { MG_LAUNCH((mg_obs_kernel<1, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else if (cpl_t == 2) { MG_LAUNCH((mg_obs_kernel<2, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+    else if (cpl_t == 4 && b.row_len == nullptr && b.max_flip == nullptr && b.obs_mask == nullptr) {
+      MG_LAUNCH((mg_obs_kernel<4, false, false, false, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask);
+    }
     else if (cpl_t == 4) { MG_LAUNCH((mg_obs_kernel<4, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else { MG_LAUNCH((mg_obs_kernel<8, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   } else if (cpl_t == 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }

@@ -1337,16 +1337,18 @@ MG_GLOBAL void mg_queue_begin_kernel(MgQueueCtl* ctl) {
 // What the observation pass leaves behind per row besides the row itself: token counts for the stats fold of
 // the next step, the side outputs for the policy (row length, running maximum, padding mask), and the
 // episode sums when this step ended the episode.
+// AUX = false: the caller knows that none of the three optional outputs is bound (the tests are compiled out)
+template <bool AUX = true>
 MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, size_t g, int attempted, uint32_t done_word, int lane) {
   const int written = attempted < b.T ? attempted : b.T;
   if (lane == 0) {
     uint16_t* tc = b.tok_counts + (size_t)g * 2;
     tc[0] = (uint16_t)written;
     tc[1] = (uint16_t)attempted;
-    if (b.row_len != nullptr) b.row_len[g] = written;
+    if (AUX && b.row_len != nullptr) b.row_len[g] = written;
     // the running maximum only moves a few times per pass: look before bumping it, so that nearly
     // all rows do without an atomic on the one shared word
-    if (b.max_flip != nullptr && written > MG_LD_L2(b.max_flip)) atomicMax(b.max_flip, written);
+    if (AUX && b.max_flip != nullptr && written > MG_LD_L2(b.max_flip)) atomicMax(b.max_flip, written);
   }
   {
     if ((done_word & 0xFFu) != 0u) {  // the episode ended in this step: add it to the batch accumulators
@@ -1355,7 +1357,7 @@ MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, siz
         accum_add(&b.episode_accum[2 + b.S + MG_GS_TOKENS_WRITTEN + lane], (float)(lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written)));
     }
   }
-  if (b.obs_mask != nullptr) {  // 8 slots per lane and round; a row of T bytes starts 8-byte aligned when T % 8 == 0
+  if (AUX && b.obs_mask != nullptr) {  // 8 slots per lane and round; a row of T bytes starts 8-byte aligned when T % 8 == 0
     uint8_t* m = b.obs_mask + (size_t)g * b.T;
     if ((b.T & 7) == 0) {
       for (int j0 = lane * 8; j0 < b.T; j0 += 256) {
@@ -1371,7 +1373,7 @@ MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, siz
 
 // One agent's row by one warp. `warp_smem`: this warp's (slot + MG_OBS_DESC_BYTES(CPL)) bytes of shared
 // memory, 16-byte aligned: [row image | cell descriptors].
-template <int CPL>
+template <int CPL, bool AUX = true>
 MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* warp_smem) {
   const size_t g = (size_t)env * b.A + ai;  // global agent index
   const int row_bytes = b.T * 3;
@@ -1441,7 +1443,7 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 #ifdef MG_OBS_DONE_LATE
   const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
 #endif
-  obs_row_finish_warp(b, env, ai, g, attempted, done_word, lane);
+  obs_row_finish_warp<AUX>(b, env, ai, g, attempted, done_word, lane);
 }
 
 // MASKED: only the envs with mask[env] != 0 (mg_reset / mg_compute_observations of some envs); the pass behind a
@@ -1452,7 +1454,8 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 // step (the step kernel appends finished envs to a queue), so CTAs are dispatched in the order their work
 // becomes available and only the ones at the frontier wait (bounded: a broken launch ends with the error flag
 // of the queue block instead of a hung GPU).
-template <int CPL, bool MASKED = true, bool FLAT = false, bool WAIT = false>
+// AUX = false: row lengths, their maximum and the padding mask are not bound (mg_set_obs_aux).
+template <int CPL, bool MASKED = true, bool FLAT = false, bool WAIT = false, bool AUX = true>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
@@ -1508,7 +1511,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
     b.dbg[(size_t)env * 16 + 14] = (uint32_t)t_go;
   }
 #endif
-  obs_row_warp<CPL>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
+  obs_row_warp<CPL, AUX>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 #if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
   if (threadIdx.x == 0 && (WAIT ? blockIdx.x == 0 : blockIdx.y == 0) && b.dbg != nullptr && b.after_step) {
     unsigned long long t_end;
