@@ -200,6 +200,9 @@ int mg_create(const int32_t* cfg, int64_t n_words, int32_t num_envs, int32_t dev
   b.max_chest = cfg[MGC_MAX_CHESTS] > 0 ? cfg[MGC_MAX_CHESTS] : 1;
   b.has_clipper = (cfg + cfg[MGC_OFF_CLIPPER])[MG_CLIP_ENABLED];
   b.obs_cells = cfg[MGC_OBS_H] * cfg[MGC_OBS_W];
+  b.obs_hr = cfg[MGC_OBS_H] >> 1;
+  b.obs_wr = cfg[MGC_OBS_W] >> 1;
+  b.feat_cooldown = cfg[MGC_FEAT_COOLDOWN];
   b.grid_stride = ((b.H * b.W + 63) / 64) * 64;  // whole 128-byte lines per env (see mg_fused_kernel)
   b.auto_reset = 1;
   b.map_stride = 0;

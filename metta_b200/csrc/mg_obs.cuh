@@ -46,11 +46,10 @@ MG_DEVICE inline uint64_t load_pattern_run(const uint8_t* pattern, int lane) {
 // window cells per lane (CPL * 32 >= obs_h * obs_w).
 template <int CPL>
 MG_DEVICE inline int obs_count_cells_warp(const MgBatch& b, int env, int ai, int lane, uint32_t current_step) {
-  const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
   const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
-  const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
+  const int hr = b.obs_hr, wr = b.obs_wr;
   const int n_global = b.gtok[((size_t)env * b.A + ai) * MG_GTOK_STRIDE];
   const uint8_t* ebase = b.etok + (((size_t)env * b.rec_slots) << b.rec_shift);
   const uint64_t kind_base = (uint64_t)b.rec_kind_base_lo | ((uint64_t)b.rec_kind_base_hi << 32);
@@ -84,7 +83,6 @@ MG_DEVICE inline int obs_count_cells_warp(const MgBatch& b, int env, int ai, int
 template <int CPL>
 MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step,
                                          int fill_words = 0) {
-  const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
   const uint32_t pos_rc = *reinterpret_cast<const uint32_t*>(b.agents + (size_t)env * b.A + ai);  // r | c << 16
   // ---- global tokens: prepared by the step kernel (a count, then up to 21 triples in a 64-byte record)
@@ -103,7 +101,7 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
     __syncwarp();
   }
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
-  const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
+  const int hr = b.obs_hr, wr = b.obs_wr;
   const int T = b.T;
   uint32_t* cells = reinterpret_cast<uint32_t*>(desc) + CPL * 32;
   {
@@ -195,7 +193,7 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
 
   // ---- pass 2: one token per lane
   const int end = pos_base < T ? pos_base : T;
-  const uint32_t cooldown_feature = (uint32_t)cfg[MGC_FEAT_COOLDOWN];
+  const uint32_t cooldown_feature = (uint32_t)b.feat_cooldown;
   int before = 0;  // descriptors that start before this group of 32 tokens
   for (int t0 = n_global; t0 < end; t0 += 32) {
     const int t = t0 + lane;
@@ -227,9 +225,8 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
 // instead of per agent (an env's reset runs it for every agent of the env on one warp).
 template <int CPL, int U>
 MG_DEVICE inline void obs_count_group_warp(const MgBatch& b, int env, int ai0, int n, int lane, uint32_t current_step, int* totals) {
-  const int32_t* cfg = b.cfg;
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
-  const int hr = cfg[MGC_OBS_H] >> 1, wr = cfg[MGC_OBS_W] >> 1;
+  const int hr = b.obs_hr, wr = b.obs_wr;
   const uint8_t* ebase = b.etok + (((size_t)env * b.rec_slots) << b.rec_shift);
   const uint64_t kind_base = (uint64_t)b.rec_kind_base_lo | ((uint64_t)b.rec_kind_base_hi << 32);
   const uint64_t locs = load_pattern_run<CPL>(b.pattern, lane);

@@ -124,6 +124,8 @@ struct MgQueueCtl {
 struct MgBatch {
   int32_t num_envs, A, H, W, T, R, S, GS, max_asm, max_chest, num_maps, has_clipper;
   int32_t obs_cells;           // obs_h * obs_w
+  int32_t obs_hr, obs_wr;      // obs_h / 2, obs_w / 2 (the window's radius), and
+  int32_t feat_cooldown;       // the feature id of cooldown_remaining: launch parameters, so that the observation kernel does not fetch them from the config
   int32_t grid_stride;         // cells per env grid, padded to a multiple of 8 (16-byte rows)
   int32_t auto_reset, map_stride;
   int32_t env_begin, env_end;  // the slice of envs this launch works on (the step is launched in chunks)
