@@ -1338,9 +1338,10 @@ MG_GLOBAL void mg_queue_begin_kernel(MgQueueCtl* ctl) {
 // the next step, the side outputs for the policy (row length, running maximum, padding mask), and the
 // episode sums when this step ended the episode.
 // AUX = false: the caller knows that none of the three optional outputs is bound (the tests are compiled out)
-template <bool AUX = true>
+template <bool AUX = true, int TT = 0>
 MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, size_t g, int attempted, uint32_t done_word, int lane) {
-  const int written = attempted < b.T ? attempted : b.T;
+  const int T = TT ? TT : b.T;
+  const int written = attempted < T ? attempted : T;
   if (lane == 0) {
     uint16_t* tc = b.tok_counts + (size_t)g * 2;
     tc[0] = (uint16_t)written;
@@ -1354,7 +1355,7 @@ MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, siz
     if ((done_word & 0xFFu) != 0u) {  // the episode ended in this step: add it to the batch accumulators
       accumulate_agent_warp(b, env, ai, lane);
       if (lane < 3)  // this pass's own token counts (folded into the game stats only when the next step starts)
-        accum_add(&b.episode_accum[2 + b.S + MG_GS_TOKENS_WRITTEN + lane], (float)(lane == 0 ? written : (lane == 1 ? attempted - written : b.T - written)));
+        accum_add(&b.episode_accum[2 + b.S + MG_GS_TOKENS_WRITTEN + lane], (float)(lane == 0 ? written : (lane == 1 ? attempted - written : T - written)));
     }
   }
   if (AUX && b.obs_mask != nullptr) {  // 8 slots per lane and round; a row of T bytes starts 8-byte aligned when T % 8 == 0
@@ -1372,62 +1373,27 @@ MG_DEVICE inline void obs_row_finish_warp(const MgBatch& b, int env, int ai, siz
 }
 
 // One agent's row by one warp. `warp_smem`: this warp's (slot + MG_OBS_DESC_BYTES(CPL)) bytes of shared
-// memory, 16-byte aligned: [row image | cell descriptors].
-template <int CPL, bool AUX = true>
+// memory, 16-byte aligned: [row image | cell descriptors]. TT > 0: the caller knows the token count per row
+// (TT, a multiple of 8) and that the observation buffer is 8-byte aligned, so sizes, loop bounds and the
+// alignment test are compile-time constants.
+template <int CPL, bool AUX = true, int TT = 0>
 MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* warp_smem) {
   const size_t g = (size_t)env * b.A + ai;  // global agent index
-  const int row_bytes = b.T * 3;
-  const int slot = b.obs_slot;
+  const int row_bytes = (TT ? TT : b.T) * 3;
+  const int slot = TT ? ((TT * 3 + 16 + 15) & ~15) : b.obs_slot;
   uint8_t* out = b.obs + (size_t)g * row_bytes;
-#ifdef MG_OBS_STORE16
-  const int mis = (int)(reinterpret_cast<uintptr_t>(out) & 15);
-#else
-  const int mis = 0;
-#endif
-  uint8_t* row = warp_smem + mis;  // warp_smem is 16-byte aligned: [row image | cell descriptors]
+  uint8_t* row = warp_smem;
   uint2* desc = reinterpret_cast<uint2*>(warp_smem + slot);
-  // read past L1 (two env records share a cache line, and the fused kernel encodes envs other SMs stepped):
+  // read past L1 (two env records share a cache line, and the hand-over modes encode envs other SMs stepped):
   // the step counter, and whether this step ended the episode (EnvRec::done, byte 40)
   const uint32_t current_step = MG_LD_L2(&b.env[env].current_step);
-#ifndef MG_OBS_DONE_LATE
   const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
-#endif
-#ifdef MG_OBS_STORE16
-  {
-    uint4 ff;
-    ff.x = ff.y = ff.z = ff.w = 0xFFFFFFFFu;
-    uint4* p = reinterpret_cast<uint4*>(warp_smem);
-    const int n16 = slot >> 4;  // 39 for 200 tokens
-    if (lane < n16) p[lane] = ff;
-    if (lane + 32 < n16) p[lane + 32] = ff;
-#pragma unroll 1
-    for (int i = lane + 64; i < n16; i += 32) p[i] = ff;
-  }
-  __syncwarp();
-  const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step);
-#else
   // (the image is filled with 0xFF inside, behind the first loads)
-  const int attempted = obs_emit_agent_warp<CPL>(b, env, ai, lane, row, desc, current_step, slot >> 4);
-#endif
+  const int attempted = obs_emit_agent_warp<CPL, TT>(b, env, ai, lane, row, desc, current_step, slot >> 4);
   __syncwarp();
-#ifdef MG_OBS_STORE16
-  {  // bytes up to the first 16-byte boundary (< 16, one per lane), 16-byte body, byte tail (< 16)
-    const int head = mis == 0 ? 0 : (16 - mis < row_bytes ? 16 - mis : row_bytes);
-    const int n16 = (row_bytes - head) >> 4;
-    const int tail = head + (n16 << 4);
-    if (lane < head) out[lane] = row[lane];
-    const uint4* s = reinterpret_cast<const uint4*>(row + head);
-    uint4* d = reinterpret_cast<uint4*>(out + head);
-    if (lane < n16) d[lane] = s[lane];
-    if (lane + 32 < n16) d[lane + 32] = s[lane + 32];
-#pragma unroll 1
-    for (int i = lane + 64; i < n16; i += 32) d[i] = s[i];
-    if (tail + lane < row_bytes) out[tail + lane] = row[tail + lane];
-  }
-#else
   // store: rows are multiples of 8 bytes for every even token count, and then 8-byte aligned whenever the
   // buffer is: 8-byte chunks, no head or tail
-  if ((row_bytes & 7) == 0 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0) {
+  if (TT || ((row_bytes & 7) == 0 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0)) {
     const uint2* s2 = reinterpret_cast<const uint2*>(row);
     uint2* d2 = reinterpret_cast<uint2*>(out);
     const int n8 = row_bytes >> 3;  // 75 for 200 tokens: three rounds, spelled out (a compiler-unrolled loop cost 79 instructions per row)
@@ -1439,11 +1405,7 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
   } else {
     for (int i = lane; i < row_bytes; i += 32) out[i] = row[i];
   }
-#endif
-#ifdef MG_OBS_DONE_LATE
-  const uint32_t done_word = (b.after_step && b.auto_reset) ? MG_LD_L2(reinterpret_cast<const uint32_t*>(&b.env[env]) + 10) : 0u;
-#endif
-  obs_row_finish_warp<AUX>(b, env, ai, g, attempted, done_word, lane);
+  obs_row_finish_warp<AUX, TT>(b, env, ai, g, attempted, done_word, lane);
 }
 
 // MASKED: only the envs with mask[env] != 0 (mg_reset / mg_compute_observations of some envs); the pass behind a
@@ -1455,7 +1417,8 @@ MG_DEVICE inline void obs_row_warp(const MgBatch& b, int env, int ai, int lane, 
 // becomes available and only the ones at the frontier wait (bounded: a broken launch ends with the error flag
 // of the queue block instead of a hung GPU).
 // AUX = false: row lengths, their maximum and the padding mask are not bound (mg_set_obs_aux).
-template <int CPL, bool MASKED = true, bool FLAT = false, bool WAIT = false, bool AUX = true>
+// TT: see obs_row_warp.
+template <int CPL, bool MASKED = true, bool FLAT = false, bool WAIT = false, bool AUX = true, int TT = 0>
 MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kernel(const MG_GRID_CONSTANT MgBatch b, const uint8_t* mask) {
   MG_DYN_SMEM(dyn);
   const int lane = threadIdx.x & 31;
@@ -1511,7 +1474,7 @@ MG_GLOBAL void MG_LAUNCH_BOUNDS(MG_OBS_WARPS * 32, MG_OBS_MIN_CTAS) mg_obs_kerne
     b.dbg[(size_t)env * 16 + 14] = (uint32_t)t_go;
   }
 #endif
-  obs_row_warp<CPL, AUX>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
+  obs_row_warp<CPL, AUX, TT>(b, env, ai, lane, dyn + warp * b.obs_warp_bytes);
 #if defined(MG_TIMING) && !defined(MG_SIMT_EMU)
   if (threadIdx.x == 0 && (WAIT ? blockIdx.x == 0 : blockIdx.y == 0) && b.dbg != nullptr && b.after_step) {
     unsigned long long t_end;

@@ -80,7 +80,7 @@ MG_DEVICE inline int obs_count_cells_warp(const MgBatch& b, int env, int ai, int
 // `fill_words`: > 0 = first set that many 16-byte words at `row` (the whole image) to 0xFF. The caller's fill is
 // done here so that the loads everything else waits for -- the agent's position, its global tokens, the
 // lane's pattern entries -- are already in flight while the image is filled.
-template <int CPL>
+template <int CPL, int TT = 0>
 MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int lane, uint8_t* row, uint2* desc, uint32_t current_step,
                                          int fill_words = 0) {
   const uint16_t* grid = b.grid + (size_t)env * b.grid_stride;
@@ -102,7 +102,7 @@ MG_DEVICE inline int obs_emit_agent_warp(const MgBatch& b, int env, int ai, int 
   }
   const int my_r = (int)(pos_rc & 0xFFFFu), my_c = (int)(pos_rc >> 16);
   const int hr = b.obs_hr, wr = b.obs_wr;
-  const int T = b.T;
+  const int T = TT ? TT : b.T;
   uint32_t* cells = reinterpret_cast<uint32_t*>(desc) + CPL * 32;
   {
     const int nb = (n_global < T ? n_global : T) * 3;  // <= 63 bytes (MG_GTOK_STRIDE)
