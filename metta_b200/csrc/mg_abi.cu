@@ -615,15 +615,16 @@ static int launch_obs_slice(MgEnvs* e, const MgBatch& b, cudaStream_t s, const u
   } else if (mask == nullptr) {
     if (cpl_t == 1) { MG_LAUNCH((mg_obs_kernel<1, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else if (cpl_t == 2) { MG_LAUNCH((mg_obs_kernel<2, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
-    else if (cpl_t == 4 && b.row_len == nullptr && b.max_flip == nullptr && b.obs_mask == nullptr) {
-      // the reference's default row of 200 tokens in an aligned buffer: sizes and loop bounds as constants
-      if (b.T == 200 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0) {
-        MG_LAUNCH((mg_obs_kernel<4, false, false, false, false, 200>), grid, MG_OBS_WARPS * 32, smem, s, b, mask);
-      } else {
-        MG_LAUNCH((mg_obs_kernel<4, false, false, false, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask);
-      }
+    else if (cpl_t == 4) {
+      // instantiations without the optional side outputs when none is bound, and for the reference's default row
+      // of 200 tokens in an aligned buffer (sizes and loop bounds as constants)
+      const bool aux = b.row_len != nullptr || b.max_flip != nullptr || b.obs_mask != nullptr;
+      const bool t200 = b.T == 200 && (reinterpret_cast<uintptr_t>(b.obs) & 7) == 0;
+      if (!aux && t200) { MG_LAUNCH((mg_obs_kernel<4, false, false, false, false, 200>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+      else if (!aux) { MG_LAUNCH((mg_obs_kernel<4, false, false, false, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+      else if (t200) { MG_LAUNCH((mg_obs_kernel<4, false, false, false, true, 200>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
+      else { MG_LAUNCH((mg_obs_kernel<4, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     }
-    else if (cpl_t == 4) { MG_LAUNCH((mg_obs_kernel<4, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
     else { MG_LAUNCH((mg_obs_kernel<8, false>), grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   } else if (cpl_t == 1) { MG_LAUNCH(mg_obs_kernel<1>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
   else if (cpl_t == 2) { MG_LAUNCH(mg_obs_kernel<2>, grid, MG_OBS_WARPS * 32, smem, s, b, mask); }
